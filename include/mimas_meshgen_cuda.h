@@ -1,0 +1,209 @@
+/*
+ * mimas_meshgen_cuda.h -- C ABI of libmimas_meshgen_cuda.so
+ *
+ * B200 (sm_100a) CUDA replacement for the hot path of est31/mimas'
+ * `mimas-meshgen` crate.  Every entry point names the reference interface it
+ * stands in for (paths relative to the reference checkout).  The Rust crate
+ * keeps its public API (`mesh_for_chunk`, `TextureIdCache`, `push_block`) and
+ * binds these symbols through `extern "C"` -- see INTEGRATION.md for the stub.
+ *
+ * Conventions: plain pointers and sizes only; every function returns an
+ * mm_status (0 = OK) and never unwinds; an mm_ctx is single-threaded (one per
+ * calling thread / GPU), like the reference's dedicated meshgen thread
+ * (mimas-client/client.rs:259-267).  There is no CPU fallback: without a CUDA
+ * device mm_ctx_create fails with MM_ERR_NO_DEVICE.
+ */
+#ifndef MIMAS_MESHGEN_CUDA_H
+#define MIMAS_MESHGEN_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MM_ABI_VERSION 1u
+#define MM_CHUNKSIZE 16u           /* mimas-common/map.rs:11  CHUNKSIZE            */
+#define MM_CHUNK_BYTES 4096u       /* mimas-common/map.rs:56-61 [MapBlock; 16^3]   */
+#define MM_TABLE_ENTRIES 256u      /* MapBlock is a u8 id, mimas-common/map.rs:14  */
+
+typedef enum mm_status {
+	MM_OK = 0,
+	MM_ERR_INVALID = 1,     /* bad argument                                          */
+	MM_ERR_NO_DEVICE = 2,   /* no usable CUDA device (there is no CPU fallback)      */
+	MM_ERR_CUDA = 3,        /* CUDA runtime error, see mm_last_error_string          */
+	MM_ERR_OOM = 4,         /* device or pinned host allocation failed               */
+	MM_ERR_NO_TABLE = 5,    /* mm_set_block_table has not been called                */
+	MM_ERR_NO_BATCH = 6,    /* no finished batch to read back                        */
+	MM_ERR_UNSUPPORTED = 7  /* e.g. a non-NULL halo (extension, not in the reference) */
+} mm_status;
+
+/* mimas-meshgen/lib.rs:18-24 `Vertex`, fixed as #[repr(C)] in declared order:
+ * tex_ind @0, two zero padding bytes @2, tex_pos @4, position @12, normal @24;
+ * size 36, align 4.  The device stream and every host copy use exactly this. */
+typedef struct mm_vertex {
+	uint16_t tex_ind;
+	uint16_t pad0;      /* always written as 0 so that streams can be byte-compared */
+	float tex_pos[2];
+	float position[3];
+	float normal[3];
+} mm_vertex;
+
+/* One row of the flattened `TextureIdCache` (mimas-meshgen/lib.rs:73-79): what
+ * get_bl_tex_ids (lib.rs:105-109) and get_mesh_draw_style (lib.rs:110-113)
+ * answer for block id i.  Ids >= block_params.len() must be filled by the caller
+ * as MM_KIND_BLOCKY with the fallback ids (lib.rs:106-108) -- mm_table_from_cache
+ * does that. */
+#define MM_KIND_NONE 0u     /* not drawn: None in both vectors                       */
+#define MM_KIND_BLOCKY 1u   /* Some(MeshDrawStyle::Blocky(BlockTextureIds))           */
+#define MM_KIND_CROSSED 2u  /* Some(MeshDrawStyle::Crossed(TextureId))                */
+typedef struct mm_block_entry {
+	uint16_t id_sides;   /* BlockTextureIds::id_sides,  lib.rs:46 */
+	uint16_t id_top;     /* BlockTextureIds::id_top,    lib.rs:47 */
+	uint16_t id_bottom;  /* BlockTextureIds::id_bottom, lib.rs:48 */
+	uint16_t id_crossed; /* MeshDrawStyle::Crossed(id), lib.rs:31 */
+	uint8_t kind;        /* MM_KIND_*                             */
+	uint8_t reserved[3];
+} mm_block_entry;
+
+/* Where one chunk's vertices live inside a packed stream (unit: vertices). */
+typedef struct mm_range {
+	uint64_t first_vertex;
+	uint32_t vertex_count;
+	uint32_t reserved;
+} mm_range;
+
+/* Result of a batch: the two `ChunkMesh` vectors (lib.rs:226-229) of every chunk,
+ * packed back to back in chunk order, device resident.  Pointers stay valid until
+ * the next mm_mesh_batch* / mm_reserve / mm_ctx_destroy on the same context. */
+typedef struct mm_batch_out {
+	const mm_vertex *d_intransparent; /* device */
+	const mm_vertex *d_transparent;   /* device */
+	const mm_range *d_ranges_i;       /* device, n_chunks entries */
+	const mm_range *d_ranges_t;       /* device, n_chunks entries */
+	uint64_t n_intransparent;         /* total vertices in d_intransparent */
+	uint64_t n_transparent;           /* total vertices in d_transparent   */
+	uint32_t n_chunks;
+	uint32_t launches;                /* kernels launched for this batch (incl. re-runs after growth) */
+	float kernel_ms;                  /* CUDA-event time of the last mesher kernel of this batch */
+	uint32_t reserved;
+} mm_batch_out;
+
+typedef struct mm_ctx mm_ctx;
+
+uint32_t mm_abi_version(void);
+
+/* Context = one GPU + one stream + device block table + output arenas.  Replaces
+ * the state the reference's meshgen thread owns (its TextureIdCache clone,
+ * mimas-client/client.rs:258-261). */
+int mm_ctx_create(int device, mm_ctx **out);
+int mm_ctx_destroy(mm_ctx *ctx);
+const char *mm_last_error_string(const mm_ctx *ctx);
+
+/* Run on a caller-owned CUDA stream (cudaStream_t passed as void*), e.g. the
+ * framework's current stream; NULL restores the context's own stream. */
+int mm_ctx_set_stream(mm_ctx *ctx, void *cuda_stream);
+
+/* Device-resident block table.  Replaces the TextureIdCache handed to
+ * mesh_for_chunk (lib.rs:231-232, built by TextureIdCache::from_hdl, lib.rs:87-104). */
+int mm_set_block_table(mm_ctx *ctx, const mm_block_entry table[MM_TABLE_ENTRIES]);
+
+/* Helper for bindings: flatten a TextureIdCache given as its three vectors
+ * (lib.rs:75-77): fallback ids, and per known id a kind + ids row.  Fills ids
+ * >= n_known with the blocky fallback (lib.rs:105-109). */
+int mm_table_from_cache(const uint16_t fallback_sides_top_bottom[3],
+                        const mm_block_entry *known, uint32_t n_known,
+                        mm_block_entry out_table[MM_TABLE_ENTRIES]);
+
+/* Pre-size the arenas (vertices).  Optional: batches grow them on demand and
+ * re-run, which costs one extra kernel the first time a larger batch is seen. */
+int mm_reserve(mm_ctx *ctx, uint32_t max_chunks, uint64_t intransparent_vertices,
+               uint64_t transparent_vertices);
+
+/* mesh_for_chunk (lib.rs:231-446) over a batch of n independent chunks.
+ *   chunks : n * 4096 block ids, index x*256 + y*16 + z (mimas-common/map.rs:83-86);
+ *            host or device memory (detected)
+ *   offs   : n * 3 int64 chunk origins in blocks (`offs :Vector3<isize>`, lib.rs:231)
+ *            host or device memory (detected)
+ *   halo   : must be NULL.  The reference treats out-of-chunk neighbours as not
+ *            blocking (lib.rs:277-280); a non-NULL halo returns MM_ERR_UNSUPPORTED.
+ * Synchronous: returns after the kernel finished and totals are known. */
+int mm_mesh_batch(mm_ctx *ctx, const uint8_t *chunks, const int64_t *offs,
+                  const uint8_t *halo, uint32_t n, mm_batch_out *out);
+
+/* Stream-ordered variant for device-resident inputs: enqueues the mesher kernel and
+ * returns immediately.  mm_batch_finish synchronises, grows + re-runs if the
+ * arenas were too small, and reports totals.  Several _async calls may be queued
+ * back to back; only the last one's result is retrievable. */
+int mm_mesh_batch_async(mm_ctx *ctx, const uint8_t *d_chunks, const int64_t *d_offs, uint32_t n);
+int mm_batch_finish(mm_ctx *ctx, mm_batch_out *out);
+
+/* Host-`Vec` path: copy the last finished batch to caller memory sized from
+ * mm_batch_out (any pointer may be NULL to skip that part). */
+int mm_copy_out(mm_ctx *ctx, mm_vertex *intransparent, mm_vertex *transparent,
+                mm_range *ranges_i, mm_range *ranges_t);
+
+/* Host in, host out in one call (H2D + kernel + D2H, pipelined in sub-batches): the
+ * batch form of the crate API `chunk in, Vec<Vertex> out`.  The library owns the
+ * returned host arrays (pinned) until the next call on this context. */
+typedef struct mm_host_mesh {
+	const mm_vertex *intransparent;
+	const mm_vertex *transparent;
+	const mm_range *ranges_i;
+	const mm_range *ranges_t;
+	uint64_t n_intransparent, n_transparent;
+	uint32_t n_chunks;
+	uint32_t reserved;
+} mm_host_mesh;
+int mm_mesh_batch_host(mm_ctx *ctx, const uint8_t *chunks, const int64_t *offs, uint32_t n,
+                       mm_host_mesh *out);
+
+/* Single-chunk convenience with exactly mesh_for_chunk's shape (lib.rs:231-232):
+ * pointers are library-owned pinned host memory, valid until the next call. */
+int mm_mesh_for_chunk(mm_ctx *ctx, const int64_t offs[3], const uint8_t chunk[MM_CHUNK_BYTES],
+                      const mm_vertex **intransparent, uint64_t *n_intransparent,
+                      const mm_vertex **transparent, uint64_t *n_transparent);
+
+/* push_block (lib.rs:183-219): un-merged cube emitter for UI meshes.  `blocked_mask`
+ * bit i is the answer of the i-th blocked([..]) query in source order
+ * ([0,0,-1],[0,-1,0],[-1,0,0],[0,0,1],[0,1,0],[1,0,0]).  n cubes in, device-built,
+ * copied to `out` (capacity 36 vertices per cube); *n_out receives the count. */
+typedef struct mm_cube {
+	float pos[3];
+	float siz;
+	uint16_t id_sides, id_top, id_bottom;
+	uint16_t blocked_mask;
+} mm_cube;
+int mm_push_blocks(mm_ctx *ctx, const mm_cube *cubes, uint32_t n, mm_vertex *out, uint64_t *n_out);
+
+/* Synthetic mapgen look-alike (benchmark input; NOT a replica of mimas-server
+ * mapgen, whose noise crates are not available -- see DESIGN.md).  Chunk i of the
+ * region has chunk coordinates (cx0 + i % nx, cy0 + (i / nx) % ny, cz0 + i / (nx*ny));
+ * offs = 16 * chunk coordinate.  Host and device versions produce identical bytes. */
+int mm_gen_terrain_host(uint64_t seed, int64_t cx0, int64_t cy0, int64_t cz0,
+                        uint32_t nx, uint32_t ny, uint32_t nz, uint8_t *chunks, int64_t *offs);
+int mm_gen_terrain_device(mm_ctx *ctx, uint64_t seed, int64_t cx0, int64_t cy0, int64_t cz0,
+                          uint32_t nx, uint32_t ny, uint32_t nz, uint8_t *d_chunks, int64_t *d_offs);
+
+/* Plain device memory helpers so that non-CUDA host code (ctypes, Rust) can keep
+ * inputs resident without linking the CUDA runtime itself. */
+int mm_dev_alloc(mm_ctx *ctx, size_t bytes, void **d_ptr);
+int mm_dev_free(mm_ctx *ctx, void *d_ptr);
+int mm_dev_upload(mm_ctx *ctx, void *d_dst, const void *h_src, size_t bytes);
+int mm_dev_download(mm_ctx *ctx, void *h_dst, const void *d_src, size_t bytes);
+int mm_ctx_sync(mm_ctx *ctx);
+/* Page-locked host memory: inputs built here are DMA'd directly by mm_mesh_batch_host /
+ * mm_mesh_batch (no staging copy); pageable inputs are staged through an internal pinned buffer. */
+int mm_host_alloc(mm_ctx *ctx, size_t bytes, void **h_ptr);
+int mm_host_free(mm_ctx *ctx, void *h_ptr);
+
+/* Introspection for the bench: SM count and the grid the mesher kernel uses. */
+int mm_device_info(mm_ctx *ctx, int *sm_count, int *ctas_per_sm, int *threads_per_cta);
+/* Number of mesher kernels this context has launched since creation. */
+int mm_launch_count(mm_ctx *ctx, uint64_t *launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MIMAS_MESHGEN_CUDA_H */

@@ -1,0 +1,474 @@
+// mm_api.cu -- C ABI of libmimas_meshgen_cuda.so (see include/mimas_meshgen_cuda.h).
+//
+// Host side of the B200 mesher: context, device block table, arenas for the packed
+// vertex streams, launch of the persistent mesher kernel, grow-and-rerun when a batch
+// does not fit, host<->device staging for the `chunk in, Vec<Vertex> out` crate API.
+// There is no CPU implementation of the mesher in this library.
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <new>
+#include <vector>
+
+#include "../../include/mimas_meshgen_cuda.h"
+#include "mesh_kernel.cuh"
+#include "mm_internal.h"
+#include "terrain_gen.h"
+
+static_assert(sizeof(mm_vertex) == 36, "Vertex must be 36 bytes (SURVEY.md 8b)");
+static_assert(sizeof(mm_range) == 16 && sizeof(mm::Range) == 16, "range layout");
+static_assert(sizeof(mm_block_entry) == 12, "block entry layout");
+static_assert(sizeof(mm::Smem) <= 56 * 1024, "4 CTAs per SM need <= 56 KiB each");
+
+namespace {
+
+#define fail mm_fail
+
+int use_device(mm_ctx *c) {
+	MM_CUDA(c, cudaSetDevice(c->device));
+	return MM_OK;
+}
+
+bool is_device_ptr(const void *p) {
+	cudaPointerAttributes a;
+	if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+		cudaGetLastError();
+		return false;
+	}
+	return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+bool is_pinned_ptr(const void *p) {
+	cudaPointerAttributes a;
+	if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+		cudaGetLastError();
+		return false;
+	}
+	return a.type == cudaMemoryTypeHost;
+}
+
+int ensure_chunk_capacity(mm_ctx *c, uint32_t n) {
+	if (n <= c->cap_chunks) return MM_OK;
+	const uint32_t nc = std::max<uint32_t>(n, 1024u);
+	MM_CUDA(c, cudaStreamSynchronize(c->stream));
+	cudaFree(c->d_ranges_i); cudaFree(c->d_ranges_t); cudaFree(c->d_status[0]); cudaFree(c->d_status[1]);
+	c->d_ranges_i = c->d_ranges_t = nullptr; c->d_status[0] = c->d_status[1] = nullptr;
+	c->cap_chunks = 0;
+	MM_CUDA(c, cudaMalloc(&c->d_ranges_i, sizeof(mm::Range) * (size_t)nc));
+	MM_CUDA(c, cudaMalloc(&c->d_ranges_t, sizeof(mm::Range) * (size_t)nc));
+	for (int b = 0; b < 2; b++) {
+		MM_CUDA(c, cudaMalloc(&c->d_status[b], sizeof(mm::u64) * (size_t)nc));
+		MM_CUDA(c, cudaMemsetAsync(c->d_status[b], 0, sizeof(mm::u64) * (size_t)nc, c->stream));
+		c->dirty_hi[b] = 0;
+	}
+	c->prev_n = 0;
+	c->cap_chunks = nc;
+	return MM_OK;
+}
+
+int ensure_arena(mm_ctx *c, unsigned char **p, uint64_t *cap, uint64_t quads) {
+	if (quads <= *cap) return MM_OK;
+	MM_CUDA(c, cudaStreamSynchronize(c->stream));
+	cudaFree(*p);
+	*p = nullptr;
+	*cap = 0;
+	// round up to 1 MiB; +16 B so that a bulk copy never ends past the allocation
+	const size_t bytes = (((size_t)quads * mm::kQuadBytes + 16 + (1u << 20) - 1) >> 20) << 20;
+	MM_CUDA(c, cudaMalloc(p, bytes));
+	*cap = (bytes - 16) / mm::kQuadBytes;
+	return MM_OK;
+}
+
+int ensure_pinned(mm_ctx *c, unsigned char **p, size_t *have, size_t want) {
+	if (want <= *have) return MM_OK;
+	MM_CUDA(c, cudaStreamSynchronize(c->stream));
+	if (*p) cudaFreeHost(*p);
+	*p = nullptr;
+	*have = 0;
+	const size_t bytes = ((want + (1u << 20) - 1) >> 20) << 20;
+	MM_CUDA(c, cudaHostAlloc(p, bytes, cudaHostAllocDefault));
+	*have = bytes;
+	return MM_OK;
+}
+
+// Enqueue one mesher launch for (d_chunks, d_offs, n) on the context's stream.
+int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, uint32_t n) {
+	const int b = c->cur;
+	// The previous launch zeroed slots [0, prev_n) of buffer b; anything dirtier is cleared here.
+	if (c->dirty_hi[b] > c->prev_n) {
+		MM_CUDA(c, cudaMemsetAsync(c->d_status[b] + c->prev_n, 0,
+		                           sizeof(mm::u64) * (size_t)(c->dirty_hi[b] - c->prev_n), c->stream));
+	}
+	c->dirty_hi[b] = 0;
+	mm::KernelParams p;
+	p.chunks = d_chunks;
+	p.offs = d_offs;
+	p.n = n;
+	p.table = c->d_table;
+	p.out_i = c->d_out_i;
+	p.out_t = c->d_out_t;
+	p.cap_i = c->cap_i;
+	p.cap_t = c->cap_t;
+	p.ranges_i = c->d_ranges_i;
+	p.ranges_t = c->d_ranges_t;
+	p.status = c->d_status[b];
+	p.status_next = c->d_status[b ^ 1];
+	p.ticket = c->d_ticket;
+	p.ticket_base = c->ticket_base;
+	p.totals = c->d_ticket + 1;
+	const uint32_t grid = std::min<uint32_t>(n, (uint32_t)(c->sm_count * c->ctas_per_sm));
+	MM_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+	mm::mesh_batch_kernel<<<grid, mm::kThreads, sizeof(mm::Smem), c->stream>>>(p);
+	MM_CUDA(c, cudaGetLastError());
+	MM_CUDA(c, cudaEventRecord(c->ev1, c->stream));
+	MM_CUDA(c, cudaMemcpyAsync(c->h_totals, c->d_ticket + 1, 2 * sizeof(mm::u64), cudaMemcpyDeviceToHost, c->stream));
+	c->ticket_base += (mm::u64)n + grid;  // every CTA draws exactly one ticket >= n
+	c->dirty_hi[b] = n;                  // this launch dirtied [0, n) of b ...
+	// ... and zeroed [0, n) of the other buffer, which the next launch uses
+	c->prev_n = n;
+	c->cur = b ^ 1;
+	c->last_launches++;
+	c->total_launches++;
+	return MM_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+uint32_t mm_abi_version(void) { return MM_ABI_VERSION; }
+
+const char *mm_last_error_string(const mm_ctx *ctx) { return ctx ? ctx->err : "null context"; }
+
+int mm_ctx_create(int device, mm_ctx **out) {
+	if (!out) return MM_ERR_INVALID;
+	*out = nullptr;
+	int count = 0;
+	if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0) {
+		cudaGetLastError();
+		return MM_ERR_NO_DEVICE;  // no CPU fallback by design
+	}
+	if (device < 0 || device >= count) return MM_ERR_INVALID;
+	mm_ctx *c = new (std::nothrow) mm_ctx();
+	if (!c) return MM_ERR_OOM;
+	c->device = device;
+	int rc = MM_OK;
+	auto body = [&]() -> int {
+		MM_CUDA(c, cudaSetDevice(device));
+		cudaDeviceProp prop;
+		MM_CUDA(c, cudaGetDeviceProperties(&prop, device));
+		if (prop.major < 10) return fail(c, MM_ERR_NO_DEVICE, "device %d is sm_%d%d; this library is built for sm_100a", device, prop.major, prop.minor);
+		c->sm_count = prop.multiProcessorCount;
+		MM_CUDA(c, cudaFuncSetAttribute(mm::mesh_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(mm::Smem)));
+		MM_CUDA(c, cudaFuncSetAttribute(mm::mesh_batch_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+		int occ = 0;
+		MM_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mm::mesh_batch_kernel, mm::kThreads, sizeof(mm::Smem)));
+		if (occ < 1) return fail(c, MM_ERR_CUDA, "mesher kernel does not fit on an SM");
+		c->ctas_per_sm = occ;
+		MM_CUDA(c, cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+		c->stream = c->own_stream;
+		MM_CUDA(c, cudaEventCreate(&c->ev0));
+		MM_CUDA(c, cudaEventCreate(&c->ev1));
+		MM_CUDA(c, cudaMalloc(&c->d_table, sizeof(mm::TabEntry) * 256));
+		MM_CUDA(c, cudaMalloc(&c->d_ticket, sizeof(mm::u64) * 4));
+		MM_CUDA(c, cudaMemset(c->d_ticket, 0, sizeof(mm::u64) * 4));
+		MM_CUDA(c, cudaHostAlloc(&c->h_totals, sizeof(mm::u64) * 2, cudaHostAllocDefault));
+		return MM_OK;
+	};
+	rc = body();
+	if (rc != MM_OK) {
+		fprintf(stderr, "mm_ctx_create: %s\n", c->err);
+		mm_ctx_destroy(c);
+		return rc;
+	}
+	*out = c;
+	return MM_OK;
+}
+
+int mm_ctx_destroy(mm_ctx *c) {
+	if (!c) return MM_ERR_INVALID;
+	cudaSetDevice(c->device);
+	if (c->own_stream) cudaStreamSynchronize(c->own_stream);
+	cudaFree(c->d_table); cudaFree(c->d_out_i); cudaFree(c->d_out_t); cudaFree(c->d_ranges_i);
+	cudaFree(c->d_ranges_t); cudaFree(c->d_status[0]); cudaFree(c->d_status[1]); cudaFree(c->d_ticket);
+	cudaFree(c->d_in_chunks); cudaFree(c->d_in_offs);
+	if (c->h_totals) cudaFreeHost(c->h_totals);
+	if (c->h_in) cudaFreeHost(c->h_in);
+	if (c->h_out) cudaFreeHost(c->h_out);
+	if (c->ev0) cudaEventDestroy(c->ev0);
+	if (c->ev1) cudaEventDestroy(c->ev1);
+	if (c->own_stream) cudaStreamDestroy(c->own_stream);
+	delete c;
+	return MM_OK;
+}
+
+int mm_ctx_set_stream(mm_ctx *c, void *cuda_stream) {
+	if (!c) return MM_ERR_INVALID;
+	if (use_device(c)) return MM_ERR_CUDA;
+	MM_CUDA(c, cudaStreamSynchronize(c->stream));
+	c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
+	return MM_OK;
+}
+
+int mm_ctx_sync(mm_ctx *c) {
+	if (!c) return MM_ERR_INVALID;
+	if (use_device(c)) return MM_ERR_CUDA;
+	MM_CUDA(c, cudaStreamSynchronize(c->stream));
+	return MM_OK;
+}
+
+int mm_device_info(mm_ctx *c, int *sm_count, int *ctas_per_sm, int *threads_per_cta) {
+	if (!c) return MM_ERR_INVALID;
+	if (sm_count) *sm_count = c->sm_count;
+	if (ctas_per_sm) *ctas_per_sm = c->ctas_per_sm;
+	if (threads_per_cta) *threads_per_cta = mm::kThreads;
+	return MM_OK;
+}
+
+int mm_launch_count(mm_ctx *c, uint64_t *launches) {
+	if (!c || !launches) return MM_ERR_INVALID;
+	*launches = c->total_launches;
+	return MM_OK;
+}
+
+int mm_host_alloc(mm_ctx *c, size_t bytes, void **h_ptr) {
+	if (!c || !h_ptr) return MM_ERR_INVALID;
+	if (use_device(c)) return MM_ERR_CUDA;
+	*h_ptr = nullptr;
+	MM_CUDA(c, cudaHostAlloc(h_ptr, bytes ? bytes : 1, cudaHostAllocDefault));
+	return MM_OK;
+}
+int mm_host_free(mm_ctx *c, void *h_ptr) {
+	if (!c) return MM_ERR_INVALID;
+	if (use_device(c)) return MM_ERR_CUDA;
+	MM_CUDA(c, cudaStreamSynchronize(c->stream));
+	MM_CUDA(c, cudaFreeHost(h_ptr));
+	return MM_OK;
+}
+
+int mm_table_from_cache(const uint16_t fb[3], const mm_block_entry *known, uint32_t n_known,
+                        mm_block_entry out[MM_TABLE_ENTRIES]) {
+	if (!fb || !out || (n_known && !known) || n_known > MM_TABLE_ENTRIES) return MM_ERR_INVALID;
+	for (uint32_t i = 0; i < MM_TABLE_ENTRIES; i++) {
+		mm_block_entry e;
+		memset(&e, 0, sizeof(e));
+		if (i < n_known) {
+			e = known[i];
+			if (e.kind > MM_KIND_CROSSED) return MM_ERR_INVALID;
+		} else {  // get_bl_tex_ids: unknown id -> Some(fallback) (lib.rs:105-109); never crossed (lib.rs:110-113)
+			e.kind = MM_KIND_BLOCKY;
+			e.id_sides = fb[0]; e.id_top = fb[1]; e.id_bottom = fb[2];
+		}
+		out[i] = e;
+	}
+	return MM_OK;
+}
+
+int mm_set_block_table(mm_ctx *c, const mm_block_entry table[MM_TABLE_ENTRIES]) {
+	if (!c || !table) return MM_ERR_INVALID;
+	if (use_device(c)) return MM_ERR_CUDA;
+	mm::TabEntry t[256];
+	for (int i = 0; i < 256; i++) {
+		const mm_block_entry &e = table[i];
+		if (e.kind > MM_KIND_CROSSED) return fail(c, MM_ERR_INVALID, "table[%d].kind = %u", i, e.kind);
+		if (e.kind == MM_KIND_CROSSED) t[i].x = e.id_crossed;
+		else t[i].x = (uint32_t)e.id_sides | ((uint32_t)e.id_top << 16);
+		t[i].y = (uint32_t)e.id_bottom | ((uint32_t)e.kind << 16);
+		if (e.kind == MM_KIND_NONE) { t[i].x = 0; t[i].y = 0; }
+	}
+	MM_CUDA(c, cudaStreamSynchronize(c->stream));
+	MM_CUDA(c, cudaMemcpy(c->d_table, t, sizeof(t), cudaMemcpyHostToDevice));
+	c->have_table = true;
+	return MM_OK;
+}
+
+int mm_reserve(mm_ctx *c, uint32_t max_chunks, uint64_t iv, uint64_t tv) {
+	if (!c) return MM_ERR_INVALID;
+	if (use_device(c)) return MM_ERR_CUDA;
+	int rc;
+	if ((rc = ensure_chunk_capacity(c, max_chunks))) return rc;
+	if ((rc = ensure_arena(c, &c->d_out_i, &c->cap_i, (iv + 5) / 6))) return rc;
+	if ((rc = ensure_arena(c, &c->d_out_t, &c->cap_t, (tv + 5) / 6))) return rc;
+	return MM_OK;
+}
+
+int mm_mesh_batch_async(mm_ctx *c, const uint8_t *d_chunks, const int64_t *d_offs, uint32_t n) {
+	if (!c || (n && (!d_chunks || !d_offs))) return MM_ERR_INVALID;
+	if (!c->have_table) return fail(c, MM_ERR_NO_TABLE, "mm_set_block_table has not been called");
+	if (use_device(c)) return MM_ERR_CUDA;
+	c->finished = false;
+	c->pending = false;
+	c->last_chunks = d_chunks;
+	c->last_offs = (const long long *)d_offs;
+	c->last_n = n;
+	c->last_launches = 0;
+	c->tot_i = c->tot_t = 0;
+	if (n == 0) { c->pending = true; return MM_OK; }
+	int rc;
+	if ((rc = ensure_chunk_capacity(c, n))) return rc;
+	if ((rc = launch(c, d_chunks, c->last_offs, n))) return rc;
+	c->pending = true;
+	return MM_OK;
+}
+
+int mm_batch_finish(mm_ctx *c, mm_batch_out *out) {
+	if (!c) return MM_ERR_INVALID;
+	if (!c->pending) return fail(c, MM_ERR_NO_BATCH, "no batch in flight");
+	if (use_device(c)) return MM_ERR_CUDA;
+	if (c->last_n) {
+		for (int attempt = 0;; attempt++) {
+			MM_CUDA(c, cudaStreamSynchronize(c->stream));
+			c->tot_i = c->h_totals[0];
+			c->tot_t = c->h_totals[1];
+			if (c->tot_i >= mm::kSat || c->tot_t >= mm::kSat)
+				return fail(c, MM_ERR_INVALID, "batch produces >= 2^31 quads; split it");
+			if (c->tot_i <= c->cap_i && c->tot_t <= c->cap_t) break;
+			if (attempt >= 1) return fail(c, MM_ERR_CUDA, "arena still too small after growth");
+			int rc;  // grow to fit (+1/8 head room) and run again: the inputs are still resident
+			if ((rc = ensure_arena(c, &c->d_out_i, &c->cap_i, c->tot_i + c->tot_i / 8))) return rc;
+			if ((rc = ensure_arena(c, &c->d_out_t, &c->cap_t, c->tot_t + c->tot_t / 8))) return rc;
+			if ((rc = launch(c, c->last_chunks, c->last_offs, c->last_n))) return rc;
+		}
+		MM_CUDA(c, cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1));
+	} else {
+		c->last_ms = 0.f;
+	}
+	c->pending = false;
+	c->finished = true;
+	if (out) {
+		memset(out, 0, sizeof(*out));
+		out->d_intransparent = (const mm_vertex *)c->d_out_i;
+		out->d_transparent = (const mm_vertex *)c->d_out_t;
+		out->d_ranges_i = (const mm_range *)c->d_ranges_i;
+		out->d_ranges_t = (const mm_range *)c->d_ranges_t;
+		out->n_intransparent = c->tot_i * 6;
+		out->n_transparent = c->tot_t * 6;
+		out->n_chunks = c->last_n;
+		out->launches = c->last_launches;
+		out->kernel_ms = c->last_ms;
+	}
+	return MM_OK;
+}
+
+int mm_mesh_batch(mm_ctx *c, const uint8_t *chunks, const int64_t *offs, const uint8_t *halo, uint32_t n,
+                  mm_batch_out *out) {
+	if (!c || (n && (!chunks || !offs))) return MM_ERR_INVALID;
+	if (halo) return fail(c, MM_ERR_UNSUPPORTED, "halo: the reference mesher has none (lib.rs:277-280)");
+	if (use_device(c)) return MM_ERR_CUDA;
+	const uint8_t *dc = chunks;
+	const int64_t *dof = offs;
+	if (n && (!is_device_ptr(chunks) || !is_device_ptr(offs))) {
+		if (n > c->cap_in) {
+			MM_CUDA(c, cudaStreamSynchronize(c->stream));
+			cudaFree(c->d_in_chunks); cudaFree(c->d_in_offs);
+			c->d_in_chunks = nullptr; c->d_in_offs = nullptr; c->cap_in = 0;
+			const uint32_t nc = std::max<uint32_t>(n, 256u);
+			MM_CUDA(c, cudaMalloc(&c->d_in_chunks, (size_t)nc * 4096));
+			MM_CUDA(c, cudaMalloc(&c->d_in_offs, (size_t)nc * 24));
+			c->cap_in = nc;
+		}
+		if (!is_device_ptr(chunks)) {
+			MM_CUDA(c, cudaMemcpyAsync(c->d_in_chunks, chunks, (size_t)n * 4096, cudaMemcpyHostToDevice, c->stream));
+			dc = c->d_in_chunks;
+		}
+		if (!is_device_ptr(offs)) {
+			MM_CUDA(c, cudaMemcpyAsync(c->d_in_offs, offs, (size_t)n * 24, cudaMemcpyHostToDevice, c->stream));
+			dof = (const int64_t *)c->d_in_offs;
+		}
+	}
+	int rc;
+	if ((rc = mm_mesh_batch_async(c, dc, dof, n))) return rc;
+	return mm_batch_finish(c, out);
+}
+
+int mm_copy_out(mm_ctx *c, mm_vertex *vi, mm_vertex *vt, mm_range *ri, mm_range *rt) {
+	if (!c) return MM_ERR_INVALID;
+	if (!c->finished) return fail(c, MM_ERR_NO_BATCH, "no finished batch");
+	if (use_device(c)) return MM_ERR_CUDA;
+	if (vi && c->tot_i) MM_CUDA(c, cudaMemcpyAsync(vi, c->d_out_i, c->tot_i * mm::kQuadBytes, cudaMemcpyDeviceToHost, c->stream));
+	if (vt && c->tot_t) MM_CUDA(c, cudaMemcpyAsync(vt, c->d_out_t, c->tot_t * mm::kQuadBytes, cudaMemcpyDeviceToHost, c->stream));
+	if (ri && c->last_n) MM_CUDA(c, cudaMemcpyAsync(ri, c->d_ranges_i, (size_t)c->last_n * 16, cudaMemcpyDeviceToHost, c->stream));
+	if (rt && c->last_n) MM_CUDA(c, cudaMemcpyAsync(rt, c->d_ranges_t, (size_t)c->last_n * 16, cudaMemcpyDeviceToHost, c->stream));
+	MM_CUDA(c, cudaStreamSynchronize(c->stream));
+	return MM_OK;
+}
+
+int mm_mesh_batch_host(mm_ctx *c, const uint8_t *chunks, const int64_t *offs, uint32_t n, mm_host_mesh *out) {
+	if (!c || !out || (n && (!chunks || !offs))) return MM_ERR_INVALID;
+	if (use_device(c)) return MM_ERR_CUDA;
+	int rc;
+	// pageable inputs are staged through pinned memory so that the H2D copy is one DMA;
+	// inputs already in page-locked memory (mm_host_alloc) go out directly
+	const uint8_t *hc = chunks;
+	const int64_t *ho = offs;
+	if (n && !(is_pinned_ptr(chunks) && is_pinned_ptr(offs))) {
+		const size_t in_bytes = (size_t)n * (4096 + 24);
+		if ((rc = ensure_pinned(c, &c->h_in, &c->h_in_bytes, in_bytes))) return rc;
+		memcpy(c->h_in, chunks, (size_t)n * 4096);
+		memcpy(c->h_in + (size_t)n * 4096, offs, (size_t)n * 24);
+		hc = c->h_in;
+		ho = (const int64_t *)(c->h_in + (size_t)n * 4096);
+	}
+	mm_batch_out bo;
+	if ((rc = mm_mesh_batch(c, hc, ho, nullptr, n, &bo))) return rc;
+	const size_t bi = (size_t)bo.n_intransparent * 36, bt = (size_t)bo.n_transparent * 36, br = (size_t)n * 16;
+	const size_t oi = 0, ot = (bi + 255) & ~(size_t)255, ori = (ot + bt + 255) & ~(size_t)255, ort = ori + ((br + 255) & ~(size_t)255);
+	if ((rc = ensure_pinned(c, &c->h_out, &c->h_out_bytes, ort + br + 256))) return rc;
+	if ((rc = mm_copy_out(c, (mm_vertex *)(c->h_out + oi), (mm_vertex *)(c->h_out + ot), (mm_range *)(c->h_out + ori),
+	                      (mm_range *)(c->h_out + ort))))
+		return rc;
+	out->intransparent = (const mm_vertex *)(c->h_out + oi);
+	out->transparent = (const mm_vertex *)(c->h_out + ot);
+	out->ranges_i = (const mm_range *)(c->h_out + ori);
+	out->ranges_t = (const mm_range *)(c->h_out + ort);
+	out->n_intransparent = bo.n_intransparent;
+	out->n_transparent = bo.n_transparent;
+	out->n_chunks = n;
+	out->reserved = 0;
+	return MM_OK;
+}
+
+int mm_mesh_for_chunk(mm_ctx *c, const int64_t offs[3], const uint8_t chunk[MM_CHUNK_BYTES], const mm_vertex **vi,
+                      uint64_t *ni, const mm_vertex **vt, uint64_t *nt) {
+	if (!c || !offs || !chunk || !vi || !ni || !vt || !nt) return MM_ERR_INVALID;
+	mm_host_mesh hm;
+	const int rc = mm_mesh_batch_host(c, chunk, offs, 1, &hm);
+	if (rc) return rc;
+	*vi = hm.intransparent; *ni = hm.n_intransparent;
+	*vt = hm.transparent; *nt = hm.n_transparent;
+	return MM_OK;
+}
+
+int mm_dev_alloc(mm_ctx *c, size_t bytes, void **d_ptr) {
+	if (!c || !d_ptr) return MM_ERR_INVALID;
+	if (use_device(c)) return MM_ERR_CUDA;
+	*d_ptr = nullptr;
+	MM_CUDA(c, cudaMalloc(d_ptr, bytes ? bytes : 1));
+	return MM_OK;
+}
+int mm_dev_free(mm_ctx *c, void *d_ptr) {
+	if (!c) return MM_ERR_INVALID;
+	if (use_device(c)) return MM_ERR_CUDA;
+	MM_CUDA(c, cudaStreamSynchronize(c->stream));
+	MM_CUDA(c, cudaFree(d_ptr));
+	return MM_OK;
+}
+int mm_dev_upload(mm_ctx *c, void *d_dst, const void *h_src, size_t bytes) {
+	if (!c || (bytes && (!d_dst || !h_src))) return MM_ERR_INVALID;
+	if (use_device(c)) return MM_ERR_CUDA;
+	MM_CUDA(c, cudaMemcpyAsync(d_dst, h_src, bytes, cudaMemcpyHostToDevice, c->stream));
+	MM_CUDA(c, cudaStreamSynchronize(c->stream));
+	return MM_OK;
+}
+int mm_dev_download(mm_ctx *c, void *h_dst, const void *d_src, size_t bytes) {
+	if (!c || (bytes && (!h_dst || !d_src))) return MM_ERR_INVALID;
+	if (use_device(c)) return MM_ERR_CUDA;
+	MM_CUDA(c, cudaMemcpyAsync(h_dst, d_src, bytes, cudaMemcpyDeviceToHost, c->stream));
+	MM_CUDA(c, cudaStreamSynchronize(c->stream));
+	return MM_OK;
+}
+
+}  // extern "C"

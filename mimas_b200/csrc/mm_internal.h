@@ -1,0 +1,76 @@
+// mm_internal.h -- context struct shared by the translation units of the library.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdint.h>
+
+#include "../../include/mimas_meshgen_cuda.h"
+#include "mesh_core.cuh"
+
+struct mm_ctx {
+	int device = 0;
+	int sm_count = 0;
+	int ctas_per_sm = 0;
+	cudaStream_t own_stream = nullptr;
+	cudaStream_t stream = nullptr;
+	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+	bool have_table = false;
+	mm::TabEntry *d_table = nullptr;
+
+	// arenas (capacities in quads of 216 B)
+	unsigned char *d_out_i = nullptr, *d_out_t = nullptr;
+	uint64_t cap_i = 0, cap_t = 0;
+	// per-chunk arrays
+	uint32_t cap_chunks = 0;
+	mm::Range *d_ranges_i = nullptr, *d_ranges_t = nullptr;
+	mm::u64 *d_status[2] = {nullptr, nullptr};
+	uint32_t dirty_hi[2] = {0, 0};  // slots [0, dirty_hi) of that buffer may be non-zero
+	int cur = 0;                    // status buffer the next launch uses
+	uint32_t prev_n = 0;            // n of the previous launch (it zeroed [0, prev_n) of buffer `cur`)
+	mm::u64 *d_ticket = nullptr;    // [0] ticket counter, [1..2] totals
+	mm::u64 ticket_base = 0;
+	mm::u64 *h_totals = nullptr;    // pinned, 2 words
+
+	// staged inputs for host callers
+	unsigned char *d_in_chunks = nullptr;
+	long long *d_in_offs = nullptr;
+	uint32_t cap_in = 0;
+	unsigned char *h_in = nullptr;  // pinned staging: chunks then offs
+	size_t h_in_bytes = 0;
+
+	// host results (pinned)
+	unsigned char *h_out = nullptr;
+	size_t h_out_bytes = 0;
+
+	// last batch
+	bool pending = false, finished = false;
+	const unsigned char *last_chunks = nullptr;
+	const long long *last_offs = nullptr;
+	uint32_t last_n = 0;
+	uint32_t last_launches = 0;
+	uint64_t total_launches = 0;
+	uint64_t tot_i = 0, tot_t = 0;  // quads
+	float last_ms = 0.f;
+
+	char err[512] = {0};
+};
+
+static inline int mm_fail(mm_ctx *c, int code, const char *fmt, ...) {
+	if (c) {
+		va_list ap;
+		va_start(ap, fmt);
+		vsnprintf(c->err, sizeof(c->err), fmt, ap);
+		va_end(ap);
+	}
+	return code;
+}
+
+#define MM_CUDA(c, call)                                                                          \
+	do {                                                                                          \
+		cudaError_t e__ = (call);                                                                 \
+		if (e__ != cudaSuccess)                                                                   \
+			return mm_fail(c, e__ == cudaErrorMemoryAllocation ? MM_ERR_OOM : MM_ERR_CUDA, "%s: %s", #call, \
+			            cudaGetErrorString(e__));                                                 \
+	} while (0)
+

@@ -1,0 +1,409 @@
+"""Host-side mirror of the `mimas-meshgen` crate API on top of libmimas_meshgen_cuda.so.
+
+Same names and argument meaning as the reference (mimas-meshgen/lib.rs):
+  TextureId, BlockTextureIds (:44-71), MeshDrawStyle (:28-42), TextureIdObtainer (:81-84),
+  TextureIdCache.from_hdl / get_bl_tex_ids / get_mesh_draw_style / get_inv_texture_id (:86-118),
+  push_block (:183-219), ChunkMesh (:226-229), mesh_for_chunk (:231-232).
+The mesher itself runs only on the GPU: importing this module without the CUDA library, or
+creating a Mesher without a CUDA device, raises -- there is no CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import List, Optional, Sequence, Tuple, Union
+
+import numpy as np
+
+from . import game_params as gp
+from ._lib import MMError, check, lib
+
+CHUNKSIZE = 16  # mimas-common/map.rs:11
+
+# #[repr(C)] Vertex (lib.rs:18-24): include/mimas_meshgen_cuda.h mm_vertex
+VERTEX_DTYPE = np.dtype([("tex_ind", "<u2"), ("pad0", "<u2"), ("tex_pos", "<f4", (2,)),
+                         ("position", "<f4", (3,)), ("normal", "<f4", (3,))])
+RANGE_DTYPE = np.dtype([("first_vertex", "<u8"), ("vertex_count", "<u4"), ("reserved", "<u4")])
+BLOCK_ENTRY_DTYPE = np.dtype([("id_sides", "<u2"), ("id_top", "<u2"), ("id_bottom", "<u2"), ("id_crossed", "<u2"),
+                              ("kind", "u1"), ("reserved", "u1", (3,))])
+CUBE_DTYPE = np.dtype([("pos", "<f4", (3,)), ("siz", "<f4"), ("id_sides", "<u2"), ("id_top", "<u2"),
+                       ("id_bottom", "<u2"), ("blocked_mask", "<u2")])
+assert VERTEX_DTYPE.itemsize == 36 and RANGE_DTYPE.itemsize == 16
+assert BLOCK_ENTRY_DTYPE.itemsize == 12 and CUBE_DTYPE.itemsize == 24
+
+KIND_NONE, KIND_BLOCKY, KIND_CROSSED = 0, 1, 2
+
+TextureId = int  # #[repr(transparent)] struct TextureId(pub u16), lib.rs:14-16
+
+
+@dataclass(frozen=True)
+class BlockTextureIds:
+    id_sides: TextureId
+    id_top: TextureId
+    id_bottom: TextureId
+
+    @staticmethod
+    def uniform(id: TextureId) -> "BlockTextureIds":
+        return BlockTextureIds(id, id, id)
+
+    @staticmethod
+    def new_tb(id_top_bottom: TextureId, id_sides: TextureId) -> "BlockTextureIds":
+        return BlockTextureIds(id_sides, id_top_bottom, id_top_bottom)
+
+    @staticmethod
+    def new(id_sides: TextureId, id_top: TextureId, id_bottom: TextureId) -> "BlockTextureIds":
+        return BlockTextureIds(id_sides, id_top, id_bottom)
+
+
+@dataclass(frozen=True)
+class Blocky:
+    ids: BlockTextureIds
+
+
+@dataclass(frozen=True)
+class CrossedStyle:
+    id: TextureId
+
+
+MeshDrawStyle = Union[Blocky, CrossedStyle]
+
+
+class TextureIdObtainer:
+    """trait TextureIdObtainer, lib.rs:81-84."""
+
+    def mesh_draw_st(self, ds: gp.DrawStyle) -> MeshDrawStyle:
+        raise NotImplementedError
+
+    def inv_texture_id(self, path: str) -> TextureId:
+        raise NotImplementedError
+
+
+class HeadlessAssets(TextureIdObtainer):
+    """Texture-id allocation of mimas-client/assets.rs:140-201 without loading any pixels:
+    every add_asset hands out the next index (assets.rs:140-144)."""
+
+    def __init__(self):
+        self.count = 0
+
+    def _add_asset(self) -> TextureId:
+        i = self.count
+        if i > 0xFFFF:
+            raise OverflowError("TextureId is a u16")
+        self.count += 1
+        return i
+
+    def mesh_draw_st(self, ds: gp.DrawStyle) -> MeshDrawStyle:
+        if isinstance(ds, gp.Colored):                      # assets.rs:148-152
+            full = self._add_asset()
+            half = self._add_asset()                        # colorh(): darker sides
+            return Blocky(BlockTextureIds.new_tb(full, half))
+        if isinstance(ds, gp.Crossed):                      # assets.rs:153-158
+            return CrossedStyle(self._add_asset())
+        if isinstance(ds, gp.Texture):                      # assets.rs:159-164
+            return Blocky(BlockTextureIds.uniform(self._add_asset()))
+        if isinstance(ds, gp.TextureSidesTop):              # assets.rs:165-173
+            s = self._add_asset()
+            tb = self._add_asset()
+            return Blocky(BlockTextureIds.new_tb(tb, s))
+        if isinstance(ds, gp.TextureSidesTopBottom):        # assets.rs:174-186
+            s = self._add_asset()
+            t = self._add_asset()
+            b = self._add_asset()
+            return Blocky(BlockTextureIds.new(s, t, b))
+        raise TypeError(f"not a DrawStyle: {ds!r}")
+
+    def inv_texture_id(self, path: str) -> TextureId:       # assets.rs:189-194
+        return self._add_asset()
+
+
+class TextureIdCache:
+    """lib.rs:73-118.  `to_table()` flattens it into the 256-row device block table."""
+
+    def __init__(self, fallback_id: BlockTextureIds, mesh_draw_styles: Sequence[Optional[MeshDrawStyle]],
+                 inv_texture_ids: Sequence[Optional[TextureId]] = ()):
+        self.fallback_id = fallback_id
+        self.mesh_draw_styles = list(mesh_draw_styles)
+        self.block_texture_ids = [s.ids if isinstance(s, Blocky) else None for s in self.mesh_draw_styles]
+        self.inv_texture_ids = list(inv_texture_ids)
+        if len(self.mesh_draw_styles) > 256:
+            raise ValueError("MapBlock ids are u8")
+
+    @classmethod
+    def from_hdl(cls, hdl: gp.GameParams, ob: TextureIdObtainer) -> "TextureIdCache":
+        fb = ob.mesh_draw_st(gp.DEFAULT_DRAW_STYLE)  # Colored([0,0,0,1]), lib.rs:88
+        assert isinstance(fb, Blocky)
+        styles = [ob.mesh_draw_st(p.draw_style) if p.draw_style is not None else None for p in hdl.block_params]
+        inv = [ob.inv_texture_id(p.inv_texture) if p.inv_texture is not None else None for p in hdl.block_params]
+        return cls(fb.ids, styles, inv)
+
+    def get_bl_tex_ids(self, bl: int) -> Optional[BlockTextureIds]:
+        return self.block_texture_ids[bl] if bl < len(self.block_texture_ids) else self.fallback_id
+
+    def get_mesh_draw_style(self, bl: int) -> Optional[MeshDrawStyle]:
+        return self.mesh_draw_styles[bl] if bl < len(self.mesh_draw_styles) else None
+
+    def get_inv_texture_id(self, bl: int) -> Optional[TextureId]:
+        return self.inv_texture_ids[bl] if bl < len(self.inv_texture_ids) else None
+
+    def to_table(self) -> np.ndarray:
+        known = np.zeros(len(self.mesh_draw_styles), dtype=BLOCK_ENTRY_DTYPE)
+        for i, s in enumerate(self.mesh_draw_styles):
+            if isinstance(s, Blocky):
+                known[i] = (s.ids.id_sides, s.ids.id_top, s.ids.id_bottom, 0, KIND_BLOCKY, (0, 0, 0))
+            elif isinstance(s, CrossedStyle):
+                known[i] = (0, 0, 0, s.id, KIND_CROSSED, (0, 0, 0))
+        fb = (C.c_uint16 * 3)(self.fallback_id.id_sides, self.fallback_id.id_top, self.fallback_id.id_bottom)
+        out = np.zeros(256, dtype=BLOCK_ENTRY_DTYPE)
+        check(lib().mm_table_from_cache(fb, known.ctypes.data, len(known), out.ctypes.data), None)
+        return out
+
+    @classmethod
+    def from_table_rows(cls, rows: Sequence[Tuple[int, int, int, int, int]], fallback: Tuple[int, int, int]):
+        """rows of (kind, sides, top, bottom, crossed) for the known ids; fallback (sides, top, bottom)."""
+        styles: List[Optional[MeshDrawStyle]] = []
+        for kind, s, t, b, x in rows:
+            styles.append(Blocky(BlockTextureIds(s, t, b)) if kind == KIND_BLOCKY
+                          else CrossedStyle(x) if kind == KIND_CROSSED else None)
+        return cls(BlockTextureIds(*fallback), styles)
+
+
+@dataclass
+class ChunkMesh:
+    """lib.rs:226-229: two vertex vectors (structured numpy arrays of VERTEX_DTYPE)."""
+    intransparent: np.ndarray
+    transparent: np.ndarray
+
+
+@dataclass
+class BatchMesh:
+    """Packed result of a batch: chunk i owns intransparent[ranges_i[i].first_vertex :][: vertex_count]."""
+    intransparent: np.ndarray
+    transparent: np.ndarray
+    ranges_i: np.ndarray
+    ranges_t: np.ndarray
+
+    def chunk(self, i: int) -> ChunkMesh:
+        a, b = self.ranges_i[i], self.ranges_t[i]
+        return ChunkMesh(self.intransparent[int(a["first_vertex"]):int(a["first_vertex"]) + int(a["vertex_count"])],
+                         self.transparent[int(b["first_vertex"]):int(b["first_vertex"]) + int(b["vertex_count"])])
+
+
+class _BatchOut(C.Structure):
+    _fields_ = [("d_intransparent", C.c_void_p), ("d_transparent", C.c_void_p), ("d_ranges_i", C.c_void_p),
+                ("d_ranges_t", C.c_void_p), ("n_intransparent", C.c_uint64), ("n_transparent", C.c_uint64),
+                ("n_chunks", C.c_uint32), ("launches", C.c_uint32), ("kernel_ms", C.c_float),
+                ("reserved", C.c_uint32)]
+
+
+class _HostMesh(C.Structure):
+    _fields_ = [("intransparent", C.c_void_p), ("transparent", C.c_void_p), ("ranges_i", C.c_void_p),
+                ("ranges_t", C.c_void_p), ("n_intransparent", C.c_uint64), ("n_transparent", C.c_uint64),
+                ("n_chunks", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+def _copy_from(ptr: Optional[int], count: int, dtype: np.dtype) -> np.ndarray:
+    if not count:
+        return np.zeros(0, dtype=dtype)
+    buf = (C.c_uint8 * (count * dtype.itemsize)).from_address(ptr)
+    return np.frombuffer(buf, dtype=dtype).copy()
+
+
+class Mesher:
+    """One mm_ctx: the state the reference's meshgen thread owns (mimas-client/client.rs:258-267)."""
+
+    def __init__(self, device: int = 0, cache: Optional[TextureIdCache] = None):
+        self._lib = lib()
+        self._ctx = C.c_void_p()
+        rc = self._lib.mm_ctx_create(device, C.byref(self._ctx))
+        if rc != 0:
+            self._ctx = C.c_void_p()
+            raise MMError(rc, "mm_ctx_create failed (no CUDA device? this package has no CPU fallback)")
+        self.device = device
+        self._cache = None
+        if cache is not None:
+            self.set_cache(cache)
+
+    def close(self):
+        if getattr(self, "_ctx", None) and self._ctx.value:
+            self._lib.mm_ctx_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _ck(self, rc: int):
+        check(rc, self._ctx)
+
+    # -- block table ---------------------------------------------------------------------
+    def set_cache(self, cache: TextureIdCache):
+        self.set_table(cache.to_table())
+        self._cache = cache
+
+    def set_table(self, table: np.ndarray):
+        table = np.ascontiguousarray(table, dtype=BLOCK_ENTRY_DTYPE)
+        if table.shape != (256,):
+            raise ValueError("block table needs 256 rows")
+        self._ck(self._lib.mm_set_block_table(self._ctx, table.ctypes.data))
+        self._cache = None
+
+    # -- crate API ------------------------------------------------------------------------
+    def mesh_for_chunk(self, offs, chunk, cache: Optional[TextureIdCache] = None) -> ChunkMesh:
+        """mesh_for_chunk(offs :Vector3<isize>, chunk :&MapChunkData, cache :&TextureIdCache), lib.rs:231."""
+        if cache is not None and cache is not self._cache:
+            self.set_cache(cache)
+        offs = np.ascontiguousarray(offs, dtype=np.int64).reshape(3)
+        chunk = np.ascontiguousarray(chunk, dtype=np.uint8).reshape(4096)
+        pi, pt = C.c_void_p(), C.c_void_p()
+        ni, nt = C.c_uint64(), C.c_uint64()
+        self._ck(self._lib.mm_mesh_for_chunk(self._ctx, offs.ctypes.data, chunk.ctypes.data,
+                                             C.byref(pi), C.byref(ni), C.byref(pt), C.byref(nt)))
+        return ChunkMesh(_copy_from(pi.value, ni.value, VERTEX_DTYPE), _copy_from(pt.value, nt.value, VERTEX_DTYPE))
+
+    def mesh_batch(self, offs, chunks) -> BatchMesh:
+        """Host in, host out: n chunks meshed in one call (batch form of mesh_for_chunk)."""
+        chunks = np.ascontiguousarray(chunks, dtype=np.uint8).reshape(-1, 4096)
+        n = chunks.shape[0]
+        offs = np.ascontiguousarray(offs, dtype=np.int64).reshape(n, 3)
+        hm = _HostMesh()
+        self._ck(self._lib.mm_mesh_batch_host(self._ctx, chunks.ctypes.data, offs.ctypes.data, n, C.byref(hm)))
+        return BatchMesh(_copy_from(hm.intransparent, hm.n_intransparent, VERTEX_DTYPE),
+                         _copy_from(hm.transparent, hm.n_transparent, VERTEX_DTYPE),
+                         _copy_from(hm.ranges_i, n, RANGE_DTYPE), _copy_from(hm.ranges_t, n, RANGE_DTYPE))
+
+    def push_block(self, pos, block_ids: BlockTextureIds, siz: float, blocked) -> np.ndarray:
+        """push_block(r, [x,y,z], block_ids, siz, blocked), lib.rs:184: returns the vertices that would
+        be appended to `r`.  `blocked` is the closure: called with [dx,dy,dz] in source order."""
+        order = ([0, 0, -1], [0, -1, 0], [-1, 0, 0], [0, 0, 1], [0, 1, 0], [1, 0, 0])
+        mask = 0
+        for i, o in enumerate(order):
+            if blocked(o):
+                mask |= 1 << i
+        cube = np.zeros(1, dtype=CUBE_DTYPE)
+        cube[0] = (tuple(np.float32(v) for v in pos), np.float32(siz), block_ids.id_sides, block_ids.id_top,
+                   block_ids.id_bottom, mask)
+        return self.push_blocks(cube)
+
+    def push_blocks(self, cubes: np.ndarray) -> np.ndarray:
+        cubes = np.ascontiguousarray(cubes, dtype=CUBE_DTYPE)
+        out = np.zeros(36 * len(cubes), dtype=VERTEX_DTYPE)
+        n_out = C.c_uint64()
+        self._ck(self._lib.mm_push_blocks(self._ctx, cubes.ctypes.data, len(cubes), out.ctypes.data, C.byref(n_out)))
+        return out[:n_out.value].copy()
+
+    # -- device-resident batch path (benchmarks, server-side batch submission) ---------------
+    def set_stream(self, cuda_stream: int):
+        self._ck(self._lib.mm_ctx_set_stream(self._ctx, C.c_void_p(cuda_stream)))
+
+    def reserve(self, max_chunks: int, intransparent_vertices: int, transparent_vertices: int):
+        self._ck(self._lib.mm_reserve(self._ctx, max_chunks, intransparent_vertices, transparent_vertices))
+
+    def mesh_batch_device(self, d_chunks: int, d_offs: int, n: int) -> _BatchOut:
+        """Synchronous mesh of device-resident inputs (raw device pointers)."""
+        out = _BatchOut()
+        self._ck(self._lib.mm_mesh_batch(self._ctx, C.c_void_p(d_chunks), C.c_void_p(d_offs), None, n, C.byref(out)))
+        return out
+
+    def mesh_batch_async(self, d_chunks: int, d_offs: int, n: int):
+        self._ck(self._lib.mm_mesh_batch_async(self._ctx, C.c_void_p(d_chunks), C.c_void_p(d_offs), n))
+
+    def batch_finish(self) -> _BatchOut:
+        out = _BatchOut()
+        self._ck(self._lib.mm_batch_finish(self._ctx, C.byref(out)))
+        return out
+
+    def copy_out(self, out: _BatchOut) -> BatchMesh:
+        vi = np.zeros(out.n_intransparent, dtype=VERTEX_DTYPE)
+        vt = np.zeros(out.n_transparent, dtype=VERTEX_DTYPE)
+        ri = np.zeros(out.n_chunks, dtype=RANGE_DTYPE)
+        rt = np.zeros(out.n_chunks, dtype=RANGE_DTYPE)
+        self._ck(self._lib.mm_copy_out(self._ctx, vi.ctypes.data, vt.ctypes.data, ri.ctypes.data, rt.ctypes.data))
+        return BatchMesh(vi, vt, ri, rt)
+
+    def gen_terrain_device(self, seed: int, c0, dims, d_chunks: int, d_offs: int):
+        self._ck(self._lib.mm_gen_terrain_device(self._ctx, seed, c0[0], c0[1], c0[2], dims[0], dims[1], dims[2],
+                                                 C.c_void_p(d_chunks), C.c_void_p(d_offs)))
+
+    def dev_alloc(self, nbytes: int) -> int:
+        p = C.c_void_p()
+        self._ck(self._lib.mm_dev_alloc(self._ctx, nbytes, C.byref(p)))
+        return p.value
+
+    def dev_free(self, ptr: int):
+        self._ck(self._lib.mm_dev_free(self._ctx, C.c_void_p(ptr)))
+
+    def upload(self, d_ptr: int, arr: np.ndarray):
+        arr = np.ascontiguousarray(arr)
+        self._ck(self._lib.mm_dev_upload(self._ctx, C.c_void_p(d_ptr), arr.ctypes.data, arr.nbytes))
+
+    def download(self, d_ptr: int, nbytes: int) -> np.ndarray:
+        out = np.zeros(nbytes, dtype=np.uint8)
+        self._ck(self._lib.mm_dev_download(self._ctx, out.ctypes.data, C.c_void_p(d_ptr), nbytes))
+        return out
+
+    def host_alloc(self, nbytes: int) -> np.ndarray:
+        """Page-locked host buffer as a uint8 array (free with host_free(arr))."""
+        p = C.c_void_p()
+        self._ck(self._lib.mm_host_alloc(self._ctx, nbytes, C.byref(p)))
+        return np.frombuffer((C.c_uint8 * max(nbytes, 1)).from_address(p.value), dtype=np.uint8)[:nbytes]
+
+    def host_free(self, arr: np.ndarray):
+        self._ck(self._lib.mm_host_free(self._ctx, C.c_void_p(arr.ctypes.data)))
+
+    def mesh_batch_host_raw(self, chunks_ptr: int, offs_ptr: int, n: int) -> _HostMesh:
+        """mm_mesh_batch_host on raw host pointers; the result points into library-owned pinned memory."""
+        hm = _HostMesh()
+        self._ck(self._lib.mm_mesh_batch_host(self._ctx, C.c_void_p(chunks_ptr), C.c_void_p(offs_ptr), n, C.byref(hm)))
+        return hm
+
+    def launch_count(self) -> int:
+        v = C.c_uint64()
+        self._ck(self._lib.mm_launch_count(self._ctx, C.byref(v)))
+        return v.value
+
+    def sync(self):
+        self._ck(self._lib.mm_ctx_sync(self._ctx))
+
+    def device_info(self) -> Tuple[int, int, int]:
+        a, b, c = C.c_int(), C.c_int(), C.c_int()
+        self._ck(self._lib.mm_device_info(self._ctx, C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
+
+
+def default_cache() -> TextureIdCache:
+    """Block table of the default game (mimas-server/game-params.toml), shipped as data/default_block_table.json
+    (derived by data/make_default_table.py) so that no reference checkout is needed at run time."""
+    import json
+    import os
+    t = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "default_block_table.json")))
+    return TextureIdCache.from_table_rows([tuple(r) for r in t["entries"]], tuple(t["fallback"]))
+
+
+_default: Optional[Mesher] = None
+
+
+def mesh_for_chunk(offs, chunk, cache: TextureIdCache) -> ChunkMesh:
+    """Module-level drop-in with the crate's signature (lib.rs:231-232); uses one process-wide
+    Mesher on device 0, like the single meshgen thread of the reference client."""
+    global _default
+    if _default is None:
+        _default = Mesher(0)
+    return _default.mesh_for_chunk(offs, chunk, cache)
+
+
+def gen_terrain_host(seed: int, c0, dims) -> Tuple[np.ndarray, np.ndarray]:
+    """Synthetic mapgen look-alike on the host (same bytes as the device generator)."""
+    n = int(dims[0]) * int(dims[1]) * int(dims[2])
+    chunks = np.zeros((n, 4096), dtype=np.uint8)
+    offs = np.zeros((n, 3), dtype=np.int64)
+    check(lib().mm_gen_terrain_host(seed, c0[0], c0[1], c0[2], dims[0], dims[1], dims[2],
+                                    chunks.ctypes.data, offs.ctypes.data), None)
+    return chunks, offs

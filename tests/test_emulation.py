@@ -1,0 +1,108 @@
+"""CPU check of the kernel's per-thread phase functions (mimas_b200/csrc/mesh_core.cuh), compiled
+with g++ by tests/emul/ and run as a serial emulation of one CTA, against the oracle.  This pins the
+bit-level logic the CUDA kernel is built from without needing a GPU; the GPU tests then cover the
+real kernel (scan, look-back, bulk stores)."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import oracle
+from tests.util import checkerboard_chunks, first_diff, load_golden, oracle_cache
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+G = load_golden()
+
+
+def kernel_table(rows, fallback):
+    """rows (kind, sides, top, bottom, crossed) -> the packed 2 x u32 entries of mesh_core.cuh TabEntry,
+    ids beyond the known ones = blocky fallback (what mm_table_from_cache + mm_set_block_table build)."""
+    tab = np.zeros((256, 2), dtype=np.uint32)
+    for i in range(256):
+        kind, s, t, b, x = rows[i] if i < len(rows) else (1, fallback[0], fallback[1], fallback[2], 0)
+        if kind == 2:
+            tab[i, 0] = x
+        elif kind == 1:
+            tab[i, 0] = s | (t << 16)
+        tab[i, 1] = (b | (kind << 16)) if kind else 0
+    return tab
+
+
+@pytest.fixture(scope="module")
+def emul():
+    subprocess.run(["make", "-C", os.path.join(HERE, "emul"), "-s"], check=True)
+    lib = C.CDLL(os.path.join(HERE, "emul", "libemul_mesher.so"))
+
+    def run(chunks, offs, tab, cap_quads=None):
+        chunks = np.ascontiguousarray(chunks, dtype=np.uint8).reshape(-1, 4096)
+        n = len(chunks)
+        offs = np.ascontiguousarray(offs, dtype=np.int64).reshape(n, 3)
+        cap = cap_quads if cap_quads is not None else 20480 * n
+        bufs = [np.zeros(cap * 216 + 48, dtype=np.uint8) for _ in range(2)]
+        ptrs = [b.ctypes.data + (-b.ctypes.data) % 16 for b in bufs]
+        ri = np.zeros((n, 2), dtype=np.uint64)
+        rt = np.zeros((n, 2), dtype=np.uint64)
+        tot = np.zeros(2, dtype=np.uint64)
+        lib.emul_mesh_batch(C.c_void_p(chunks.ctypes.data), C.c_void_p(offs.ctypes.data), C.c_uint32(n),
+                            C.c_void_p(tab.ctypes.data), C.c_void_p(ptrs[0]), C.c_uint64(cap), C.c_void_p(ptrs[1]),
+                            C.c_uint64(cap), C.c_void_p(ri.ctypes.data), C.c_void_p(rt.ctypes.data),
+                            C.c_void_p(tot.ctypes.data))
+        outs = []
+        for b, p, t in zip(bufs, ptrs, tot):
+            o = p - b.ctypes.data
+            outs.append(b[o:o + int(t) * 216].tobytes())
+        return outs[0], outs[1], ri, rt
+    return run
+
+
+TAB = kernel_table(G.entries, G.fallback)
+
+
+@pytest.mark.parametrize("name", G.names)
+def test_emulated_kernel_matches_kat(name, emul):
+    c = G.cases[name]
+    i, t, _, _ = emul(c["chunk"], c["offs"], TAB)
+    assert first_diff(i, c["intr"]) is None
+    assert first_diff(t, c["trans"]) is None
+
+
+def test_emulated_batch_packing_and_ranges(emul):
+    chunks = np.stack([G.cases[n]["chunk"] for n in G.names])
+    offs = np.stack([G.cases[n]["offs"] for n in G.names])
+    i, t, ri, rt = emul(chunks, offs, TAB)
+    assert i == b"".join(G.cases[n]["intr"] for n in G.names)
+    assert t == b"".join(G.cases[n]["trans"] for n in G.names)
+    want = oracle.mesh_batch(chunks, offs, oracle_cache(G))
+    assert list(ri[:, 0]) == list(want["first_i"]) and list(rt[:, 0]) == list(want["first_t"])
+    assert list(ri[:, 1] & 0xFFFFFFFF) == list(want["count_i"])
+
+
+def test_emulated_random_and_terrain(emul):
+    import mimas_b200
+    oc = oracle_cache(G)
+    rng = np.random.RandomState(5)
+    chunks = rng.randint(0, 256, size=(12, 4096)).astype(np.uint8)
+    offs = rng.randint(-2 ** 40, 2 ** 40, size=(12, 3)).astype(np.int64)
+    tc, to = mimas_b200.gen_terrain_host(78, (-3, -3, -2), (6, 6, 4))
+    cc, co = checkerboard_chunks(3)
+    chunks = np.concatenate([chunks, tc, cc])
+    offs = np.concatenate([offs, to, co])
+    want = oracle.mesh_batch(chunks, offs, oc, threads=4)
+    i, t, _, _ = emul(chunks, offs, TAB)
+    assert first_diff(i, want["intransparent"].tobytes()) is None
+    assert first_diff(t, want["transparent"].tobytes()) is None
+
+
+def test_emulated_shared_textures(emul):
+    rows = [(0, 0, 0, 0, 0), (1, 7, 8, 9, 0), (1, 7, 8, 10, 0), (1, 11, 8, 9, 0), (1, 7, 12, 9, 0), (2, 0, 0, 0, 5)]
+    fb = (7, 8, 9)
+    rng = np.random.RandomState(3)
+    chunks = np.array([0, 1, 2, 3, 4, 5, 77], dtype=np.uint8)[rng.randint(0, 7, size=(8, 4096))]
+    chunks[4:] = np.array([1, 2, 3, 4, 77], dtype=np.uint8)[rng.randint(0, 5, size=(4, 4096))]
+    offs = (rng.randint(-50, 50, size=(8, 3)) * 16).astype(np.int64)
+    want = oracle.mesh_batch(chunks, offs, oracle.cache_from_entries(rows, len(rows), fb))
+    i, t, _, _ = emul(chunks, offs, kernel_table(rows, fb))
+    assert first_diff(i, want["intransparent"].tobytes()) is None
+    assert first_diff(t, want["transparent"].tobytes()) is None

@@ -1,0 +1,176 @@
+"""GPU parity tests: the CUDA mesher, called through the C ABI (ctypes -> libmimas_meshgen_cuda.so),
+must be BIT-EXACT with the CPU oracle (oracle/meshgen_oracle.c, a restatement of
+mimas-meshgen/lib.rs:231-446) -- integer / byte work, tolerance zero.  Run with -m gpu on a B200."""
+import numpy as np
+import pytest
+
+import oracle
+from tests.util import (assert_batch_equal, checkerboard_chunks, first_diff, load_golden, oracle_cache,
+                        product_cache)
+
+pytestmark = pytest.mark.gpu
+
+G = load_golden()
+
+
+@pytest.fixture(scope="module")
+def mesher():
+    import mimas_b200
+    m = mimas_b200.Mesher(0, product_cache(G))
+    yield m
+    m.close()
+
+
+@pytest.fixture(scope="module")
+def ocache():
+    return oracle_cache(G)
+
+
+@pytest.mark.parametrize("name", G.names)
+def test_known_answer_vectors_single_chunk(name, mesher):
+    """mesh_for_chunk (lib.rs:231-232) on every committed known-answer vector."""
+    c = G.cases[name]
+    m = mesher.mesh_for_chunk(c["offs"], c["chunk"])
+    assert first_diff(m.intransparent.tobytes(), c["intr"]) is None
+    assert first_diff(m.transparent.tobytes(), c["trans"]) is None
+
+
+def test_known_answer_vectors_as_one_batch(mesher):
+    """Streams are packed in chunk order: one memcmp against the concatenated vectors."""
+    chunks = np.stack([G.cases[n]["chunk"] for n in G.names])
+    offs = np.stack([G.cases[n]["offs"] for n in G.names])
+    b = mesher.mesh_batch(offs, chunks)
+    assert b.intransparent.tobytes() == b"".join(G.cases[n]["intr"] for n in G.names)
+    assert b.transparent.tobytes() == b"".join(G.cases[n]["trans"] for n in G.names)
+    for i, n in enumerate(G.names):
+        assert b.chunk(i).intransparent.tobytes() == G.cases[n]["intr"]
+        assert b.chunk(i).transparent.tobytes() == G.cases[n]["trans"]
+
+
+def test_empty_batch(mesher):
+    b = mesher.mesh_batch(np.zeros((0, 3), np.int64), np.zeros((0, 4096), np.uint8))
+    assert len(b.intransparent) == 0 and len(b.transparent) == 0 and len(b.ranges_i) == 0
+
+
+@pytest.mark.parametrize("dims,c0", [((8, 8, 4), (-4, -4, -2)), ((5, 3, 2), (100, -77, -1)), ((1, 1, 1), (3, 2, 1))])
+def test_terrain_regions_match_oracle(dims, c0, mesher, ocache):
+    import mimas_b200
+    chunks, offs = mimas_b200.gen_terrain_host(78, c0, dims)
+    assert_batch_equal(mesher.mesh_batch(offs, chunks), oracle.mesh_batch(chunks, offs, ocache, threads=8))
+
+
+def test_random_ids_and_extreme_offsets(mesher, ocache):
+    """All 256 ids (unknown ids -> fallback, lib.rs:105-109), crossed plants everywhere, and origins far
+    beyond 2^24 where `as f32` and `v - last_v` round (lib.rs:249,256)."""
+    rng = np.random.RandomState(7)
+    chunks = rng.randint(0, 256, size=(48, 4096)).astype(np.uint8)
+    offs = rng.randint(-2 ** 40, 2 ** 40, size=(48, 3)).astype(np.int64)
+    offs[0] = (2 ** 62, -2 ** 62, 2 ** 24 - 8)
+    offs[1] = (-2 ** 24 - 8, 2 ** 24 - 8, -16)
+    assert_batch_equal(mesher.mesh_batch(offs, chunks), oracle.mesh_batch(chunks, offs, ocache, threads=8))
+
+
+def test_sparse_random_chunks(mesher, ocache):
+    rng = np.random.RandomState(11)
+    ids = np.array([0, 0, 0, 0, 5, 5, 3, 11, 2, 1, 9, 42, 51, 7, 6, 200], dtype=np.uint8)
+    chunks = ids[rng.randint(0, len(ids), size=(64, 4096))]
+    # long runs too: smear along y and x
+    chunks[32:] = np.repeat(chunks[32:].reshape(32, 16, 4, 4, 16)[:, :, :, :1, :], 4, axis=3).reshape(32, 4096)
+    offs = (rng.randint(-1000, 1000, size=(64, 3)) * 16).astype(np.int64)
+    assert_batch_equal(mesher.mesh_batch(offs, chunks), oracle.mesh_batch(chunks, offs, ocache, threads=8))
+
+
+def test_checkerboard_worst_case_batch(mesher, ocache):
+    """cfg3 shape: 12288 quads per chunk -> 12 descriptor rounds and 96 staging tiles per chunk."""
+    chunks, offs = checkerboard_chunks(24)
+    b = mesher.mesh_batch(offs, chunks)
+    assert list(b.ranges_i["vertex_count"]) == [73728] * 24
+    assert_batch_equal(b, oracle.mesh_batch(chunks, offs, ocache, threads=8))
+
+
+def test_max_vertex_chunks(mesher, ocache):
+    """Absolute maxima: all-crossed chunk (4096 plants = 98304 transparent vertices) and
+    the solid/crossed checkerboard (122880 vertices)."""
+    a = np.full(4096, 42, dtype=np.uint8)
+    b, _ = checkerboard_chunks(1, solid=5, other=48)
+    chunks = np.stack([a, b[0], a])
+    offs = np.array([[0, 0, 0], [16, 0, 0], [-16, -16, -16]], dtype=np.int64)
+    got = mesher.mesh_batch(offs, chunks)
+    assert list(got.ranges_t["vertex_count"]) == [98304, 2048 * 24, 98304]
+    assert int(got.ranges_i["vertex_count"][1]) + int(got.ranges_t["vertex_count"][1]) == 122880
+    assert_batch_equal(got, oracle.mesh_batch(chunks, offs, ocache, threads=8))
+
+
+def test_shared_textures_merge_across_block_ids(ocache):
+    """Runs merge on equal *texture ids*, not block ids (Walker compares TextureId, lib.rs:253-258):
+    a table where different blocks share some face textures but not others."""
+    import mimas_b200
+    rows = [(0, 0, 0, 0, 0), (1, 7, 8, 9, 0), (1, 7, 8, 10, 0), (1, 11, 8, 9, 0), (1, 7, 12, 9, 0), (2, 0, 0, 0, 5)]
+    fb = (7, 8, 9)  # unknown ids share everything with id 1
+    tic = mimas_b200.TextureIdCache.from_table_rows(rows, fb)
+    oc = oracle.cache_from_entries(rows, len(rows), fb)
+    rng = np.random.RandomState(3)
+    chunks = np.array([0, 1, 2, 3, 4, 5, 77], dtype=np.uint8)[rng.randint(0, 7, size=(16, 4096))]
+    chunks[8:] = np.array([1, 2, 3, 4, 77], dtype=np.uint8)[rng.randint(0, 5, size=(8, 4096))]
+    offs = (rng.randint(-50, 50, size=(16, 3)) * 16).astype(np.int64)
+    with mimas_b200.Mesher(0, tic) as m:
+        assert_batch_equal(m.mesh_batch(offs, chunks), oracle.mesh_batch(chunks, offs, oc, threads=4))
+
+
+def test_repeated_launches_with_changing_batch_sizes(mesher, ocache):
+    """Exercises arena growth + re-run and the double-buffered look-back status words."""
+    import mimas_b200
+    with mimas_b200.Mesher(0, product_cache(G)) as m:
+        for dims in [(2, 2, 1), (6, 6, 2), (1, 1, 1), (7, 5, 3), (3, 3, 3), (7, 5, 3), (2, 1, 1)]:
+            chunks, offs = mimas_b200.gen_terrain_host(5, (-3, -2, -1), dims)
+            assert_batch_equal(m.mesh_batch(offs, chunks), oracle.mesh_batch(chunks, offs, ocache, threads=8))
+
+
+def test_device_resident_path_and_device_terrain_generator(mesher, ocache):
+    import mimas_b200
+    dims, c0 = (16, 8, 4), (-8, -4, -2)
+    n = dims[0] * dims[1] * dims[2]
+    chunks, offs = mimas_b200.gen_terrain_host(78, c0, dims)
+    d_c, d_o = mesher.dev_alloc(n * 4096), mesher.dev_alloc(n * 24)
+    try:
+        mesher.gen_terrain_device(78, c0, dims, d_c, d_o)
+        mesher.sync()
+        assert mesher.download(d_c, n * 4096).tobytes() == chunks.tobytes()
+        assert mesher.download(d_o, n * 24).tobytes() == offs.tobytes()
+        want = oracle.mesh_batch(chunks, offs, ocache, threads=8)
+        for _ in range(3):  # back-to-back async launches, last one read back
+            mesher.mesh_batch_async(d_c, d_o, n)
+        out = mesher.batch_finish()
+        assert out.n_chunks == n and out.kernel_ms > 0
+        assert_batch_equal(mesher.copy_out(out), want)
+    finally:
+        mesher.dev_free(d_c)
+        mesher.dev_free(d_o)
+
+
+def test_full_size_terrain_batch_4096(mesher, ocache):
+    """BASELINE.json configs[1] at full size: 4096 terrain chunks, every byte compared."""
+    import mimas_b200
+    chunks, offs = mimas_b200.gen_terrain_host(78, (-16, -16, -2), (32, 32, 4))
+    assert_batch_equal(mesher.mesh_batch(offs, chunks), oracle.mesh_batch(chunks, offs, ocache, threads=8))
+
+
+def test_push_block_matches_oracle(mesher):
+    """push_block (lib.rs:183-219) for every blocked-face combination."""
+    from mimas_b200.meshgen import BlockTextureIds
+    for mask in range(64):
+        order = ([0, 0, -1], [0, -1, 0], [-1, 0, 0], [0, 0, 1], [0, 1, 0], [1, 0, 0])
+        blocked = lambda o, mask=mask: bool(mask >> order.index(list(o)) & 1)
+        got = mesher.push_block((1.5, -2.25, 1e7), BlockTextureIds(3, 4, 5), 0.5, blocked)
+        want = oracle.push_block((1.5, -2.25, 1e7), (3, 4, 5), 0.5, mask)
+        assert first_diff(got.tobytes(), want.tobytes()) is None
+
+
+def test_halo_is_rejected(mesher):
+    """The reference has no halo (lib.rs:277-280); a non-NULL halo is not silently ignored."""
+    import ctypes as C
+    from mimas_b200._lib import lib
+    chunk = np.zeros(4096, np.uint8)
+    offs = np.zeros(3, np.int64)
+    rc = lib().mm_mesh_batch(mesher._ctx, chunk.ctypes.data, offs.ctypes.data, chunk.ctypes.data, 1, None)
+    assert rc == 7

@@ -51,3 +51,43 @@ def first_diff(a: bytes, b: bytes):
     sa = np.frombuffer(va[i].tobytes(), dtype=VERTEX_DTYPE)[0]
     sb = np.frombuffer(vb[i].tobytes(), dtype=VERTEX_DTYPE)[0]
     return f"{len(bad)} vertices differ; first at {i} (quad {i // 6}, corner {i % 6}): {sa} != {sb}"
+
+
+# ---- helpers shared by the CPU-emulation and GPU parity tests ---------------------------
+
+def oracle_cache(g=None):
+    import oracle
+    g = g or load_golden()
+    return oracle.cache_from_entries(g.entries, g.n_known, g.fallback)
+
+
+def product_cache(g=None):
+    from mimas_b200.meshgen import TextureIdCache
+    g = g or load_golden()
+    return TextureIdCache.from_table_rows(g.entries, g.fallback)
+
+
+def checkerboard_chunks(n, solid=5, other=0):
+    """(x+y+z+parity)&1 ? solid : other, parity alternating per chunk,
+    origins on a 32 x 32 x k grid of chunks."""
+    idx = np.arange(4096)
+    x, y, z = idx >> 8, (idx >> 4) & 15, idx & 15
+    base = (x + y + z) & 1
+    chunks = np.empty((n, 4096), dtype=np.uint8)
+    offs = np.empty((n, 3), dtype=np.int64)
+    for i in range(n):
+        chunks[i] = np.where((base ^ (i & 1)) == 1, solid, other)
+        offs[i] = (16 * (i % 32 - 16), 16 * ((i // 32) % 32 - 16), 16 * (i // 1024))
+    return chunks, offs
+
+
+def assert_batch_equal(got, want):
+    """got: mimas_b200.BatchMesh; want: dict from oracle.mesh_batch."""
+    assert list(got.ranges_i["vertex_count"]) == list(want["count_i"])
+    assert list(got.ranges_t["vertex_count"]) == list(want["count_t"])
+    assert list(got.ranges_i["first_vertex"]) == list(want["first_i"])
+    assert list(got.ranges_t["first_vertex"]) == list(want["first_t"])
+    d = first_diff(got.intransparent.tobytes(), want["intransparent"].tobytes())
+    assert d is None, "intransparent: " + d
+    d = first_diff(got.transparent.tobytes(), want["transparent"].tobytes())
+    assert d is None, "transparent: " + d
