@@ -1,20 +1,25 @@
-// mesh_core.cuh -- per-chunk data-path logic of the B200 chunk mesher.
+// mesh_core.cuh -- per-lane data-path logic of the B200 chunk mesher (kernel v2: one warp per chunk).
 //
-// Everything in this header is written per *logical thread* (tid) between
-// CTA-wide barriers, against an explicit shared-memory struct.  The CUDA kernel
-// (mesh_kernel.cuh) calls these functions with tid = threadIdx.x and real
-// barriers; tests/emul/ compiles the very same functions with g++ and runs the
-// logical threads in a loop, so the bit-level logic can be checked on a machine
-// without a GPU.  (That emulation is test infrastructure; the product library
-// never runs it.)
+// Everything in this header is written per *logical lane* against an explicit per-warp
+// shared-memory struct; data crosses lanes only through that struct (or through values the
+// caller hands in).  The CUDA kernel (mesh_kernel.cuh) calls these functions with
+// lane = threadIdx.x & 31, real shuffles and __syncwarp() between the phases; tests/emul/
+// compiles the very same functions with g++ and runs the 32 lanes in a loop, so the
+// bit-level logic can be checked on a machine without a GPU.  (That emulation is test
+// infrastructure; the product library never runs it.)
 //
 // What is computed: mimas-meshgen/lib.rs:231-446 `mesh_for_chunk`
 //   * six run-merging face passes (lib.rs:316-410) -> `intransparent`
 //   * crossed-plant pass (lib.rs:412-440)          -> `transparent`
-// re-formulated for a GPU as: per-row bit masks -> run-start masks -> CTA-wide
-// exclusive scan in emission order -> 32-bit quad descriptors -> one thread per
-// quad expands 216 bytes into a shared-memory staging tile that a bulk async
-// copy (TMA) stores to the packed vertex stream.
+// re-formulated for one warp as
+//   A. lane <-> column (x, y): 16 block ids along z (one 16-byte load) -> 16-bit "blocky"
+//      mask over z, plus SWAR id-equality masks against the (x, y-1) and (x-1, y) columns
+//   B. visibility and run-start masks of all six passes as bit operations on z-masks
+//   C. 16x16 bit-matrix transposes (in registers) turn the z-masks into masks over the
+//      merge axis, one 16-bit word per row (pass, c1, c2) in the reference's emission order
+//   D. popc + warp scan -> quad counts and offsets; chunk base from the batch-wide prefix
+//   E. lane <-> quad: find the quad's row and start bit, measure the run, expand 216 bytes
+//      into a staging tile that a bulk async copy (TMA) stores to the packed vertex stream.
 #pragma once
 #include <stdint.h>
 
@@ -37,15 +42,15 @@ struct Range {  // = mm_range (include/mimas_meshgen_cuda.h)
 	uint32_t reserved;
 };
 
-constexpr int kThreads = 128;          // logical threads per CTA
-constexpr int kRows = 256;             // rows per pass: (c1, c2) in 16 x 16
+constexpr int kLanes = 32;
 constexpr int kPasses = 6;             // lib.rs:316-410
-constexpr int kTileQuads = 128;        // quads expanded per staging tile (one per thread)
+constexpr int kGroups = 96;            // (pass, c1) groups of 16 rows, in emission order
+constexpr int kTileQuads = 32;         // quads expanded per staging tile (one per lane)
 constexpr int kQuadBytes = 216;        // 6 vertices x 36 B
 constexpr int kQuadWords = 54;
-constexpr int kDescCap = 1024;         // descriptors held in shared memory per round
 constexpr int kPlantQuads = 4;         // 2 x rpush_face_bidi! = 24 vertices = 4 quad slots
-constexpr int kStageBytes = kTileQuads * kQuadBytes;  // 27648, a multiple of 16
+constexpr int kStageBytes = kTileQuads * kQuadBytes;  // 6912, a multiple of 16
+constexpr int kBzStride = 18;          // Bzp is a 18 x 18 array: the 16 x 16 columns plus a zero border
 
 // Block-table entry as the kernel sees it (built from mm_block_entry on the host):
 //   x = id_sides | id_top << 16   (for a crossed block: x = crossed texture id)
@@ -53,31 +58,39 @@ constexpr int kStageBytes = kTileQuads * kQuadBytes;  // 27648, a multiple of 16
 struct TabEntry {
 	uint32_t x, y;
 };
+// Per-id flag byte derived from the table: bit 0 = blocky, bit 5 = crossed.  Summed over the
+// 16 cells of a column the low 5 bits count blocky cells and bits 5.. count crossed cells.
+constexpr uint32_t kFlagBlocky = 1u, kFlagCrossed = 32u;
 
-// Shared memory of one CTA.  Plain struct so that host emulation can allocate it.
-struct alignas(128) Smem {
-	// staging tile: +16 so the tile can be shifted by 8 B to match the 16-B phase of
-	// its destination in the vertex stream (quads are only 8-B aligned: 216 = 8 * 27)
-	alignas(128) unsigned char stage[kStageBytes + 16];
-	alignas(16) unsigned char raw[4096];       // the chunk, index x*256 + y*16 + z (map.rs:83-86)
-	alignas(16) TabEntry tab[256];             // block table
-	alignas(16) uint32_t desc[kDescCap];       // quad / plant descriptors of the current round
-	uint16_t S[kPasses][kRows];                // run-start mask per (pass, row), bit = inner coordinate
-	uint16_t T[kPasses][kRows];                // run-boundary mask: start | not visible
-	uint16_t pre[kPasses * kRows];             // counts, then exclusive prefix (emission order)
-	uint16_t By[kRows];                        // blocky mask over y for row (x, z)
-	uint16_t Bx[kRows];                        // blocky mask over x for row (y, z)
-	uint16_t Cz[kRows];                        // crossed mask over z for column (x, y)
-	uint16_t cpre[kRows];                      // plants: counts, then exclusive prefix (x, y order)
-	float pos[3][20];                          // (offs + c) as f32 for c in 0..16, per axis
-	uint32_t warp_sums[8];
-	uint32_t n_quads, n_plants;                // chunk totals
-	uint32_t any_crossed;
-	unsigned long long base_q, base_t;         // first quad slot of this chunk in each stream
-	unsigned long long ticket;
+// 16 block ids of one column (x, y), z = 0..15: byte z&3 of word z>>2 (map.rs:83-86).
+struct Col {
+	uint32_t w[4];
 };
 
-MM_HD int popc16(uint32_t v) {
+// Shared memory of one warp.  Plain struct so that host emulation can allocate it.
+struct alignas(16) WarpSmem {
+	// staging tile: +16 so the tile can be shifted by 8 B to match the 16-B phase of its
+	// destination in the vertex stream (quads are only 8-B aligned: 216 = 8 * 27).
+	// Before the expansion phase the same bytes hold the id-equality masks (Ey, Ex).
+	alignas(16) unsigned char stage[kStageBytes + 16];
+	// run-start masks.  Phase B writes them over z per column: passes 1,3,4,6 (p = 0,2,3,5) at
+	// [p][x*16 + y], passes 2,5 (p = 1,4) at [p][y*16 + x]; phase C transposes every 16-entry
+	// block in place into [p][c1*16 + c2] = mask over the merge axis of row (c1, c2).
+	// After the intransparent stream is written, S[0..] is reused for the plant prefix (cpre).
+	alignas(16) uint16_t S[kPasses * 256 + 16];
+	alignas(16) uint16_t By[256];              // blocky mask over y for row (x, z): [x*16 + z]
+	alignas(16) uint16_t Bx[256];              // blocky mask over x for row (y, z): [y*16 + z]
+	alignas(16) uint16_t Cz[256];              // crossed mask over z for column (x, y): [x*16 + y]
+	alignas(16) uint16_t gpre[128];            // exclusive quad prefix per group; [96..127] = 0xffff
+	uint16_t Bzp[kBzStride * kBzStride];       // blocky mask over z per column, zero border
+	float pos[3][17];                          // (offs + c) as f32 for c in 0..=16, per axis
+};
+
+MM_HD uint16_t *smem_Ey(WarpSmem &s) { return reinterpret_cast<uint16_t *>(s.stage); }
+MM_HD uint16_t *smem_Ex(WarpSmem &s) { return reinterpret_cast<uint16_t *>(s.stage) + 256; }
+MM_HD uint16_t *smem_cpre(WarpSmem &s) { return s.S; }  // 257 entries, [256] = 0xffff
+
+MM_HD int popc32(uint32_t v) {
 #if defined(__CUDA_ARCH__)
 	return __popc(v);
 #else
@@ -89,6 +102,23 @@ MM_HD int ffs32(uint32_t v) {  // 1-based, 0 if v == 0
 	return __ffs((int)v);
 #else
 	return __builtin_ffs((int)v);
+#endif
+}
+MM_HD uint32_t funnel_r1(uint32_t lo, uint32_t hi) {  // (hi:lo) >> 1, low word
+#if defined(__CUDA_ARCH__)
+	return __funnelshift_r(lo, hi, 1);
+#else
+	return (lo >> 1) | (hi << 31);
+#endif
+}
+MM_HD uint32_t byte_perm(uint32_t a, uint32_t b, uint32_t sel) {
+#if defined(__CUDA_ARCH__)
+	return __byte_perm(a, b, sel);
+#else
+	const u64 v = ((u64)b << 32) | a;
+	uint32_t r = 0;
+	for (int i = 0; i < 4; i++) r |= (uint32_t)((v >> (8 * ((sel >> (4 * i)) & 7))) & 0xff) << (8 * i);
+	return r;
 #endif
 }
 // IEEE binary32 add / sub, round to nearest even, never contracted into an FMA --
@@ -126,144 +156,228 @@ MM_HD uint32_t f2u(float f) {
 // mimas-meshgen/lib.rs:123-131 `zsig` (NOT signum: +-0 -> +0)
 MM_HD float zsig(float v) { return v > 0.0f ? 1.0f : (v < 0.0f ? -1.0f : 0.0f); }
 
-// ---- phase 1: world coordinates --------------------------------------------------
+// ---- warp set-up ---------------------------------------------------------------------
+// Once per warp: the zero border of Bzp (a neighbour outside the chunk never blocks,
+// lib.rs:277-280) and the sentinels of the group prefix.
+MM_HD void init_warp_smem(WarpSmem &s, int lane) {
+	for (int i = lane; i < kBzStride * kBzStride; i += kLanes) s.Bzp[i] = 0;
+	s.gpre[kGroups + lane] = 0xffffu;
+}
+
 // pos[a][c] = (offs[a] + c) as f32 for c in 0..=16: every `pos.x as f32` the reference
 // evaluates (lib.rs:323-325 etc.), including the sentinel cell 16 (lib.rs:309).
-MM_HD void phase_pos(Smem &s, int tid, const long long *offs3) {
-	if (tid < 51) {
-		int a = tid / 17, c = tid % 17;
+MM_HD void phase_pos(WarpSmem &s, int lane, const long long *offs3) {
+	for (int i = lane; i < 51; i += kLanes) {
+		const int a = i / 17, c = i % 17;
 		s.pos[a][c] = i64_to_f32(offs3[a] + (long long)c);
 	}
 }
 
-// ---- phase 2: per-row masks --------------------------------------------------------
-// Registers a logical thread carries from phase 2 to phase 3 for one row index r.
-struct RowRegs {
-	uint32_t Es_Et;  // low 16: sides-texture equality along y, high 16: top-texture
-	uint32_t Eb_Ex;  // low 16: bottom-texture equality along y, high 16: sides equality along x
-	uint32_t By_Bx;  // low 16: blocky over y (row (x,z)), high 16: blocky over x (row (y,z))
-};
-
-// Row r is (c1, c2) = (r >> 4, r & 15).  For the y-inner passes (1,3,4,6; lib.rs:318)
-// that is (x, z); for the x-inner passes (2,5; lib.rs:334) it is (y, z).
-// Bit i of an equality mask says: cell i and cell i-1 of the row have the same
-// texture id for that face (bit 0 is never used).
-MM_HD RowRegs phase_rows(Smem &s, int r, uint32_t &any_crossed) {
-	const int c1 = r >> 4, c2 = r & 15;
-	RowRegs o;
-	uint32_t By = 0, Es = 0, Et = 0, Eb = 0, cr = 0;
-	TabEntry prev = {0xffffffffu, 0xffffffffu};
+// ---- phase A: one column (x, y) ------------------------------------------------------
+// Blocky mask over z (bit z <=> cell (x, y, z) is drawn as a cube, i.e. get_bl_tex_ids is
+// Some, lib.rs:105-109) in the return value; `sum` receives the flag sum of the column
+// (sum >> 5 = number of crossed cells).  flags = 256-entry byte table (see kFlagBlocky).
+MM_HD uint32_t col_flags(const uint8_t *flags, const Col &c, uint32_t &sum) {
+	uint32_t acc = 0, sm = 0;
 #pragma unroll
-	for (int y = 0; y < 16; y++) {  // row (x = c1, z = c2), cells along y
-		const TabEntry e = s.tab[s.raw[c1 * 256 + y * 16 + c2]];
-		const uint32_t kind = e.y >> 16;
-		By |= (kind == 1u ? 1u : 0u) << y;
-		cr |= (kind == 2u ? 1u : 0u);
-		Es |= (((e.x ^ prev.x) & 0xffffu) == 0u ? 1u : 0u) << y;
-		Et |= (((e.x ^ prev.x) >> 16) == 0u ? 1u : 0u) << y;
-		Eb |= (((e.y ^ prev.y) & 0xffffu) == 0u ? 1u : 0u) << y;
-		prev = e;
-	}
-	uint32_t Bx = 0, Ex = 0;
-	prev.x = 0xffffffffu;
+	for (int k = 0; k < 4; k++) {
 #pragma unroll
-	for (int x = 0; x < 16; x++) {  // row (y = c1, z = c2), cells along x
-		const TabEntry e = s.tab[s.raw[x * 256 + c1 * 16 + c2]];
-		Bx |= ((e.y >> 16) == 1u ? 1u : 0u) << x;
-		Ex |= (((e.x ^ prev.x) & 0xffffu) == 0u ? 1u : 0u) << x;
-		prev = e;
+		for (int b = 0; b < 4; b++) {
+			const uint32_t f = flags[(c.w[k] >> (8 * b)) & 0xffu];
+			acc = funnel_r1(acc, f);  // bit 0 of f enters at bit 31
+			sm += f;
+		}
 	}
-	s.By[r] = (uint16_t)By;
-	s.Bx[r] = (uint16_t)Bx;
-	any_crossed |= cr;
-	o.Es_Et = Es | (Et << 16);
-	o.Eb_Ex = Eb | (Ex << 16);
-	o.By_Bx = By | (Bx << 16);
-	return o;
+	sum = sm;
+	return acc >> 16;
 }
 
-// ---- phase 3: visibility, run starts, counts ---------------------------------------
-// lib.rs:273-293: a face is visible iff the cell is blocky and the neighbour in the
-// pass direction is outside the chunk or not blocky.  A run (lib.rs:244-271) starts
-// at cell i iff it is visible and (cell i-1 is not visible or has another texture).
-MM_HD void start_masks(Smem &s, int p, int r, uint32_t V, uint32_t E) {
-	const uint32_t S = V & ~((V << 1) & E);
-	const uint32_t T = (S | ~V) & 0xffffu;
-	s.S[p][r] = (uint16_t)S;
-	s.T[p][r] = (uint16_t)T;
-	s.pre[p * kRows + r] = (uint16_t)popc16(S);
+// Bit z set <=> the two columns hold the same block id at z (equal ids => equal textures
+// for every face; different ids are settled exactly by fix_equal()).
+MM_HD uint32_t eq_mask16(const Col &a, const Col &b) {
+	uint32_t m = 0;
+#pragma unroll
+	for (int k = 0; k < 4; k++) {
+		const uint32_t v = a.w[k] ^ b.w[k];
+		const uint32_t t = ((v & 0x7f7f7f7fu) + 0x7f7f7f7fu) | v;  // bit 7 of a byte: byte != 0
+		const uint32_t u = (~t & 0x80808080u) >> 7;                // bit 0 of a byte: ids equal
+		m |= (((u * 0x00204081u) >> 21) & 0xfu) << (4 * k);        // gather bits 0,8,16,24 -> 0..3
+	}
+	return m;
 }
 
-MM_HD void phase_vis(Smem &s, int r, const RowRegs &g) {
-	const int c1 = r >> 4, c2 = r & 15;
-	const uint32_t By = g.By_Bx & 0xffffu, Bx = g.By_Bx >> 16;
-	// y-inner rows: (x, z) = (c1, c2)
-	const uint32_t Bzm = c2 > 0 ? s.By[r - 1] : 0u;    // (x, *, z-1)
-	const uint32_t Bzp = c2 < 15 ? s.By[r + 1] : 0u;   // (x, *, z+1)
-	const uint32_t Bxm = c1 > 0 ? s.By[r - 16] : 0u;   // (x-1, *, z)
-	const uint32_t Bxp = c1 < 15 ? s.By[r + 16] : 0u;  // (x+1, *, z)
-	start_masks(s, 0, r, By & ~Bzm, g.Eb_Ex & 0xffffu);  // pass 1, [0,0,-1], id_bottom (lib.rs:317-330)
-	start_masks(s, 2, r, By & ~Bxm, g.Es_Et & 0xffffu);  // pass 3, [-1,0,0], id_sides  (lib.rs:349-362)
-	start_masks(s, 3, r, By & ~Bzp, g.Es_Et >> 16);      // pass 4, [0,0,1],  id_top    (lib.rs:365-378)
-	start_masks(s, 5, r, By & ~Bxp, g.Es_Et & 0xffffu);  // pass 6, [1,0,0],  id_sides  (lib.rs:397-410)
-	// x-inner rows: (y, z) = (c1, c2)
-	const uint32_t Bym = c1 > 0 ? s.Bx[r - 16] : 0u;   // (*, y-1, z)
-	const uint32_t Byp = c1 < 15 ? s.Bx[r + 16] : 0u;  // (*, y+1, z)
-	start_masks(s, 1, r, Bx & ~Bym, g.Eb_Ex >> 16);      // pass 2, [0,-1,0], id_sides  (lib.rs:333-346)
-	start_masks(s, 4, r, Bx & ~Byp, g.Eb_Ex >> 16);      // pass 5, [0,1,0],  id_sides  (lib.rs:381-394)
-}
-
-// Crossed plants (lib.rs:414-425): column (x, y) = (col >> 4, col & 15), bit z.
-MM_HD void phase_crossed_cols(Smem &s, int col) {
-	uint32_t C = 0;
+// Crossed mask over z of one column (slow path, only for columns whose flag sum says so).
+MM_HD uint32_t col_crossed(const uint8_t *flags, const Col &c) {
+	uint32_t m = 0;
 #pragma unroll
 	for (int z = 0; z < 16; z++)
-		C |= ((s.tab[s.raw[col * 16 + z]].y >> 16) == 2u ? 1u : 0u) << z;
-	s.Cz[col] = (uint16_t)C;
-	s.cpre[col] = (uint16_t)popc16(C);
+		m |= ((flags[(c.w[z >> 2] >> (8 * (z & 3))) & 0xffu] >> 5) & 1u) << z;
+	return m;
 }
 
-// ---- descriptors -------------------------------------------------------------------
-// quad:  pass(3) | row(8) << 3 | start(4) << 11 | (len-1)(4) << 15 | block id(8) << 19
-// plant: cell index(12) | block id(8) << 12
-MM_HD void phase_desc_row(Smem &s, int r, uint32_t w0) {
-	const int c1 = r >> 4, c2 = r & 15;
-#pragma unroll 1
-	for (int p = 0; p < kPasses; p++) {
-		uint32_t S = s.S[p][r];
-		if (S == 0u) continue;
-		uint32_t slot = s.pre[p * kRows + r];
-		if (slot >= w0 + (uint32_t)kDescCap || slot + (uint32_t)popc16(S) <= w0) continue;
-		const uint32_t T = s.T[p][r];
-		const bool xin = (p == 1 || p == 4);
-		while (S) {
-			const int st = ffs32(S) - 1;
-			S &= S - 1u;
-			if (slot >= w0 && slot < w0 + (uint32_t)kDescCap) {
-				const uint32_t m = T >> (st + 1);
-				const int len = m ? ffs32(m) : 16 - st;
-				const int cell = xin ? (st * 256 + c1 * 16 + c2) : (c1 * 256 + st * 16 + c2);
-				const uint32_t id = s.raw[cell];
-				s.desc[slot - w0] = (uint32_t)p | ((uint32_t)r << 3) | ((uint32_t)st << 11) |
-				                    ((uint32_t)(len - 1) << 15) | (id << 19);
+// ---- phase B: visibility and run starts of one column, all six passes -----------------
+// lib.rs:273-293: a face is visible iff the cell is blocky and the neighbour in the pass
+// direction is outside the chunk or not blocky.  A run (lib.rs:244-271) starts at a cell
+// iff its face is visible and the previous cell along the merge axis is not visible or
+// has another texture for that face.
+//
+// Exact texture comparison for the (rare) pairs of visible faces with different block ids.
+// `d` = z bits to settle, cells (x, y, z) vs (px, py, z); face: 0 sides, 1 top, 2 bottom.
+MM_HD uint32_t fix_equal(const TabEntry *tab, const uint8_t *chunk, uint32_t d, int x, int y, int px, int py,
+                         int face) {
+	uint32_t eq = 0;
+	while (d) {
+		const int z = ffs32(d) - 1;
+		d &= d - 1u;
+		const TabEntry a = tab[chunk[x * 256 + y * 16 + z]], b = tab[chunk[px * 256 + py * 16 + z]];
+		const uint32_t ta = face == 0 ? (a.x & 0xffffu) : face == 1 ? (a.x >> 16) : (a.y & 0xffffu);
+		const uint32_t tb = face == 0 ? (b.x & 0xffffu) : face == 1 ? (b.x >> 16) : (b.y & 0xffffu);
+		eq |= (ta == tb ? 1u : 0u) << z;
+	}
+	return eq;
+}
+
+MM_HD void col_starts(WarpSmem &s, const TabEntry *tab, const uint8_t *chunk, int x, int y) {
+	const uint16_t *B = s.Bzp + (x + 1) * kBzStride + (y + 1);
+	const uint32_t b = B[0];
+	const uint32_t bym = B[-1], byp = B[1], bxm = B[-kBzStride], bxp = B[kBzStride];
+	const uint32_t bmm = B[-kBzStride - 1], bpm = B[kBzStride - 1], bmp = B[-kBzStride + 1];
+	const int col = x * 16 + y;
+	const uint32_t ey = smem_Ey(s)[col], ex = smem_Ex(s)[col];
+	// own faces
+	const uint32_t V1 = b & ~(b << 1), V4 = b & ~(b >> 1);   // [0,0,-1] lib.rs:317, [0,0,1] lib.rs:365
+	const uint32_t V3 = b & ~bxm, V6 = b & ~bxp;             // [-1,0,0] lib.rs:349, [1,0,0] lib.rs:397
+	const uint32_t V2 = b & ~bym, V5 = b & ~byp;             // [0,-1,0] lib.rs:333, [0,1,0] lib.rs:381
+	// the same faces of the previous cell along the merge axis: (x, y-1) for the y-inner
+	// passes 1,3,4,6 and (x-1, y) for the x-inner passes 2,5 (zero border: no previous cell)
+	const uint32_t Q1 = V1 & bym & ~(bym << 1), Q4 = V4 & bym & ~(bym >> 1);
+	const uint32_t Q3 = V3 & bym & ~bmm, Q6 = V6 & bym & ~bpm;
+	const uint32_t Q2 = V2 & bxm & ~bmm, Q5 = V5 & bxm & ~bmp;
+	uint32_t e1 = ey, e3 = ey, e4 = ey, e6 = ey, e2 = ex, e5 = ex;
+	if (((Q1 | Q3 | Q4 | Q6) & ~ey) | ((Q2 | Q5) & ~ex)) {  // rare: visible neighbours with different ids
+		e1 |= fix_equal(tab, chunk, Q1 & ~ey, x, y, x, y - 1, 2);  // id_bottom, lib.rs:329
+		e3 |= fix_equal(tab, chunk, Q3 & ~ey, x, y, x, y - 1, 0);  // id_sides,  lib.rs:361
+		e4 |= fix_equal(tab, chunk, Q4 & ~ey, x, y, x, y - 1, 1);  // id_top,    lib.rs:377
+		e6 |= fix_equal(tab, chunk, Q6 & ~ey, x, y, x, y - 1, 0);  // id_sides,  lib.rs:409
+		e2 |= fix_equal(tab, chunk, Q2 & ~ex, x, y, x - 1, y, 0);  // id_sides,  lib.rs:345
+		e5 |= fix_equal(tab, chunk, Q5 & ~ex, x, y, x - 1, y, 0);  // id_sides,  lib.rs:393
+	}
+	const int row = y * 16 + x;
+	s.S[0 * 256 + col] = (uint16_t)(V1 & ~(Q1 & e1));
+	s.S[1 * 256 + row] = (uint16_t)(V2 & ~(Q2 & e2));
+	s.S[2 * 256 + col] = (uint16_t)(V3 & ~(Q3 & e3));
+	s.S[3 * 256 + col] = (uint16_t)(V4 & ~(Q4 & e4));
+	s.S[4 * 256 + row] = (uint16_t)(V5 & ~(Q5 & e5));
+	s.S[5 * 256 + col] = (uint16_t)(V6 & ~(Q6 & e6));
+}
+
+// ---- phase C: 16 x 16 bit-matrix transpose in registers --------------------------------
+// w[k] holds rows 2k (low half) and 2k+1 (high half); bit c of row r <-> bit r of row c.
+MM_HD void transpose16(uint32_t w[8]) {
+	// 8 x 8 blocks: byte 1 of rows 0..7 <-> byte 0 of rows 8..15
+#pragma unroll
+	for (int k = 0; k < 4; k++) {
+		const uint32_t a = w[k], b = w[k + 4];
+		w[k] = byte_perm(a, b, 0x6240);      // a.b0, b.b0, a.b2, b.b2
+		w[k + 4] = byte_perm(a, b, 0x7351);  // a.b1, b.b1, a.b3, b.b3
+	}
+	// 4 x 4 blocks: rows r and r+4
+#pragma unroll
+	for (int k = 0; k < 8; k++) {
+		if (k & 2) continue;
+		const uint32_t t = ((w[k] >> 4) ^ w[k + 2]) & 0x0f0f0f0fu;
+		w[k + 2] ^= t;
+		w[k] ^= t << 4;
+	}
+	// 2 x 2 blocks: rows r and r+2
+#pragma unroll
+	for (int k = 0; k < 8; k += 2) {
+		const uint32_t t = ((w[k] >> 2) ^ w[k + 1]) & 0x33333333u;
+		w[k + 1] ^= t;
+		w[k] ^= t << 2;
+	}
+	// 1 x 1: rows 2k and 2k+1 live in one word: bit 2j+1 <-> bit 16+2j
+#pragma unroll
+	for (int k = 0; k < 8; k++) {
+		const uint32_t t = ((w[k] >> 15) ^ w[k]) & 0x0000aaaau;
+		w[k] ^= t ^ (t << 15);
+	}
+}
+
+// Transposes the 16-entry block at S[m*16 ..] in place and returns the number of run
+// starts (= quads) in group m = pass*16 + c1.
+MM_HD uint32_t transpose_group(WarpSmem &s, int m) {
+	uint32_t *p = reinterpret_cast<uint32_t *>(s.S + m * 16);
+	uint32_t w[8];
+	uint32_t any = 0;
+#pragma unroll
+	for (int k = 0; k < 8; k++) {
+		w[k] = p[k];
+		any |= w[k];
+	}
+	if (any == 0) return 0;
+	transpose16(w);
+	uint32_t cnt = 0;
+#pragma unroll
+	for (int k = 0; k < 8; k++) {
+		p[k] = w[k];
+		cnt += (uint32_t)popc32(w[k]);
+	}
+	return cnt;
+}
+
+// Blocky masks over the merge axes, from the z-masks: job 0..15 -> By rows of x = job
+// (bits over y), job 16..31 -> Bx rows of y = job - 16 (bits over x).
+MM_HD void transpose_blocky(WarpSmem &s, int job) {
+	uint32_t w[8];
+	const bool over_y = job < 16;
+	const int f = job & 15;
+#pragma unroll
+	for (int k = 0; k < 8; k++) {
+		const int r0 = 2 * k, r1 = 2 * k + 1;
+		const uint32_t lo = over_y ? s.Bzp[(f + 1) * kBzStride + r0 + 1] : s.Bzp[(r0 + 1) * kBzStride + f + 1];
+		const uint32_t hi = over_y ? s.Bzp[(f + 1) * kBzStride + r1 + 1] : s.Bzp[(r1 + 1) * kBzStride + f + 1];
+		w[k] = lo | (hi << 16);
+	}
+	transpose16(w);
+	uint32_t *p = reinterpret_cast<uint32_t *>((over_y ? s.By : s.Bx) + f * 16);
+#pragma unroll
+	for (int k = 0; k < 8; k++) p[k] = w[k];
+}
+
+// ---- phase E: quad lookup ---------------------------------------------------------------
+// Quad q (0 <= q < nq, emission order) -> group m = pass*16 + c1, row c2, start bit st.
+// gpre[m] = number of quads before group m; gpre[96..127] = 0xffff.
+MM_HD void find_quad(const WarpSmem &s, uint32_t q, int &m, int &c2, int &st) {
+	int lo = 0;
+#pragma unroll
+	for (int step = 64; step >= 1; step >>= 1)
+		if ((uint32_t)s.gpre[lo + step] <= q) lo += step;  // largest m with gpre[m] <= q
+	m = lo;
+	const uint32_t r = q - s.gpre[lo];
+	const uint32_t *p = reinterpret_cast<const uint32_t *>(s.S + lo * 16);
+	uint32_t run = 0, base = 0, mask = 0;
+	int row = 0;
+	bool found = false;
+#pragma unroll
+	for (int k = 0; k < 8; k++) {
+		const uint32_t w = p[k];
+#pragma unroll
+		for (int h = 0; h < 2; h++) {
+			const uint32_t rm = h ? (w >> 16) : (w & 0xffffu);
+			const uint32_t nxt = run + (uint32_t)popc32(rm);
+			if (!found && r < nxt) {  // first row whose inclusive count exceeds r
+				found = true;
+				row = 2 * k + h;
+				base = run;
+				mask = rm;
 			}
-			slot++;
+			run = nxt;
 		}
 	}
-}
-
-MM_HD void phase_desc_col(Smem &s, int col, uint32_t w0) {
-	uint32_t C = s.Cz[col];
-	uint32_t slot = s.cpre[col];
-	while (C) {
-		const int z = ffs32(C) - 1;
-		C &= C - 1u;
-		if (slot >= w0 && slot < w0 + (uint32_t)kDescCap) {
-			const uint32_t cell = (uint32_t)col * 16u + (uint32_t)z;
-			s.desc[slot - w0] = cell | ((uint32_t)s.raw[cell] << 12);
-		}
-		slot++;
-	}
+	c2 = row;
+	for (uint32_t i = r - base; i > 0; i--) mask &= mask - 1u;  // drop the lower run starts
+	st = ffs32(mask) - 1;
 }
 
 // ---- quad expansion -----------------------------------------------------------------
@@ -321,14 +435,28 @@ MM_HD void write_quad(unsigned char *dst, const QuadArgs &a) {
 	}
 }
 
-// One quad of the six face passes from its descriptor (pass table: SURVEY.md §8a A5).
-MM_HD void expand_face_quad(const Smem &s, uint32_t d, unsigned char *dst) {
-	const int p = d & 7, r = (d >> 3) & 255, st = (d >> 11) & 15, len = ((d >> 15) & 15) + 1;
-	const TabEntry e = s.tab[(d >> 19) & 255];
-	const int c1 = r >> 4, c2 = r & 15;
+// One quad of the six face passes (pass table: SURVEY.md §8a A5) from its row and start
+// bit.  `chunk` = the 4096 block ids (global memory), `tab` = texture table.
+MM_HD void expand_face_quad(const WarpSmem &s, const TabEntry *tab, const uint8_t *chunk, int m, int c2, int st,
+                            unsigned char *dst) {
+	const int p = m >> 4, c1 = m & 15;
+	const bool xin = (p == 1 || p == 4);
+	// visibility over the merge axis of this row, to find where the run ends
+	const uint16_t *Bm = xin ? s.Bx : s.By;
+	const uint32_t b = Bm[c1 * 16 + c2];
+	uint32_t nb;
+	if (p == 0) nb = c2 > 0 ? Bm[c1 * 16 + c2 - 1] : 0u;          // [0,0,-1]
+	else if (p == 3) nb = c2 < 15 ? Bm[c1 * 16 + c2 + 1] : 0u;    // [0,0,1]
+	else if (p == 2 || p == 1) nb = c1 > 0 ? Bm[(c1 - 1) * 16 + c2] : 0u;   // [-1,0,0] / [0,-1,0]
+	else nb = c1 < 15 ? Bm[(c1 + 1) * 16 + c2] : 0u;              // [1,0,0] / [0,1,0]
+	const uint32_t T = ((uint32_t)s.S[m * 16 + c2] | ~(b & ~nb)) & 0xffffu;  // run boundary: start | not visible
+	const uint32_t above = T >> (st + 1);
+	const int len = above ? ffs32(above) : 16 - st;
+	const int cell = xin ? (st * 256 + c1 * 16 + c2) : (c1 * 256 + st * 16 + c2);
+	const TabEntry e = tab[chunk[cell]];
 	const float siz = 1.0f;  // lib.rs:314
 	QuadArgs a;
-	if (p == 1 || p == 4) {  // x-inner: row (y, z); run along x
+	if (xin) {  // x-inner: row (y, z); run along x
 		const float last_x = s.pos[0][st];
 		const float xlen = fsub(s.pos[0][st + len], last_x);  // vlen = v - last_v, lib.rs:249,256
 		const float y = s.pos[1][c1], z = s.pos[2][c2];
@@ -361,12 +489,25 @@ MM_HD void expand_face_quad(const Smem &s, uint32_t d, unsigned char *dst) {
 	write_quad(dst, a);
 }
 
+// ---- crossed plants (lib.rs:412-440) ----------------------------------------------------
+// Plant number pl (x outer, y, z inner = linear cell order) -> cell index.
+// cpre[col] = plants before column col = x*16 + y; cpre[256] = 0xffff.
+MM_HD int find_plant(WarpSmem &s, uint32_t pl) {
+	const uint16_t *cpre = smem_cpre(s);
+	int lo = 0;
+#pragma unroll
+	for (int step = 128; step >= 1; step >>= 1)
+		if ((uint32_t)cpre[lo + step] <= pl) lo += step;
+	uint32_t mask = s.Cz[lo];
+	for (uint32_t i = pl - cpre[lo]; i > 0; i--) mask &= mask - 1u;
+	return lo * 16 + ffs32(mask) - 1;
+}
+
 // Quad slot `part` (0..3) of a crossed plant: lib.rs:426-437.  Parts 0,1 are the
-// forward and reverse halves of the first rpush_face_bidi! (X-Z), parts 2,3 of the
-// second (Y-Z).
-MM_HD void expand_plant_quad(const Smem &s, uint32_t d, int part, unsigned char *dst) {
-	const int cell = d & 4095;
-	const TabEntry e = s.tab[(d >> 12) & 255];
+// forward and reverse halves of the first rpush_face_bidi!, parts 2,3 of the second.
+MM_HD void expand_plant_quad(const WarpSmem &s, const TabEntry *tab, const uint8_t *chunk, int cell, int part,
+                             unsigned char *dst) {
+	const TabEntry e = tab[chunk[cell]];
 	const int cx = cell >> 8, cy = (cell >> 4) & 15, cz = cell & 15;
 	const float siz = 1.0f;
 	const float sq = siz * 1.41421356237309504880168872420969808f * 0.5f;  // lib.rs:428 (exact: *1, *0.5)

@@ -1,42 +1,60 @@
-// mesh_kernel.cuh -- the sm_100a batch mesher kernel (device only).
+// mesh_kernel.cuh -- the sm_100a batch mesher kernel, v2 (device only).
 //
-// One persistent CTA (128 threads) takes chunk tickets in order.  Per chunk:
-//   1. 4 KiB of block ids -> shared memory with two 16-byte read-only loads per thread
-//   2. mesh_core.cuh phases: row masks, visibility, run starts, counts
-//   3. CTA-wide exclusive scan of the 6 x 256 row counts in emission order
-//   4. chunk base = exclusive prefix over all earlier chunks, obtained in the same
-//      launch by decoupled look-back over a per-chunk status word (single pass, the
-//      streams come out tightly packed in chunk order)
-//   5. descriptors -> one thread per quad writes 216 B into a staging tile ->
-//      cp.async.bulk (TMA) shared -> global store of the tile, overlapped with the
-//      next tile / next chunk
-// No tensor cores: the path is a scan/compaction, bound by the vertex-stream writes.
+// Persistent CTAs of 8 warps; every WARP is an independent chunk worker that draws chunk
+// tickets in order and runs the phases of mesh_core.cuh with its 32 lanes:
+//   A. 8 x (one 16-byte streaming load per lane) = the 4 KiB chunk; blocky masks, id-equality
+//      masks (neighbour columns arrive by warp shuffle)
+//   B. visibility / run starts of the six passes as bit operations on 16-bit z-masks
+//   C. in-register 16x16 bit transposes -> row masks in emission order, popc -> counts,
+//      warp shuffle scan -> quad offsets inside the chunk
+//   D. chunk base in the packed streams: every chunk publishes its counts in a status word;
+//      groups of 32 chunks and of 1024 chunks are summed by whichever warp arrives last
+//      (one atomic per chunk on a per-group counter), so a chunk's exclusive prefix is
+//      3 coalesced 32-lane loads (chunks of its group, groups of its super-group, super-groups)
+//      -- single pass, tightly packed, chunk order, no serial chain between chunks
+//   E. lane <-> quad: 216 B per lane into the warp's staging tile, then one cp.async.bulk
+//      (TMA) shared -> global store per tile, overlapped with the search for the next tile
+// No CTA-wide barrier after set-up; no tensor cores: the path is a scan/compaction bound by
+// the vertex-stream writes.
 #pragma once
 #include <cuda_runtime.h>
 #include "mesh_core.cuh"
 
 namespace mm {
 
+constexpr int kWarpsPerCta = 8;
+constexpr int kThreads = kWarpsPerCta * 32;
+constexpr uint32_t kMaxLaunchChunks = 32768;  // 32 super-groups of 32 groups of 32 chunks
+constexpr size_t kCtaTableBytes = 2048 + 256;
+constexpr size_t kCtaSmemBytes = kCtaTableBytes + kWarpsPerCta * sizeof(WarpSmem);
+
 struct KernelParams {
 	const unsigned char *chunks;  // n * 4096
 	const long long *offs;        // n * 3
-	uint32_t n;
+	uint32_t n;                   // <= kMaxLaunchChunks
+	uint32_t epoch;               // 1..16383, tags the status words of this launch
 	const TabEntry *table;        // 256 entries
+	const unsigned char *flags;   // 256 flag bytes (kFlagBlocky / kFlagCrossed)
 	unsigned char *out_i;         // intransparent vertex stream
 	unsigned char *out_t;         // transparent vertex stream
 	u64 cap_i, cap_t;             // arena capacities in quads (216 B units)
-	Range *ranges_i, *ranges_t;
-	u64 *status;                  // n look-back words for this launch (all zero at launch)
-	u64 *status_next;             // the other buffer: slot c is zeroed for the next launch
+	Range *ranges_i, *ranges_t;   // n entries each
+	u64 *st_chunk;                // status words: per chunk, per group of 32, per super-group of 1024
+	u64 *st_group;
+	u64 *st_super;
+	uint32_t *cnt_group;          // arrival counters (zero between launches)
+	uint32_t *cnt_super;
 	u64 *ticket;                  // monotonically increasing across launches
 	u64 ticket_base;              // its value at launch
-	u64 *totals;                  // [0] quads in out_i, [1] quad slots in out_t
+	const u64 *carry_in;          // quads already in the streams (earlier launches of the batch) or NULL
+	u64 *totals;                  // [0] quads in out_i, [1] quad slots in out_t after this launch
 };
 
-// look-back word: flag(2) | t quad slots (31) | i quads (31); counts saturate at kSat
-constexpr u64 kFlagAgg = 1ull << 62, kFlagPre = 2ull << 62;
-constexpr u64 kSat = 0x7fffffffull;
-
+// status word: epoch(14) | t quad slots(25) | i quads(25)
+constexpr u64 kCntMask = (1ull << 25) - 1;
+__device__ __forceinline__ u64 pack_status(uint32_t epoch, uint32_t i, uint32_t t) {
+	return ((u64)epoch << 50) | ((u64)t << 25) | (u64)i;
+}
 __device__ __forceinline__ u64 ld_status(const u64 *p) {
 	u64 v;
 	asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
@@ -45,16 +63,27 @@ __device__ __forceinline__ u64 ld_status(const u64 *p) {
 __device__ __forceinline__ void st_status(u64 *p, u64 v) {
 	asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
-__device__ __forceinline__ u64 pack_counts(u64 i, u64 t) {
-	return (i > kSat ? kSat : i) | ((t > kSat ? kSat : t) << 31);
+__device__ __forceinline__ uint32_t arrive(uint32_t *p) {  // release our status store, acquire the others'
+	uint32_t old;
+	asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(old) : "l"(p) : "memory");
+	return old;
 }
-__device__ __forceinline__ uint4 ld_stream16(const uint4 *p) {  // read-once input: keep it out of L1
-	uint4 r;
+__device__ __forceinline__ u64 wait_status(const u64 *p, uint32_t epoch) {
+	u64 w = ld_status(p);
+	while ((uint32_t)(w >> 50) != epoch) {
+		__nanosleep(64);
+		w = ld_status(p);
+	}
+	return w;
+}
+__device__ __forceinline__ Col ld_col(const unsigned char *p) {  // read-once input: keep it out of L1
+	Col c;
 	asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
-	             : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+	             : "=r"(c.w[0]), "=r"(c.w[1]), "=r"(c.w[2]), "=r"(c.w[3])
 	             : "l"(p));
-	return r;
+	return c;
 }
+__device__ __forceinline__ uint32_t warp_sum(uint32_t v) { return __reduce_add_sync(0xffffffffu, v); }
 
 // ---- TMA bulk store of a staging tile ------------------------------------------------
 __device__ __forceinline__ void fence_proxy_async_smem() {
@@ -72,7 +101,7 @@ __device__ __forceinline__ void bulk_wait_read_all() {
 }
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
-// Called by ONE thread after the tile is complete and fenced.  `g` is the byte address
+// Called by ONE lane after the tile is complete and fenced.  `g` is the byte address
 // of the tile in the stream (8-byte aligned); `sp` is the tile in shared memory with
 // sp == g (mod 16), so the 16-byte aligned middle goes out as one bulk copy and at
 // most 8 bytes at either end as ordinary stores.
@@ -89,206 +118,227 @@ __device__ __forceinline__ void store_tile(unsigned char *g, const unsigned char
 		*reinterpret_cast<uint2 *>(g + head + body) = *reinterpret_cast<const uint2 *>(sp + head + body);
 }
 
-// ---- CTA-wide exclusive scan over u16 counts -----------------------------------------
-// a[0 .. kThreads*PER) counts -> exclusive prefix in place; returns the total.
-template <int PER>
-__device__ __forceinline__ uint32_t block_exclusive_scan_u16(uint16_t *a, Smem &s, int tid) {
-	uint32_t v[PER];
-	uint32_t sum = 0;
-#pragma unroll
-	for (int i = 0; i < PER; i += 2) {
-		const uint32_t w = *reinterpret_cast<const uint32_t *>(a + tid * PER + i);
-		v[i] = w & 0xffffu;
-		v[i + 1] = w >> 16;
-		sum += v[i] + v[i + 1];
-	}
-	const int lane = tid & 31, warp = tid >> 5;
-	uint32_t inc = sum;
-#pragma unroll
-	for (int d = 1; d < 32; d <<= 1) {
-		const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
-		if (lane >= d) inc += o;
-	}
-	if (lane == 31) s.warp_sums[warp] = inc;
-	__syncthreads();
-	uint32_t base = 0, total = 0;
-#pragma unroll
-	for (int w = 0; w < kThreads / 32; w++) {
-		const uint32_t ws = s.warp_sums[w];
-		if (w < warp) base += ws;
-		total += ws;
-	}
-	uint32_t run = base + inc - sum;
-#pragma unroll
-	for (int i = 0; i < PER; i += 2) {
-		const uint32_t lo = run;
-		run += v[i];
-		const uint32_t hi = run;
-		run += v[i + 1];
-		*reinterpret_cast<uint32_t *>(a + tid * PER + i) = lo | (hi << 16);
-	}
-	__syncthreads();
-	return total;
+// ---- phase D: publish this chunk's counts, obtain its exclusive prefix --------------------
+__device__ __forceinline__ void sum_status(u64 w, uint32_t &si, uint32_t &st) {
+	si = warp_sum((uint32_t)(w & kCntMask));
+	st = warp_sum((uint32_t)((w >> 25) & kCntMask));
 }
 
-// ---- decoupled look-back (warp 0) ----------------------------------------------------
-__device__ __forceinline__ void lookback_and_publish(const KernelParams &p, Smem &s, uint32_t c,
-                                                     uint32_t nq, uint32_t nts, int lane) {
-	u64 ex_i = 0, ex_t = 0;
-	if (c == 0) {
-		if (lane == 0) st_status(p.status, kFlagPre | pack_counts(nq, nts));
-	} else {
-		if (lane == 0) st_status(p.status + c, kFlagAgg | pack_counts(nq, nts));
-		long long j = (long long)c - 1;
-		for (;;) {
-			const long long idx = j - lane;
-			u64 w = kFlagPre;  // virtual chunk -1: prefix 0
-			if (idx >= 0) {
-				w = ld_status(p.status + idx);
-				while ((w >> 62) == 0) {
-					__nanosleep(32);
-					w = ld_status(p.status + idx);
-				}
-			}
-			const unsigned pm = __ballot_sync(0xffffffffu, (w >> 62) == 2);
-			const int first = pm ? (__ffs((int)pm) - 1) : 32;
-			u64 vi = (lane <= first) ? (w & kSat) : 0;
-			u64 vt = (lane <= first) ? ((w >> 31) & kSat) : 0;
-#pragma unroll
-			for (int d = 16; d >= 1; d >>= 1) {
-				vi += __shfl_xor_sync(0xffffffffu, vi, d);
-				vt += __shfl_xor_sync(0xffffffffu, vt, d);
-			}
-			ex_i += vi;
-			ex_t += vt;
-			if (pm) break;
-			j -= 32;
-		}
-		if (lane == 0) st_status(p.status + c, kFlagPre | pack_counts(ex_i + nq, ex_t + nts));
-	}
+__device__ __forceinline__ void publish_and_prefix(const KernelParams &p, uint32_t c, uint32_t nq, uint32_t nts,
+                                                   int lane, u64 &base_i, u64 &base_t) {
+	const uint32_t g = c >> 5, r = c & 31u, sg = g >> 5, gs = g & 31u;
+	uint32_t old = 0;
 	if (lane == 0) {
-		p.status_next[c] = 0;
-		s.base_q = ex_i;
-		s.base_t = ex_t;
-		Range ri, rt;
-		ri.first_vertex = ex_i * 6ull; ri.vertex_count = nq * 6u; ri.reserved = 0;
-		rt.first_vertex = ex_t * 6ull; rt.vertex_count = nts * 6u; rt.reserved = 0;
-		p.ranges_i[c] = ri;
-		p.ranges_t[c] = rt;
-		if (c == p.n - 1) {
-			p.totals[0] = ex_i + nq;
-			p.totals[1] = ex_t + nts;
+		st_status(p.st_chunk + c, pack_status(p.epoch, nq, nts));
+		old = arrive(p.cnt_group + g);
+	}
+	old = __shfl_sync(0xffffffffu, old, 0);
+	const uint32_t size1 = min(32u, p.n - (g << 5));
+	if (old == size1 - 1u) {  // last chunk of its group to arrive: publish the group sum
+		const u64 w = (uint32_t)lane < size1 ? wait_status(p.st_chunk + (g << 5) + lane, p.epoch) : 0ull;
+		uint32_t si, st;
+		sum_status(w, si, st);
+		uint32_t old2 = 0;
+		if (lane == 0) {
+			st_status(p.st_group + g, pack_status(p.epoch, si, st));
+			p.cnt_group[g] = 0;  // ready for the next launch
+			old2 = arrive(p.cnt_super + sg);
+		}
+		old2 = __shfl_sync(0xffffffffu, old2, 0);
+		const uint32_t size2 = min(32u, ((p.n + 31u) >> 5) - (sg << 5));
+		if (old2 == size2 - 1u) {  // last group of its super-group
+			const u64 w2 = (uint32_t)lane < size2 ? wait_status(p.st_group + (sg << 5) + lane, p.epoch) : 0ull;
+			sum_status(w2, si, st);
+			if (lane == 0) {
+				st_status(p.st_super + sg, pack_status(p.epoch, si, st));
+				p.cnt_super[sg] = 0;
+			}
 		}
 	}
+	// exclusive prefix = earlier chunks of this group + earlier groups of this super-group
+	// + earlier super-groups (each at most 31 words, one per lane)
+	uint32_t ai = 0, at = 0;
+	if ((uint32_t)lane < r) {
+		const u64 w = wait_status(p.st_chunk + (g << 5) + lane, p.epoch);
+		ai += (uint32_t)(w & kCntMask);
+		at += (uint32_t)((w >> 25) & kCntMask);
+	}
+	if ((uint32_t)lane < gs) {
+		const u64 w = wait_status(p.st_group + (sg << 5) + lane, p.epoch);
+		ai += (uint32_t)(w & kCntMask);
+		at += (uint32_t)((w >> 25) & kCntMask);
+	}
+	if ((uint32_t)lane < sg) {
+		const u64 w = wait_status(p.st_super + lane, p.epoch);
+		ai += (uint32_t)(w & kCntMask);
+		at += (uint32_t)((w >> 25) & kCntMask);
+	}
+	u64 ci = 0, ct = 0;
+	if (p.carry_in) {
+		ci = p.carry_in[0];
+		ct = p.carry_in[1];
+	}
+	base_i = ci + warp_sum(ai);
+	base_t = ct + warp_sum(at);
 }
 
 // ---- the kernel -------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads, 4) mesh_batch_kernel(const KernelParams p) {
+__global__ void __launch_bounds__(kThreads, 2) mesh_batch_kernel(const KernelParams p) {
 	extern __shared__ __align__(128) unsigned char smem_raw[];
-	Smem &s = *reinterpret_cast<Smem *>(smem_raw);
+	TabEntry *tab = reinterpret_cast<TabEntry *>(smem_raw);
+	unsigned char *flags = smem_raw + 2048;
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+	WarpSmem &s = *reinterpret_cast<WarpSmem *>(smem_raw + kCtaTableBytes + (size_t)warp * sizeof(WarpSmem));
+	const unsigned full = 0xffffffffu;
 
-	// block table -> shared memory, once per CTA (2 KiB)
-	{
-		const uint4 *t4 = reinterpret_cast<const uint4 *>(p.table);
-		reinterpret_cast<uint4 *>(s.tab)[tid] = __ldg(t4 + tid);
-	}
+	// block table + flag bytes -> shared memory, once per CTA
+	if (tid < 128) reinterpret_cast<uint4 *>(tab)[tid] = __ldg(reinterpret_cast<const uint4 *>(p.table) + tid);
+	if (tid < 16) reinterpret_cast<uint4 *>(flags)[tid] = __ldg(reinterpret_cast<const uint4 *>(p.flags) + tid);
+	init_warp_smem(s, lane);
+	__syncthreads();
 
+	const int h = lane >> 4, y = lane & 15;
 	for (;;) {
-		__syncthreads();  // previous chunk fully consumed (desc, masks, ticket)
-		if (tid == 0) s.ticket = atomicAdd(p.ticket, 1ull) - p.ticket_base;
-		__syncthreads();
-		const u64 ticket = s.ticket;
+		// the staging tile (= Ey/Ex scratch) is free once the last bulk store has read it
+		if (lane == 0) bulk_wait_read_all();
+		u64 ticket = 0;
+		if (lane == 0) ticket = atomicAdd(p.ticket, 1ull) - p.ticket_base;
+		ticket = __shfl_sync(full, ticket, 0);  // also orders the previous chunk's smem reads before this one's writes
 		if (ticket >= (u64)p.n) break;
 		const uint32_t c = (uint32_t)ticket;
+		const unsigned char *chunk = p.chunks + (size_t)c * 4096u;
 
-		// 1. stage the chunk
-		const uint4 *src = reinterpret_cast<const uint4 *>(p.chunks + (size_t)c * 4096u);
-		const uint4 v0 = ld_stream16(src + tid), v1 = ld_stream16(src + tid + kThreads);
-		reinterpret_cast<uint4 *>(s.raw)[tid] = v0;
-		reinterpret_cast<uint4 *>(s.raw)[tid + kThreads] = v1;
-		phase_pos(s, tid, p.offs + 3 * (size_t)c);
-		if (tid == 0) s.any_crossed = 0;
-		const uint32_t w = v0.x;
-		const bool local_uniform = (v0.y == w) & (v0.z == w) & (v0.w == w) & (v1.x == w) & (v1.y == w) &
-		                           (v1.z == w) & (v1.w == w) & (w == (w & 0xffu) * 0x01010101u);
-		__syncthreads();
-		const bool uniform =
-		    __syncthreads_and(local_uniform && w == reinterpret_cast<const uint32_t *>(s.raw)[0]);
-
-		// 2./3. masks, counts, scan
-		uint32_t nq = 0, npl = 0;
-		const bool trivial = uniform && (s.tab[w & 0xffu].y >> 16) == 0u;  // e.g. an all-air chunk
-		if (!trivial) {
-			uint32_t cr = 0;
-			const RowRegs g0 = phase_rows(s, tid, cr);
-			const RowRegs g1 = phase_rows(s, tid + kThreads, cr);
-			if (cr) s.any_crossed = 1;
-			__syncthreads();
-			phase_vis(s, tid, g0);
-			phase_vis(s, tid + kThreads, g1);
-			const bool anyc = s.any_crossed != 0;
-			if (anyc) {
-				phase_crossed_cols(s, tid);
-				phase_crossed_cols(s, tid + kThreads);
+		// A. the chunk: lane (h, y) owns columns (x = 2j + h, y), j = 0..7
+		Col cols[8];
+#pragma unroll
+		for (int j = 0; j < 8; j++) cols[j] = ld_col(chunk + (size_t)(32 * j + lane) * 16u);
+		phase_pos(s, lane, p.offs + 3 * (size_t)c);
+		uint32_t anyb = 0, crossed_cols = 0;
+#pragma unroll
+		for (int j = 0; j < 8; j++) {
+			Col ny, nx;  // columns (x, y-1) and (x-1, y)
+#pragma unroll
+			for (int k = 0; k < 4; k++) {
+				ny.w[k] = __shfl_up_sync(full, cols[j].w[k], 1);
+				const uint32_t send = h ? (j > 0 ? cols[j > 0 ? j - 1 : 0].w[k] : 0u) : cols[j].w[k];
+				nx.w[k] = __shfl_xor_sync(full, send, 16);
 			}
-			__syncthreads();
-			nq = block_exclusive_scan_u16<12>(s.pre, s, tid);
-			if (anyc) npl = block_exclusive_scan_u16<2>(s.cpre, s, tid);
+			uint32_t sum;
+			const uint32_t bz = col_flags(flags, cols[j], sum);
+			const int col = 32 * j + lane;
+			s.Bzp[(2 * j + h + 1) * kBzStride + y + 1] = (uint16_t)bz;
+			smem_Ey(s)[col] = (uint16_t)eq_mask16(cols[j], ny);
+			smem_Ex(s)[col] = (uint16_t)eq_mask16(cols[j], nx);
+			anyb |= bz;
+			crossed_cols |= ((sum >> 5) ? 1u : 0u) << j;
+		}
+		uint32_t nq = 0, npl = 0;
+		if (__any_sync(full, (anyb | crossed_cols) != 0u)) {  // else: nothing drawn (e.g. an all-air chunk)
+			__syncwarp();
+			// B. run starts over z; crossed masks
+#pragma unroll
+			for (int j = 0; j < 8; j++) col_starts(s, tab, chunk, 2 * j + h, y);
+			if (__any_sync(full, crossed_cols != 0u)) {
+				uint32_t mine = 0;
+#pragma unroll
+				for (int j = 0; j < 8; j++) {
+					const uint32_t cz = ((crossed_cols >> j) & 1u) ? col_crossed(flags, cols[j]) : 0u;
+					s.Cz[32 * j + lane] = (uint16_t)cz;
+					mine += (uint32_t)__popc(cz);
+				}
+				npl = warp_sum(mine);
+			}
+			__syncwarp();
+			// C. masks over the merge axes; per-group quad counts; scan in emission order
+			transpose_blocky(s, lane);
+			uint32_t run = 0;
+#pragma unroll
+			for (int k = 0; k < 3; k++) {
+				const uint32_t cnt = transpose_group(s, lane + 32 * k);
+				uint32_t inc = cnt;
+#pragma unroll
+				for (int d = 1; d < 32; d <<= 1) {
+					const uint32_t o = __shfl_up_sync(full, inc, d);
+					if (lane >= d) inc += o;
+				}
+				s.gpre[lane + 32 * k] = (uint16_t)(run + inc - cnt);
+				run += __shfl_sync(full, inc, 31);
+			}
+			nq = run;
+			__syncwarp();
 		}
 		const uint32_t nts = npl * (uint32_t)kPlantQuads;
 
-		// 4. chunk base offsets
-		if (warp == 0) lookback_and_publish(p, s, c, nq, nts, lane);
-		__syncthreads();
-		const u64 base_q = s.base_q, base_t = s.base_t;
-
-		// 5a. intransparent stream: the six face passes
-		if (nq != 0 && base_q + nq <= p.cap_i) {
-			for (uint32_t w0 = 0; w0 < nq; w0 += kDescCap) {
-				phase_desc_row(s, tid, w0);
-				phase_desc_row(s, tid + kThreads, w0);
-				__syncthreads();
-				const uint32_t wend = min(nq, w0 + (uint32_t)kDescCap);
-				for (uint32_t t0 = w0; t0 < wend; t0 += kTileQuads) {
-					const uint32_t tn = min((uint32_t)kTileQuads, wend - t0);
-					if (tid == 0) bulk_wait_read_all();  // staging tile free again
-					__syncthreads();
-					unsigned char *g = p.out_i + (base_q + t0) * (u64)kQuadBytes;
-					unsigned char *sp = s.stage + ((uintptr_t)g & 8u);
-					if ((uint32_t)tid < tn) expand_face_quad(s, s.desc[t0 - w0 + tid], sp + tid * kQuadBytes);
-					fence_proxy_async_smem();
-					__syncthreads();
-					if (tid == 0) store_tile(g, sp, tn * kQuadBytes);
-				}
+		// D. where this chunk's vertices go
+		u64 base_i, base_t;
+		publish_and_prefix(p, c, nq, nts, lane, base_i, base_t);
+		if (lane == 0) {
+			Range ri, rt;
+			ri.first_vertex = base_i * 6ull; ri.vertex_count = nq * 6u; ri.reserved = 0;
+			rt.first_vertex = base_t * 6ull; rt.vertex_count = nts * 6u; rt.reserved = 0;
+			p.ranges_i[c] = ri;
+			p.ranges_t[c] = rt;
+			if (c == p.n - 1) {
+				p.totals[0] = base_i + nq;
+				p.totals[1] = base_t + nts;
 			}
 		}
-		// 5b. transparent stream: crossed plants, 4 quad slots each
+
+		// E1. intransparent stream: the six face passes
+		if (nq != 0 && base_i + nq <= p.cap_i) {
+			for (uint32_t t0 = 0; t0 < nq; t0 += kTileQuads) {
+				const uint32_t tn = min((uint32_t)kTileQuads, nq - t0);
+				int m = 0, c2 = 0, st = 0;
+				if ((uint32_t)lane < tn) find_quad(s, t0 + lane, m, c2, st);
+				if (lane == 0) bulk_wait_read_all();  // staging tile free again
+				__syncwarp();
+				unsigned char *g = p.out_i + (base_i + t0) * (u64)kQuadBytes;
+				unsigned char *sp = s.stage + ((uintptr_t)g & 8u);
+				if ((uint32_t)lane < tn) expand_face_quad(s, tab, chunk, m, c2, st, sp + lane * kQuadBytes);
+				fence_proxy_async_smem();
+				__syncwarp();
+				if (lane == 0) store_tile(g, sp, tn * kQuadBytes);
+			}
+		}
+		// E2. transparent stream: crossed plants, 4 quad slots each
 		if (npl != 0 && base_t + nts <= p.cap_t) {
-			for (uint32_t w0 = 0; w0 < npl; w0 += kDescCap) {
-				__syncthreads();  // descriptors of the previous round / stream are consumed
-				phase_desc_col(s, tid, w0);
-				phase_desc_col(s, tid + kThreads, w0);
-				__syncthreads();
-				const uint32_t qend = min(npl, w0 + (uint32_t)kDescCap) * kPlantQuads;
-				for (uint32_t t0 = w0 * kPlantQuads; t0 < qend; t0 += kTileQuads) {
-					const uint32_t tn = min((uint32_t)kTileQuads, qend - t0);
-					if (tid == 0) bulk_wait_read_all();
-					__syncthreads();
-					unsigned char *g = p.out_t + (base_t + t0) * (u64)kQuadBytes;
-					unsigned char *sp = s.stage + ((uintptr_t)g & 8u);
-					if ((uint32_t)tid < tn) {
-						const uint32_t q = t0 + tid;
-						expand_plant_quad(s, s.desc[(q >> 2) - w0], (int)(q & 3u), sp + tid * kQuadBytes);
-					}
-					fence_proxy_async_smem();
-					__syncthreads();
-					if (tid == 0) store_tile(g, sp, tn * kQuadBytes);
-				}
+			__syncwarp();  // S is no longer read: reuse it for the plant prefix
+			uint16_t *cpre = smem_cpre(s);
+			uint32_t cnt[8], mine = 0;
+#pragma unroll
+			for (int k = 0; k < 8; k++) {
+				cnt[k] = (uint32_t)__popc((uint32_t)s.Cz[lane * 8 + k]);
+				mine += cnt[k];
+			}
+			uint32_t inc = mine;
+#pragma unroll
+			for (int d = 1; d < 32; d <<= 1) {
+				const uint32_t o = __shfl_up_sync(full, inc, d);
+				if (lane >= d) inc += o;
+			}
+			uint32_t ex = inc - mine;
+#pragma unroll
+			for (int k = 0; k < 8; k++) {
+				cpre[lane * 8 + k] = (uint16_t)ex;
+				ex += cnt[k];
+			}
+			__syncwarp();
+			for (uint32_t t0 = 0; t0 < nts; t0 += kTileQuads) {
+				const uint32_t tn = min((uint32_t)kTileQuads, nts - t0);
+				int cell = 0;
+				if ((uint32_t)lane < tn) cell = find_plant(s, (t0 + lane) >> 2);
+				if (lane == 0) bulk_wait_read_all();
+				__syncwarp();
+				unsigned char *g = p.out_t + (base_t + t0) * (u64)kQuadBytes;
+				unsigned char *sp = s.stage + ((uintptr_t)g & 8u);
+				if ((uint32_t)lane < tn) expand_plant_quad(s, tab, chunk, cell, (int)((t0 + lane) & 3u), sp + lane * kQuadBytes);
+				fence_proxy_async_smem();
+				__syncwarp();
+				if (lane == 0) store_tile(g, sp, tn * kQuadBytes);
 			}
 		}
 	}
-	if (tid == 0) bulk_wait_all();  // all bulk stores of this CTA have landed before it exits
+	if (lane == 0) bulk_wait_all();  // all bulk stores of this warp have landed before it exits
 }
 
 }  // namespace mm

@@ -21,7 +21,7 @@
 static_assert(sizeof(mm_vertex) == 36, "Vertex must be 36 bytes (SURVEY.md 8b)");
 static_assert(sizeof(mm_range) == 16 && sizeof(mm::Range) == 16, "range layout");
 static_assert(sizeof(mm_block_entry) == 12, "block entry layout");
-static_assert(sizeof(mm::Smem) <= 56 * 1024, "4 CTAs per SM need <= 56 KiB each");
+static_assert(mm::kCtaSmemBytes <= 113 * 1024, "2 CTAs per SM need <= 113 KiB each");
 
 namespace {
 
@@ -54,17 +54,11 @@ int ensure_chunk_capacity(mm_ctx *c, uint32_t n) {
 	if (n <= c->cap_chunks) return MM_OK;
 	const uint32_t nc = std::max<uint32_t>(n, 1024u);
 	MM_CUDA(c, cudaStreamSynchronize(c->stream));
-	cudaFree(c->d_ranges_i); cudaFree(c->d_ranges_t); cudaFree(c->d_status[0]); cudaFree(c->d_status[1]);
-	c->d_ranges_i = c->d_ranges_t = nullptr; c->d_status[0] = c->d_status[1] = nullptr;
+	cudaFree(c->d_ranges_i); cudaFree(c->d_ranges_t);
+	c->d_ranges_i = c->d_ranges_t = nullptr;
 	c->cap_chunks = 0;
 	MM_CUDA(c, cudaMalloc(&c->d_ranges_i, sizeof(mm::Range) * (size_t)nc));
 	MM_CUDA(c, cudaMalloc(&c->d_ranges_t, sizeof(mm::Range) * (size_t)nc));
-	for (int b = 0; b < 2; b++) {
-		MM_CUDA(c, cudaMalloc(&c->d_status[b], sizeof(mm::u64) * (size_t)nc));
-		MM_CUDA(c, cudaMemsetAsync(c->d_status[b], 0, sizeof(mm::u64) * (size_t)nc, c->stream));
-		c->dirty_hi[b] = 0;
-	}
-	c->prev_n = 0;
 	c->cap_chunks = nc;
 	return MM_OK;
 }
@@ -94,44 +88,56 @@ int ensure_pinned(mm_ctx *c, unsigned char **p, size_t *have, size_t want) {
 	return MM_OK;
 }
 
-// Enqueue one mesher launch for (d_chunks, d_offs, n) on the context's stream.
+// Sizes of the prefix state for one launch of up to kMaxLaunchChunks chunks.
+constexpr size_t kSyncChunkWords = mm::kMaxLaunchChunks, kSyncGroupWords = mm::kMaxLaunchChunks / 32, kSyncSuperWords = 32;
+constexpr size_t kSyncStatusBytes = 8 * (kSyncChunkWords + kSyncGroupWords + kSyncSuperWords);
+constexpr size_t kSyncBytes = kSyncStatusBytes + 4 * (kSyncGroupWords + kSyncSuperWords);
+
+// Enqueue the mesher for (d_chunks, d_offs, n) on the context's stream: one launch per
+// kMaxLaunchChunks chunks, each continuing the packed streams where the previous one ended.
 int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, uint32_t n) {
-	const int b = c->cur;
-	// The previous launch zeroed slots [0, prev_n) of buffer b; anything dirtier is cleared here.
-	if (c->dirty_hi[b] > c->prev_n) {
-		MM_CUDA(c, cudaMemsetAsync(c->d_status[b] + c->prev_n, 0,
-		                           sizeof(mm::u64) * (size_t)(c->dirty_hi[b] - c->prev_n), c->stream));
-	}
-	c->dirty_hi[b] = 0;
-	mm::KernelParams p;
-	p.chunks = d_chunks;
-	p.offs = d_offs;
-	p.n = n;
-	p.table = c->d_table;
-	p.out_i = c->d_out_i;
-	p.out_t = c->d_out_t;
-	p.cap_i = c->cap_i;
-	p.cap_t = c->cap_t;
-	p.ranges_i = c->d_ranges_i;
-	p.ranges_t = c->d_ranges_t;
-	p.status = c->d_status[b];
-	p.status_next = c->d_status[b ^ 1];
-	p.ticket = c->d_ticket;
-	p.ticket_base = c->ticket_base;
-	p.totals = c->d_ticket + 1;
-	const uint32_t grid = std::min<uint32_t>(n, (uint32_t)(c->sm_count * c->ctas_per_sm));
 	MM_CUDA(c, cudaEventRecord(c->ev0, c->stream));
-	mm::mesh_batch_kernel<<<grid, mm::kThreads, sizeof(mm::Smem), c->stream>>>(p);
-	MM_CUDA(c, cudaGetLastError());
+	const mm::u64 *carry = nullptr;
+	for (uint32_t first = 0; first < n; first += mm::kMaxLaunchChunks) {
+		const uint32_t m = std::min<uint32_t>(n - first, mm::kMaxLaunchChunks);
+		if (++c->epoch >= (1u << 14)) {  // epoch tags wrap: forget every old status word
+			MM_CUDA(c, cudaMemsetAsync(c->d_sync, 0, kSyncStatusBytes, c->stream));
+			c->epoch = 1;
+		}
+		c->totals_slot ^= 1;
+		mm::KernelParams p;
+		p.chunks = d_chunks + (size_t)first * 4096u;
+		p.offs = d_offs + (size_t)first * 3u;
+		p.n = m;
+		p.epoch = c->epoch;
+		p.table = c->d_table;
+		p.flags = c->d_flags;
+		p.out_i = c->d_out_i;
+		p.out_t = c->d_out_t;
+		p.cap_i = c->cap_i;
+		p.cap_t = c->cap_t;
+		p.ranges_i = c->d_ranges_i + first;
+		p.ranges_t = c->d_ranges_t + first;
+		p.st_chunk = c->d_st_chunk;
+		p.st_group = c->d_st_group;
+		p.st_super = c->d_st_super;
+		p.cnt_group = c->d_cnt_group;
+		p.cnt_super = c->d_cnt_super;
+		p.ticket = c->d_ticket;
+		p.ticket_base = c->ticket_base;
+		p.carry_in = carry;
+		p.totals = c->d_ticket + 2 + 2 * c->totals_slot;
+		const uint32_t ctas = (m + mm::kWarpsPerCta - 1) / mm::kWarpsPerCta;
+		const uint32_t grid = std::min<uint32_t>(ctas, (uint32_t)(c->sm_count * c->ctas_per_sm));
+		mm::mesh_batch_kernel<<<grid, mm::kThreads, mm::kCtaSmemBytes, c->stream>>>(p);
+		MM_CUDA(c, cudaGetLastError());
+		c->ticket_base += (mm::u64)m + (mm::u64)grid * mm::kWarpsPerCta;  // every warp draws exactly one ticket >= m
+		carry = p.totals;
+		c->last_launches++;
+		c->total_launches++;
+	}
 	MM_CUDA(c, cudaEventRecord(c->ev1, c->stream));
-	MM_CUDA(c, cudaMemcpyAsync(c->h_totals, c->d_ticket + 1, 2 * sizeof(mm::u64), cudaMemcpyDeviceToHost, c->stream));
-	c->ticket_base += (mm::u64)n + grid;  // every CTA draws exactly one ticket >= n
-	c->dirty_hi[b] = n;                  // this launch dirtied [0, n) of b ...
-	// ... and zeroed [0, n) of the other buffer, which the next launch uses
-	c->prev_n = n;
-	c->cur = b ^ 1;
-	c->last_launches++;
-	c->total_launches++;
+	MM_CUDA(c, cudaMemcpyAsync(c->h_totals, carry, 2 * sizeof(mm::u64), cudaMemcpyDeviceToHost, c->stream));
 	return MM_OK;
 }
 
@@ -162,10 +168,10 @@ int mm_ctx_create(int device, mm_ctx **out) {
 		MM_CUDA(c, cudaGetDeviceProperties(&prop, device));
 		if (prop.major < 10) return fail(c, MM_ERR_NO_DEVICE, "device %d is sm_%d%d; this library is built for sm_100a", device, prop.major, prop.minor);
 		c->sm_count = prop.multiProcessorCount;
-		MM_CUDA(c, cudaFuncSetAttribute(mm::mesh_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(mm::Smem)));
+		MM_CUDA(c, cudaFuncSetAttribute(mm::mesh_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mm::kCtaSmemBytes));
 		MM_CUDA(c, cudaFuncSetAttribute(mm::mesh_batch_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
 		int occ = 0;
-		MM_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mm::mesh_batch_kernel, mm::kThreads, sizeof(mm::Smem)));
+		MM_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mm::mesh_batch_kernel, mm::kThreads, mm::kCtaSmemBytes));
 		if (occ < 1) return fail(c, MM_ERR_CUDA, "mesher kernel does not fit on an SM");
 		c->ctas_per_sm = occ;
 		MM_CUDA(c, cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
@@ -173,8 +179,16 @@ int mm_ctx_create(int device, mm_ctx **out) {
 		MM_CUDA(c, cudaEventCreate(&c->ev0));
 		MM_CUDA(c, cudaEventCreate(&c->ev1));
 		MM_CUDA(c, cudaMalloc(&c->d_table, sizeof(mm::TabEntry) * 256));
-		MM_CUDA(c, cudaMalloc(&c->d_ticket, sizeof(mm::u64) * 4));
-		MM_CUDA(c, cudaMemset(c->d_ticket, 0, sizeof(mm::u64) * 4));
+		MM_CUDA(c, cudaMalloc(&c->d_ticket, sizeof(mm::u64) * 8));
+		MM_CUDA(c, cudaMemset(c->d_ticket, 0, sizeof(mm::u64) * 8));
+		MM_CUDA(c, cudaMalloc(&c->d_flags, 256));
+		MM_CUDA(c, cudaMalloc(&c->d_sync, kSyncBytes));
+		MM_CUDA(c, cudaMemset(c->d_sync, 0, kSyncBytes));
+		c->d_st_chunk = reinterpret_cast<mm::u64 *>(c->d_sync);
+		c->d_st_group = c->d_st_chunk + kSyncChunkWords;
+		c->d_st_super = c->d_st_group + kSyncGroupWords;
+		c->d_cnt_group = reinterpret_cast<uint32_t *>(c->d_st_super + kSyncSuperWords);
+		c->d_cnt_super = c->d_cnt_group + kSyncGroupWords;
 		MM_CUDA(c, cudaHostAlloc(&c->h_totals, sizeof(mm::u64) * 2, cudaHostAllocDefault));
 		return MM_OK;
 	};
@@ -193,7 +207,7 @@ int mm_ctx_destroy(mm_ctx *c) {
 	cudaSetDevice(c->device);
 	if (c->own_stream) cudaStreamSynchronize(c->own_stream);
 	cudaFree(c->d_table); cudaFree(c->d_out_i); cudaFree(c->d_out_t); cudaFree(c->d_ranges_i);
-	cudaFree(c->d_ranges_t); cudaFree(c->d_status[0]); cudaFree(c->d_status[1]); cudaFree(c->d_ticket);
+	cudaFree(c->d_ranges_t); cudaFree(c->d_sync); cudaFree(c->d_flags); cudaFree(c->d_ticket);
 	cudaFree(c->d_in_chunks); cudaFree(c->d_in_offs);
 	if (c->h_totals) cudaFreeHost(c->h_totals);
 	if (c->h_in) cudaFreeHost(c->h_in);
@@ -271,6 +285,7 @@ int mm_set_block_table(mm_ctx *c, const mm_block_entry table[MM_TABLE_ENTRIES]) 
 	if (!c || !table) return MM_ERR_INVALID;
 	if (use_device(c)) return MM_ERR_CUDA;
 	mm::TabEntry t[256];
+	unsigned char fl[256];
 	for (int i = 0; i < 256; i++) {
 		const mm_block_entry &e = table[i];
 		if (e.kind > MM_KIND_CROSSED) return fail(c, MM_ERR_INVALID, "table[%d].kind = %u", i, e.kind);
@@ -278,9 +293,11 @@ int mm_set_block_table(mm_ctx *c, const mm_block_entry table[MM_TABLE_ENTRIES]) 
 		else t[i].x = (uint32_t)e.id_sides | ((uint32_t)e.id_top << 16);
 		t[i].y = (uint32_t)e.id_bottom | ((uint32_t)e.kind << 16);
 		if (e.kind == MM_KIND_NONE) { t[i].x = 0; t[i].y = 0; }
+		fl[i] = e.kind == MM_KIND_BLOCKY ? mm::kFlagBlocky : e.kind == MM_KIND_CROSSED ? mm::kFlagCrossed : 0;
 	}
 	MM_CUDA(c, cudaStreamSynchronize(c->stream));
 	MM_CUDA(c, cudaMemcpy(c->d_table, t, sizeof(t), cudaMemcpyHostToDevice));
+	MM_CUDA(c, cudaMemcpy(c->d_flags, fl, sizeof(fl), cudaMemcpyHostToDevice));
 	c->have_table = true;
 	return MM_OK;
 }
@@ -323,8 +340,6 @@ int mm_batch_finish(mm_ctx *c, mm_batch_out *out) {
 			MM_CUDA(c, cudaStreamSynchronize(c->stream));
 			c->tot_i = c->h_totals[0];
 			c->tot_t = c->h_totals[1];
-			if (c->tot_i >= mm::kSat || c->tot_t >= mm::kSat)
-				return fail(c, MM_ERR_INVALID, "batch produces >= 2^31 quads; split it");
 			if (c->tot_i <= c->cap_i && c->tot_t <= c->cap_t) break;
 			if (attempt >= 1) return fail(c, MM_ERR_CUDA, "arena still too small after growth");
 			int rc;  // grow to fit (+1/8 head room) and run again: the inputs are still resident

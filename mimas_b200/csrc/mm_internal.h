@@ -24,12 +24,16 @@ struct mm_ctx {
 	// per-chunk arrays
 	uint32_t cap_chunks = 0;
 	mm::Range *d_ranges_i = nullptr, *d_ranges_t = nullptr;
-	mm::u64 *d_status[2] = {nullptr, nullptr};
-	uint32_t dirty_hi[2] = {0, 0};  // slots [0, dirty_hi) of that buffer may be non-zero
-	int cur = 0;                    // status buffer the next launch uses
-	uint32_t prev_n = 0;            // n of the previous launch (it zeroed [0, prev_n) of buffer `cur`)
-	mm::u64 *d_ticket = nullptr;    // [0] ticket counter, [1..2] totals
+	// batch-wide prefix state (mesh_kernel.cuh phase D): status words tagged with the launch epoch,
+	// arrival counters that every launch leaves at zero
+	unsigned char *d_sync = nullptr;  // one allocation holding all of the below
+	mm::u64 *d_st_chunk = nullptr, *d_st_group = nullptr, *d_st_super = nullptr;
+	uint32_t *d_cnt_group = nullptr, *d_cnt_super = nullptr;
+	uint32_t epoch = 0;               // of the last launch; 1..16383, status words are cleared on wrap
+	mm::u64 *d_ticket = nullptr;      // [0] ticket counter, [2..3] and [4..5] alternating totals slots
+	int totals_slot = 0;              // slot the last launch wrote
 	mm::u64 ticket_base = 0;
+	unsigned char *d_flags = nullptr; // 256 flag bytes derived from the block table
 	mm::u64 *h_totals = nullptr;    // pinned, 2 words
 
 	// staged inputs for host callers

@@ -1,10 +1,10 @@
 // TEST INFRASTRUCTURE -- host emulation of the mesher kernel's control flow.
 //
-// Compiles mimas_b200/csrc/mesh_core.cuh (the per-thread phase functions the CUDA kernel
-// is built from) with g++ and runs the 128 logical threads of one CTA in a loop, with the
-// CTA-wide scan, the look-back prefix and the tile stores replaced by their serial
-// meaning.  Lets the bit-level logic be checked against the oracle on a machine without
-// a GPU.  Never linked into libmimas_meshgen_cuda.so.
+// Compiles mimas_b200/csrc/mesh_core.cuh (the per-lane phase functions the CUDA kernel
+// is built from) with g++ and runs the 32 logical lanes of one warp in a loop per phase,
+// with the warp shuffles, the warp scans, the batch-wide prefix and the tile stores
+// replaced by their serial meaning.  Lets the bit-level logic be checked against the
+// oracle on a machine without a GPU.  Never linked into libmimas_meshgen_cuda.so.
 #include <stdint.h>
 #include <string.h>
 
@@ -13,16 +13,6 @@
 #include "../../mimas_b200/csrc/mesh_core.cuh"
 
 using namespace mm;
-
-static uint32_t serial_exclusive_scan(uint16_t *a, int n) {
-	uint32_t run = 0;
-	for (int i = 0; i < n; i++) {
-		const uint32_t v = a[i];
-		a[i] = (uint16_t)run;
-		run += v;
-	}
-	return run;
-}
 
 // the three-part store of mesh_kernel.cuh store_tile(): head / 16-byte aligned body / tail
 static void store_tile(unsigned char *g, const unsigned char *sp, uint32_t bytes) {
@@ -34,65 +24,129 @@ static void store_tile(unsigned char *g, const unsigned char *sp, uint32_t bytes
 	if (bytes - head - body) memcpy(g + head + body, sp + head + body, 8);
 }
 
+static Col load_col(const uint8_t *chunk, int x, int y) {
+	Col c;
+	memcpy(c.w, chunk + (x * 16 + y) * 16, 16);
+	return c;
+}
+
+extern "C" void emul_transpose16(uint16_t rows[16]) {
+	uint32_t w[8];
+	for (int k = 0; k < 8; k++) w[k] = rows[2 * k] | ((uint32_t)rows[2 * k + 1] << 16);
+	transpose16(w);
+	for (int k = 0; k < 8; k++) {
+		rows[2 * k] = (uint16_t)w[k];
+		rows[2 * k + 1] = (uint16_t)(w[k] >> 16);
+	}
+}
+
+extern "C" uint32_t emul_eq_mask16(const uint8_t a[16], const uint8_t b[16]) {
+	Col ca, cb;
+	memcpy(ca.w, a, 16);
+	memcpy(cb.w, b, 16);
+	return eq_mask16(ca, cb);
+}
+
 extern "C" int emul_mesh_batch(const uint8_t *chunks, const int64_t *offs, uint32_t n, const TabEntry *tab,
                                unsigned char *out_i, uint64_t cap_i, unsigned char *out_t, uint64_t cap_t,
                                Range *ranges_i, Range *ranges_t, uint64_t *totals) {
-	Smem *sp = new Smem();
-	Smem &s = *sp;
-	memcpy(s.tab, tab, sizeof(s.tab));
+	WarpSmem *sp = new WarpSmem();
+	WarpSmem &s = *sp;
+	memset(&s, 0xA5, sizeof(s));  // nothing may depend on stale shared memory
+	uint8_t flags[256];
+	for (int i = 0; i < 256; i++) {
+		const uint32_t kind = tab[i].y >> 16;
+		flags[i] = kind == 1 ? kFlagBlocky : kind == 2 ? kFlagCrossed : 0;
+	}
+	for (int lane = 0; lane < kLanes; lane++) init_warp_smem(s, lane);
 	uint64_t run_q = 0, run_t = 0;
 	for (uint32_t c = 0; c < n; c++) {
-		memcpy(s.raw, chunks + (size_t)c * 4096, 4096);
+		const uint8_t *chunk = chunks + (size_t)c * 4096;
 		long long o3[3] = {offs[3 * c], offs[3 * c + 1], offs[3 * c + 2]};
-		for (int tid = 0; tid < kThreads; tid++) phase_pos(s, tid, o3);
-		bool uniform = true;
-		for (int i = 1; i < 4096; i++) uniform &= s.raw[i] == s.raw[0];
+		for (int lane = 0; lane < kLanes; lane++) phase_pos(s, lane, o3);
+		// A
+		uint32_t anyb = 0;
+		uint32_t crossed_cols[kLanes] = {0};
+		for (int j = 0; j < 8; j++)
+			for (int lane = 0; lane < kLanes; lane++) {
+				const int h = lane >> 4, y = lane & 15, x = 2 * j + h;
+				const Col own = load_col(chunk, x, y);
+				// what the shuffles deliver: lane-1 (wraps to garbage at y = 0) and the (x-1, y) column
+				Col ny = y > 0 ? load_col(chunk, x, y - 1) : own;
+				Col nx;
+				if (x > 0) nx = load_col(chunk, x - 1, y);
+				else memset(nx.w, 0, sizeof(nx.w));
+				uint32_t sum;
+				const uint32_t bz = col_flags(flags, own, sum);
+				s.Bzp[(x + 1) * kBzStride + y + 1] = (uint16_t)bz;
+				smem_Ey(s)[32 * j + lane] = (uint16_t)eq_mask16(own, ny);
+				smem_Ex(s)[32 * j + lane] = (uint16_t)eq_mask16(own, nx);
+				anyb |= bz;
+				crossed_cols[lane] |= ((sum >> 5) ? 1u : 0u) << j;
+			}
+		uint32_t anyc = 0;
+		for (int lane = 0; lane < kLanes; lane++) anyc |= crossed_cols[lane];
 		uint32_t nq = 0, npl = 0;
-		const bool trivial = uniform && (s.tab[s.raw[0]].y >> 16) == 0u;
-		if (!trivial) {
-			RowRegs g[kRows];
-			uint32_t cr = 0;
-			for (int r = 0; r < kRows; r++) g[r] = phase_rows(s, r, cr);
-			for (int r = 0; r < kRows; r++) phase_vis(s, r, g[r]);
-			if (cr)
-				for (int col = 0; col < kRows; col++) phase_crossed_cols(s, col);
-			nq = serial_exclusive_scan(s.pre, kPasses * kRows);
-			if (cr) npl = serial_exclusive_scan(s.cpre, kRows);
+		if (anyb | anyc) {
+			// B
+			for (int j = 0; j < 8; j++)
+				for (int lane = 0; lane < kLanes; lane++) col_starts(s, tab, chunk, 2 * j + (lane >> 4), lane & 15);
+			if (anyc) {
+				for (int j = 0; j < 8; j++)
+					for (int lane = 0; lane < kLanes; lane++) {
+						const int h = lane >> 4, y = lane & 15, x = 2 * j + h;
+						const uint32_t cz = ((crossed_cols[lane] >> j) & 1u) ? col_crossed(flags, load_col(chunk, x, y)) : 0u;
+						s.Cz[32 * j + lane] = (uint16_t)cz;
+						npl += (uint32_t)popc32(cz);
+					}
+			}
+			// C
+			for (int lane = 0; lane < kLanes; lane++) transpose_blocky(s, lane);
+			uint32_t cnt[kGroups];
+			for (int k = 0; k < 3; k++)
+				for (int lane = 0; lane < kLanes; lane++) cnt[lane + 32 * k] = transpose_group(s, lane + 32 * k);
+			for (int m = 0; m < kGroups; m++) {
+				s.gpre[m] = (uint16_t)nq;
+				nq += cnt[m];
+			}
 		}
 		const uint32_t nts = npl * kPlantQuads;
+		// D
 		const uint64_t base_q = run_q, base_t = run_t;
 		run_q += nq;
 		run_t += nts;
 		ranges_i[c].first_vertex = base_q * 6; ranges_i[c].vertex_count = nq * 6; ranges_i[c].reserved = 0;
 		ranges_t[c].first_vertex = base_t * 6; ranges_t[c].vertex_count = nts * 6; ranges_t[c].reserved = 0;
+		// E1
 		if (nq && base_q + nq <= cap_i) {
-			for (uint32_t w0 = 0; w0 < nq; w0 += kDescCap) {
-				for (int r = 0; r < kRows; r++) phase_desc_row(s, r, w0);
-				const uint32_t wend = std::min<uint32_t>(nq, w0 + kDescCap);
-				for (uint32_t t0 = w0; t0 < wend; t0 += kTileQuads) {
-					const uint32_t tn = std::min<uint32_t>(kTileQuads, wend - t0);
-					unsigned char *g = out_i + (base_q + t0) * (uint64_t)kQuadBytes;
-					unsigned char *st = s.stage + ((uintptr_t)g & 8u);
-					for (uint32_t tid = 0; tid < tn; tid++)
-						expand_face_quad(s, s.desc[t0 - w0 + tid], st + tid * kQuadBytes);
-					store_tile(g, st, tn * kQuadBytes);
-				}
+			for (uint32_t t0 = 0; t0 < nq; t0 += kTileQuads) {
+				const uint32_t tn = std::min<uint32_t>(kTileQuads, nq - t0);
+				int m[kLanes], c2[kLanes], st[kLanes];
+				for (uint32_t lane = 0; lane < tn; lane++) find_quad(s, t0 + lane, m[lane], c2[lane], st[lane]);
+				unsigned char *g = out_i + (base_q + t0) * (uint64_t)kQuadBytes;
+				unsigned char *stg = s.stage + ((uintptr_t)g & 8u);
+				for (uint32_t lane = 0; lane < tn; lane++)
+					expand_face_quad(s, tab, chunk, m[lane], c2[lane], st[lane], stg + lane * kQuadBytes);
+				store_tile(g, stg, tn * kQuadBytes);
 			}
 		}
+		// E2
 		if (npl && base_t + nts <= cap_t) {
-			for (uint32_t w0 = 0; w0 < npl; w0 += kDescCap) {
-				for (int col = 0; col < kRows; col++) phase_desc_col(s, col, w0);
-				const uint32_t qend = std::min<uint32_t>(npl, w0 + kDescCap) * kPlantQuads;
-				for (uint32_t t0 = w0 * kPlantQuads; t0 < qend; t0 += kTileQuads) {
-					const uint32_t tn = std::min<uint32_t>(kTileQuads, qend - t0);
-					unsigned char *g = out_t + (base_t + t0) * (uint64_t)kQuadBytes;
-					unsigned char *st = s.stage + ((uintptr_t)g & 8u);
-					for (uint32_t tid = 0; tid < tn; tid++) {
-						const uint32_t q = t0 + tid;
-						expand_plant_quad(s, s.desc[(q >> 2) - w0], (int)(q & 3u), st + tid * kQuadBytes);
-					}
-					store_tile(g, st, tn * kQuadBytes);
-				}
+			uint16_t *cpre = smem_cpre(s);
+			uint32_t ex = 0;
+			for (int col = 0; col < 256; col++) {
+				cpre[col] = (uint16_t)ex;
+				ex += (uint32_t)popc32(s.Cz[col]);
+			}
+			for (uint32_t t0 = 0; t0 < nts; t0 += kTileQuads) {
+				const uint32_t tn = std::min<uint32_t>(kTileQuads, nts - t0);
+				int cell[kLanes];
+				for (uint32_t lane = 0; lane < tn; lane++) cell[lane] = find_plant(s, (t0 + lane) >> 2);
+				unsigned char *g = out_t + (base_t + t0) * (uint64_t)kQuadBytes;
+				unsigned char *stg = s.stage + ((uintptr_t)g & 8u);
+				for (uint32_t lane = 0; lane < tn; lane++)
+					expand_plant_quad(s, tab, chunk, cell[lane], (int)((t0 + lane) & 3u), stg + lane * kQuadBytes);
+				store_tile(g, stg, tn * kQuadBytes);
 			}
 		}
 	}

@@ -54,7 +54,31 @@ def emul():
             o = p - b.ctypes.data
             outs.append(b[o:o + int(t) * 216].tobytes())
         return outs[0], outs[1], ri, rt
+    run.lib = lib
     return run
+
+
+def test_bit_transpose_and_equality_mask(emul):
+    """The two SWAR building blocks of phases A and C against their naive meaning."""
+    rng = np.random.RandomState(1)
+    for _ in range(200):
+        rows = rng.randint(0, 65536, size=16).astype(np.uint16)
+        want = np.zeros(16, dtype=np.uint16)
+        for r in range(16):
+            for c in range(16):
+                want[c] |= ((int(rows[r]) >> c) & 1) << r
+        got = rows.copy()
+        emul.lib.emul_transpose16(C.c_void_p(got.ctypes.data))
+        assert list(got) == list(want)
+    emul.lib.emul_eq_mask16.restype = C.c_uint32
+    for _ in range(500):
+        a = rng.randint(0, 256, size=16).astype(np.uint8)
+        b = a.copy()
+        flip = rng.rand(16) < rng.rand()
+        b[flip] = rng.randint(0, 256, size=int(flip.sum()))
+        b[0] ^= rng.choice([0, 0x80, 0x01, 0xff])
+        want = sum(1 << z for z in range(16) if a[z] == b[z])
+        assert emul.lib.emul_eq_mask16(C.c_void_p(a.ctypes.data), C.c_void_p(b.ctypes.data)) == want
 
 
 TAB = kernel_table(G.entries, G.fallback)
