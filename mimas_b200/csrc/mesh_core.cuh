@@ -71,24 +71,33 @@ struct Col {
 struct alignas(16) WarpSmem {
 	// staging tile: +16 so the tile can be shifted by 8 B to match the 16-B phase of its
 	// destination in the vertex stream (quads are only 8-B aligned: 216 = 8 * 27).
-	// Before the expansion phase the same bytes hold the id-equality masks (Ey, Ex).
+	// During the analysis phases the same bytes hold the id-equality masks (Ey, Ex: 2 x 512 B)
+	// and the chunk itself (raw, 4096 B at offset 1024, filled by one bulk async copy).
 	alignas(16) unsigned char stage[kStageBytes + 16];
 	// run-start masks.  Phase B writes them over z per column: passes 1,3,4,6 (p = 0,2,3,5) at
 	// [p][x*16 + y], passes 2,5 (p = 1,4) at [p][y*16 + x]; phase C transposes every 16-entry
 	// block in place into [p][c1*16 + c2] = mask over the merge axis of row (c1, c2).
-	// After the intransparent stream is written, S[0..] is reused for the plant prefix (cpre).
+	// After the intransparent stream is written, S[0..511] is reused for the plants (Cz, cpre).
 	alignas(16) uint16_t S[kPasses * 256 + 16];
 	alignas(16) uint16_t By[256];              // blocky mask over y for row (x, z): [x*16 + z]
 	alignas(16) uint16_t Bx[256];              // blocky mask over x for row (y, z): [y*16 + z]
-	alignas(16) uint16_t Cz[256];              // crossed mask over z for column (x, y): [x*16 + y]
 	alignas(16) uint16_t gpre[128];            // exclusive quad prefix per group; [96..127] = 0xffff
-	uint16_t Bzp[kBzStride * kBzStride];       // blocky mask over z per column, zero border
+	// phases A-C: Bzp = blocky mask over z per column, 18 x 18 with a zero border;
+	// from phase C on: rowpre[m*16 + c2] = run starts of group m before row c2 (<= 240)
+	alignas(16) unsigned char rowpre[kGroups * 16];
 	float pos[3][17];                          // (offs + c) as f32 for c in 0..=16, per axis
+	alignas(8) unsigned long long mbar;        // mbarrier of the chunk load (device only)
 };
+static_assert(kBzStride * kBzStride * 2 <= kGroups * 16, "Bzp aliases rowpre");
+static_assert(1024 + 4096 <= kStageBytes, "Ey, Ex and the raw chunk alias the staging tile");
 
 MM_HD uint16_t *smem_Ey(WarpSmem &s) { return reinterpret_cast<uint16_t *>(s.stage); }
 MM_HD uint16_t *smem_Ex(WarpSmem &s) { return reinterpret_cast<uint16_t *>(s.stage) + 256; }
-MM_HD uint16_t *smem_cpre(WarpSmem &s) { return s.S; }  // 257 entries, [256] = 0xffff
+MM_HD unsigned char *smem_raw(WarpSmem &s) { return s.stage + 1024; }
+MM_HD uint16_t *smem_Bzp(WarpSmem &s) { return reinterpret_cast<uint16_t *>(s.rowpre); }
+MM_HD const uint16_t *smem_Bzp(const WarpSmem &s) { return reinterpret_cast<const uint16_t *>(s.rowpre); }
+MM_HD uint16_t *smem_Cz(WarpSmem &s) { return s.S; }           // crossed mask over z per column (plants phase)
+MM_HD uint16_t *smem_cpre(WarpSmem &s) { return s.S + 256; }   // plants before column col
 
 MM_HD int popc32(uint32_t v) {
 #if defined(__CUDA_ARCH__)
@@ -157,19 +166,29 @@ MM_HD uint32_t f2u(float f) {
 MM_HD float zsig(float v) { return v > 0.0f ? 1.0f : (v < 0.0f ? -1.0f : 0.0f); }
 
 // ---- warp set-up ---------------------------------------------------------------------
-// Once per warp: the zero border of Bzp (a neighbour outside the chunk never blocks,
-// lib.rs:277-280) and the sentinels of the group prefix.
-MM_HD void init_warp_smem(WarpSmem &s, int lane) {
-	for (int i = lane; i < kBzStride * kBzStride; i += kLanes) s.Bzp[i] = 0;
-	s.gpre[kGroups + lane] = 0xffffu;
+// Once per warp: the sentinels of the group prefix.
+MM_HD void init_warp_smem(WarpSmem &s, int lane) { s.gpre[kGroups + lane] = 0xffffu; }
+
+// Once per chunk: the zero border of Bzp (a neighbour outside the chunk never blocks,
+// lib.rs:277-280); the interior is written by phase A.
+MM_HD void zero_border(WarpSmem &s, int lane) {
+	uint16_t *B = smem_Bzp(s);
+	if (lane < kBzStride) {
+		B[lane] = 0;
+		B[(kBzStride - 1) * kBzStride + lane] = 0;
+	}
+	if (lane < 16) {
+		B[(lane + 1) * kBzStride] = 0;
+		B[(lane + 1) * kBzStride + kBzStride - 1] = 0;
+	}
 }
 
 // pos[a][c] = (offs[a] + c) as f32 for c in 0..=16: every `pos.x as f32` the reference
 // evaluates (lib.rs:323-325 etc.), including the sentinel cell 16 (lib.rs:309).
 MM_HD void phase_pos(WarpSmem &s, int lane, const long long *offs3) {
-	for (int i = lane; i < 51; i += kLanes) {
-		const int a = i / 17, c = i % 17;
-		s.pos[a][c] = i64_to_f32(offs3[a] + (long long)c);
+	if (lane < 17) {
+#pragma unroll
+		for (int a = 0; a < 3; a++) s.pos[a][lane] = i64_to_f32(offs3[a] + (long long)lane);
 	}
 }
 
@@ -194,16 +213,32 @@ MM_HD uint32_t col_flags(const uint8_t *flags, const Col &c, uint32_t &sum) {
 
 // Bit z set <=> the two columns hold the same block id at z (equal ids => equal textures
 // for every face; different ids are settled exactly by fix_equal()).
+MM_HD uint32_t mulhi32(uint32_t a, uint32_t b) {
+#if defined(__CUDA_ARCH__)
+	return __umulhi(a, b);
+#else
+	return (uint32_t)(((u64)a * (u64)b) >> 32);
+#endif
+}
+MM_HD uint32_t funnel_r4(uint32_t lo, uint32_t hi) {  // (hi:lo) >> 4, low word
+#if defined(__CUDA_ARCH__)
+	return __funnelshift_r(lo, hi, 4);
+#else
+	return (lo >> 4) | (hi << 28);
+#endif
+}
 MM_HD uint32_t eq_mask16(const Col &a, const Col &b) {
-	uint32_t m = 0;
+	uint32_t acc = 0;
 #pragma unroll
 	for (int k = 0; k < 4; k++) {
 		const uint32_t v = a.w[k] ^ b.w[k];
-		const uint32_t t = ((v & 0x7f7f7f7fu) + 0x7f7f7f7fu) | v;  // bit 7 of a byte: byte != 0
-		const uint32_t u = (~t & 0x80808080u) >> 7;                // bit 0 of a byte: ids equal
-		m |= (((u * 0x00204081u) >> 21) & 0xfu) << (4 * k);        // gather bits 0,8,16,24 -> 0..3
+		const uint32_t t = ((v & 0x7f7f7f7fu) + 0x7f7f7f7fu) | v;  // bit 7 of a byte: ids differ
+		const uint32_t u = ~t & 0x80808080u;                       // bit 7 of a byte: ids equal
+		// bits 7,15,23,31 -> bits 32..35 of the 64-bit product (multiplier 2^25 + 2^18 + 2^11 + 2^4; all
+		// partial products land on distinct bits, so nothing carries); the nibble enters acc from the top
+		acc = funnel_r4(acc, mulhi32(u, 0x02040810u));
 	}
-	return m;
+	return acc >> 16;
 }
 
 // Crossed mask over z of one column (slow path, only for columns whose flag sum says so).
@@ -238,7 +273,7 @@ MM_HD uint32_t fix_equal(const TabEntry *tab, const uint8_t *chunk, uint32_t d, 
 }
 
 MM_HD void col_starts(WarpSmem &s, const TabEntry *tab, const uint8_t *chunk, int x, int y) {
-	const uint16_t *B = s.Bzp + (x + 1) * kBzStride + (y + 1);
+	const uint16_t *B = smem_Bzp(s) + (x + 1) * kBzStride + (y + 1);
 	const uint32_t b = B[0];
 	const uint32_t bym = B[-1], byp = B[1], bxm = B[-kBzStride], bxp = B[kBzStride];
 	const uint32_t bmm = B[-kBzStride - 1], bpm = B[kBzStride - 1], bmp = B[-kBzStride + 1];
@@ -304,8 +339,9 @@ MM_HD void transpose16(uint32_t w[8]) {
 	}
 }
 
-// Transposes the 16-entry block at S[m*16 ..] in place and returns the number of run
-// starts (= quads) in group m = pass*16 + c1.
+// Transposes the 16-entry block at S[m*16 ..] in place, writes the per-row prefix of the
+// group (rowpre) and returns the number of run starts (= quads) in group m = pass*16 + c1.
+// Must not run before every lane has finished transpose_blocky (rowpre aliases Bzp).
 MM_HD uint32_t transpose_group(WarpSmem &s, int m) {
 	uint32_t *p = reinterpret_cast<uint32_t *>(s.S + m * 16);
 	uint32_t w[8];
@@ -317,13 +353,21 @@ MM_HD uint32_t transpose_group(WarpSmem &s, int m) {
 	}
 	if (any == 0) return 0;
 	transpose16(w);
-	uint32_t cnt = 0;
+	uint32_t run = 0;
+	uint32_t pre[4];
 #pragma unroll
 	for (int k = 0; k < 8; k++) {
 		p[k] = w[k];
-		cnt += (uint32_t)popc32(w[k]);
+		const uint32_t c0 = (uint32_t)popc32(w[k] & 0xffffu), c1 = (uint32_t)popc32(w[k] >> 16);
+		const uint32_t e = run | ((run + c0) << 8);  // exclusive prefixes of rows 2k, 2k+1 (<= 240)
+		if (k & 1) pre[k >> 1] |= e << 16;
+		else pre[k >> 1] = e;
+		run += c0 + c1;
 	}
-	return cnt;
+	uint32_t *rp = reinterpret_cast<uint32_t *>(s.rowpre + m * 16);
+#pragma unroll
+	for (int k = 0; k < 4; k++) rp[k] = pre[k];
+	return run;
 }
 
 // Blocky masks over the merge axes, from the z-masks: job 0..15 -> By rows of x = job
@@ -335,8 +379,9 @@ MM_HD void transpose_blocky(WarpSmem &s, int job) {
 #pragma unroll
 	for (int k = 0; k < 8; k++) {
 		const int r0 = 2 * k, r1 = 2 * k + 1;
-		const uint32_t lo = over_y ? s.Bzp[(f + 1) * kBzStride + r0 + 1] : s.Bzp[(r0 + 1) * kBzStride + f + 1];
-		const uint32_t hi = over_y ? s.Bzp[(f + 1) * kBzStride + r1 + 1] : s.Bzp[(r1 + 1) * kBzStride + f + 1];
+		const uint16_t *B = smem_Bzp(s);
+		const uint32_t lo = over_y ? B[(f + 1) * kBzStride + r0 + 1] : B[(r0 + 1) * kBzStride + f + 1];
+		const uint32_t hi = over_y ? B[(f + 1) * kBzStride + r1 + 1] : B[(r1 + 1) * kBzStride + f + 1];
 		w[k] = lo | (hi << 16);
 	}
 	transpose16(w);
@@ -355,28 +400,14 @@ MM_HD void find_quad(const WarpSmem &s, uint32_t q, int &m, int &c2, int &st) {
 		if ((uint32_t)s.gpre[lo + step] <= q) lo += step;  // largest m with gpre[m] <= q
 	m = lo;
 	const uint32_t r = q - s.gpre[lo];
-	const uint32_t *p = reinterpret_cast<const uint32_t *>(s.S + lo * 16);
-	uint32_t run = 0, base = 0, mask = 0;
+	const unsigned char *rp = s.rowpre + lo * 16;
 	int row = 0;
-	bool found = false;
 #pragma unroll
-	for (int k = 0; k < 8; k++) {
-		const uint32_t w = p[k];
-#pragma unroll
-		for (int h = 0; h < 2; h++) {
-			const uint32_t rm = h ? (w >> 16) : (w & 0xffffu);
-			const uint32_t nxt = run + (uint32_t)popc32(rm);
-			if (!found && r < nxt) {  // first row whose inclusive count exceeds r
-				found = true;
-				row = 2 * k + h;
-				base = run;
-				mask = rm;
-			}
-			run = nxt;
-		}
-	}
+	for (int step = 8; step >= 1; step >>= 1)
+		if ((uint32_t)rp[row + step] <= r) row += step;    // largest row with rowpre <= r: it holds quad r
 	c2 = row;
-	for (uint32_t i = r - base; i > 0; i--) mask &= mask - 1u;  // drop the lower run starts
+	uint32_t mask = s.S[lo * 16 + row];
+	for (uint32_t i = r - rp[row]; i > 0; i--) mask &= mask - 1u;  // drop the lower run starts
 	st = ffs32(mask) - 1;
 }
 
@@ -498,7 +529,7 @@ MM_HD int find_plant(WarpSmem &s, uint32_t pl) {
 #pragma unroll
 	for (int step = 128; step >= 1; step >>= 1)
 		if ((uint32_t)cpre[lo + step] <= pl) lo += step;
-	uint32_t mask = s.Cz[lo];
+	uint32_t mask = smem_Cz(s)[lo];
 	for (uint32_t i = pl - cpre[lo]; i > 0; i--) mask &= mask - 1u;
 	return lo * 16 + ffs32(mask) - 1;
 }

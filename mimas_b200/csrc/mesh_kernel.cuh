@@ -63,25 +63,51 @@ __device__ __forceinline__ u64 ld_status(const u64 *p) {
 __device__ __forceinline__ void st_status(u64 *p, u64 v) {
 	asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
-__device__ __forceinline__ uint32_t arrive(uint32_t *p) {  // release our status store, acquire the others'
+// Arrival counter of a group.  Relaxed on purpose: the counter only elects the warp that sums the
+// group; every status word it then reads carries its own epoch tag and is waited for individually.
+__device__ __forceinline__ uint32_t arrive(uint32_t *p) {
 	uint32_t old;
-	asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(old) : "l"(p) : "memory");
+	asm volatile("atom.relaxed.gpu.global.add.u32 %0, [%1], 1;" : "=r"(old) : "l"(p) : "memory");
 	return old;
 }
-__device__ __forceinline__ u64 wait_status(const u64 *p, uint32_t epoch) {
+__device__ __forceinline__ u64 wait_status(const u64 *p, uint32_t epoch, uint32_t max_ns) {
 	u64 w = ld_status(p);
+	uint32_t ns = 32;
 	while ((uint32_t)(w >> 50) != epoch) {
-		__nanosleep(64);
+		__nanosleep(ns);
+		if (ns < max_ns) ns <<= 1;
 		w = ld_status(p);
 	}
 	return w;
 }
-__device__ __forceinline__ Col ld_col(const unsigned char *p) {  // read-once input: keep it out of L1
+__device__ __forceinline__ Col lds_col(const unsigned char *p) {
+	const uint4 v = *reinterpret_cast<const uint4 *>(p);
 	Col c;
-	asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
-	             : "=r"(c.w[0]), "=r"(c.w[1]), "=r"(c.w[2]), "=r"(c.w[3])
-	             : "l"(p));
+	c.w[0] = v.x; c.w[1] = v.y; c.w[2] = v.z; c.w[3] = v.w;
 	return c;
+}
+
+// ---- TMA bulk load of one chunk (4 KiB, global -> shared) ------------------------------
+__device__ __forceinline__ void mbar_init(unsigned long long *mbar) {
+	const uint32_t a = (uint32_t)__cvta_generic_to_shared(mbar);
+	asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(a) : "memory");
+}
+__device__ __forceinline__ void bulk_load_g2s(void *sdst, const void *gsrc, uint32_t bytes, unsigned long long *mbar) {
+	const uint32_t d = (uint32_t)__cvta_generic_to_shared(sdst), b = (uint32_t)__cvta_generic_to_shared(mbar);
+	asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(b), "r"(bytes) : "memory");
+	asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(d),
+	             "l"(gsrc), "r"(bytes), "r"(b)
+	             : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *mbar, uint32_t parity) {
+	const uint32_t b = (uint32_t)__cvta_generic_to_shared(mbar);
+	uint32_t done;
+	do {
+		asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+		             : "=r"(done)
+		             : "r"(b), "r"(parity)
+		             : "memory");
+	} while (!done);
 }
 __device__ __forceinline__ uint32_t warp_sum(uint32_t v) { return __reduce_add_sync(0xffffffffu, v); }
 
@@ -126,6 +152,7 @@ __device__ __forceinline__ void sum_status(u64 w, uint32_t &si, uint32_t &st) {
 
 __device__ __forceinline__ void publish_and_prefix(const KernelParams &p, uint32_t c, uint32_t nq, uint32_t nts,
                                                    int lane, u64 &base_i, u64 &base_t) {
+	const uint32_t max_ns = (nq | nts) ? 256u : 2048u;  // an empty chunk is in no hurry
 	const uint32_t g = c >> 5, r = c & 31u, sg = g >> 5, gs = g & 31u;
 	uint32_t old = 0;
 	if (lane == 0) {
@@ -135,7 +162,7 @@ __device__ __forceinline__ void publish_and_prefix(const KernelParams &p, uint32
 	old = __shfl_sync(0xffffffffu, old, 0);
 	const uint32_t size1 = min(32u, p.n - (g << 5));
 	if (old == size1 - 1u) {  // last chunk of its group to arrive: publish the group sum
-		const u64 w = (uint32_t)lane < size1 ? wait_status(p.st_chunk + (g << 5) + lane, p.epoch) : 0ull;
+		const u64 w = (uint32_t)lane < size1 ? wait_status(p.st_chunk + (g << 5) + lane, p.epoch, 64u) : 0ull;
 		uint32_t si, st;
 		sum_status(w, si, st);
 		uint32_t old2 = 0;
@@ -147,7 +174,7 @@ __device__ __forceinline__ void publish_and_prefix(const KernelParams &p, uint32
 		old2 = __shfl_sync(0xffffffffu, old2, 0);
 		const uint32_t size2 = min(32u, ((p.n + 31u) >> 5) - (sg << 5));
 		if (old2 == size2 - 1u) {  // last group of its super-group
-			const u64 w2 = (uint32_t)lane < size2 ? wait_status(p.st_group + (sg << 5) + lane, p.epoch) : 0ull;
+			const u64 w2 = (uint32_t)lane < size2 ? wait_status(p.st_group + (sg << 5) + lane, p.epoch, 64u) : 0ull;
 			sum_status(w2, si, st);
 			if (lane == 0) {
 				st_status(p.st_super + sg, pack_status(p.epoch, si, st));
@@ -159,17 +186,17 @@ __device__ __forceinline__ void publish_and_prefix(const KernelParams &p, uint32
 	// + earlier super-groups (each at most 31 words, one per lane)
 	uint32_t ai = 0, at = 0;
 	if ((uint32_t)lane < r) {
-		const u64 w = wait_status(p.st_chunk + (g << 5) + lane, p.epoch);
+		const u64 w = wait_status(p.st_chunk + (g << 5) + lane, p.epoch, max_ns);
 		ai += (uint32_t)(w & kCntMask);
 		at += (uint32_t)((w >> 25) & kCntMask);
 	}
 	if ((uint32_t)lane < gs) {
-		const u64 w = wait_status(p.st_group + (sg << 5) + lane, p.epoch);
+		const u64 w = wait_status(p.st_group + (sg << 5) + lane, p.epoch, max_ns);
 		ai += (uint32_t)(w & kCntMask);
 		at += (uint32_t)((w >> 25) & kCntMask);
 	}
 	if ((uint32_t)lane < sg) {
-		const u64 w = wait_status(p.st_super + lane, p.epoch);
+		const u64 w = wait_status(p.st_super + lane, p.epoch, max_ns);
 		ai += (uint32_t)(w & kCntMask);
 		at += (uint32_t)((w >> 25) & kCntMask);
 	}
@@ -184,75 +211,72 @@ __device__ __forceinline__ void publish_and_prefix(const KernelParams &p, uint32
 
 // ---- the kernel -------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads, 2) mesh_batch_kernel(const KernelParams p) {
-	extern __shared__ __align__(128) unsigned char smem_raw[];
-	TabEntry *tab = reinterpret_cast<TabEntry *>(smem_raw);
-	unsigned char *flags = smem_raw + 2048;
+	extern __shared__ __align__(128) unsigned char smem_raw_bytes[];
+	TabEntry *tab = reinterpret_cast<TabEntry *>(smem_raw_bytes);
+	unsigned char *flags = smem_raw_bytes + 2048;
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-	WarpSmem &s = *reinterpret_cast<WarpSmem *>(smem_raw + kCtaTableBytes + (size_t)warp * sizeof(WarpSmem));
+	WarpSmem &s = *reinterpret_cast<WarpSmem *>(smem_raw_bytes + kCtaTableBytes + (size_t)warp * sizeof(WarpSmem));
 	const unsigned full = 0xffffffffu;
 
 	// block table + flag bytes -> shared memory, once per CTA
 	if (tid < 128) reinterpret_cast<uint4 *>(tab)[tid] = __ldg(reinterpret_cast<const uint4 *>(p.table) + tid);
 	if (tid < 16) reinterpret_cast<uint4 *>(flags)[tid] = __ldg(reinterpret_cast<const uint4 *>(p.flags) + tid);
 	init_warp_smem(s, lane);
+	if (lane == 0) {
+		mbar_init(&s.mbar);
+		fence_proxy_async_smem();  // the barrier is visible to the bulk-copy engine
+	}
 	__syncthreads();
 
 	const int h = lane >> 4, y = lane & 15;
+	unsigned char *raw = smem_raw(s);
+	uint32_t parity = 0;
 	for (;;) {
-		// the staging tile (= Ey/Ex scratch) is free once the last bulk store has read it
-		if (lane == 0) bulk_wait_read_all();
 		u64 ticket = 0;
-		if (lane == 0) ticket = atomicAdd(p.ticket, 1ull) - p.ticket_base;
+		if (lane == 0) {
+			bulk_wait_read_all();  // the staging tile (= raw chunk + Ey/Ex) is free once the last bulk store has read it
+			ticket = atomicAdd(p.ticket, 1ull) - p.ticket_base;
+		}
 		ticket = __shfl_sync(full, ticket, 0);  // also orders the previous chunk's smem reads before this one's writes
 		if (ticket >= (u64)p.n) break;
 		const uint32_t c = (uint32_t)ticket;
 		const unsigned char *chunk = p.chunks + (size_t)c * 4096u;
-
-		// A. the chunk: lane (h, y) owns columns (x = 2j + h, y), j = 0..7
-		Col cols[8];
-#pragma unroll
-		for (int j = 0; j < 8; j++) cols[j] = ld_col(chunk + (size_t)(32 * j + lane) * 16u);
+		if (lane == 0) bulk_load_g2s(raw, chunk, 4096u, &s.mbar);  // TMA: 4 KiB chunk -> shared memory
 		phase_pos(s, lane, p.offs + 3 * (size_t)c);
-		uint32_t anyb = 0, crossed_cols = 0;
-#pragma unroll
+		zero_border(s, lane);
+		mbar_wait(&s.mbar, parity);
+		parity ^= 1u;
+
+		// A. lane (h, y) owns columns (x = 2j + h, y), j = 0..7: blocky masks and id-equality masks
+		uint32_t anyb = 0, crossed_cols = 0, ncrossed = 0;
+#pragma unroll 2
 		for (int j = 0; j < 8; j++) {
-			Col ny, nx;  // columns (x, y-1) and (x-1, y)
-#pragma unroll
-			for (int k = 0; k < 4; k++) {
-				ny.w[k] = __shfl_up_sync(full, cols[j].w[k], 1);
-				const uint32_t send = h ? (j > 0 ? cols[j > 0 ? j - 1 : 0].w[k] : 0u) : cols[j].w[k];
-				nx.w[k] = __shfl_xor_sync(full, send, 16);
-			}
-			uint32_t sum;
-			const uint32_t bz = col_flags(flags, cols[j], sum);
 			const int col = 32 * j + lane;
-			s.Bzp[(2 * j + h + 1) * kBzStride + y + 1] = (uint16_t)bz;
-			smem_Ey(s)[col] = (uint16_t)eq_mask16(cols[j], ny);
-			smem_Ex(s)[col] = (uint16_t)eq_mask16(cols[j], nx);
+			const Col own = lds_col(raw + col * 16);
+			const Col ny = lds_col(raw + (col - 1) * 16);   // (x, y-1); unused garbage for y = 0
+			const Col nx = lds_col(raw + (col - 16) * 16);  // (x-1, y); unused garbage for x = 0
+			uint32_t sum;
+			const uint32_t bz = col_flags(flags, own, sum);
+			smem_Bzp(s)[(2 * j + h + 1) * kBzStride + y + 1] = (uint16_t)bz;
+			smem_Ey(s)[col] = (uint16_t)eq_mask16(own, ny);
+			smem_Ex(s)[col] = (uint16_t)eq_mask16(own, nx);
 			anyb |= bz;
 			crossed_cols |= ((sum >> 5) ? 1u : 0u) << j;
+			ncrossed += sum >> 5;
 		}
 		uint32_t nq = 0, npl = 0;
 		if (__any_sync(full, (anyb | crossed_cols) != 0u)) {  // else: nothing drawn (e.g. an all-air chunk)
+			npl = warp_sum(ncrossed);
 			__syncwarp();
-			// B. run starts over z; crossed masks
-#pragma unroll
-			for (int j = 0; j < 8; j++) col_starts(s, tab, chunk, 2 * j + h, y);
-			if (__any_sync(full, crossed_cols != 0u)) {
-				uint32_t mine = 0;
-#pragma unroll
-				for (int j = 0; j < 8; j++) {
-					const uint32_t cz = ((crossed_cols >> j) & 1u) ? col_crossed(flags, cols[j]) : 0u;
-					s.Cz[32 * j + lane] = (uint16_t)cz;
-					mine += (uint32_t)__popc(cz);
-				}
-				npl = warp_sum(mine);
-			}
+			// B. run starts over z for the six passes
+#pragma unroll 1
+			for (int j = 0; j < 8; j++) col_starts(s, tab, raw, 2 * j + h, y);
 			__syncwarp();
 			// C. masks over the merge axes; per-group quad counts; scan in emission order
 			transpose_blocky(s, lane);
+			__syncwarp();  // Bzp is dead from here on: its bytes become rowpre
 			uint32_t run = 0;
-#pragma unroll
+#pragma unroll 1
 			for (int k = 0; k < 3; k++) {
 				const uint32_t cnt = transpose_group(s, lane + 32 * k);
 				uint32_t inc = cnt;
@@ -286,6 +310,7 @@ __global__ void __launch_bounds__(kThreads, 2) mesh_batch_kernel(const KernelPar
 
 		// E1. intransparent stream: the six face passes
 		if (nq != 0 && base_i + nq <= p.cap_i) {
+#pragma unroll 1
 			for (uint32_t t0 = 0; t0 < nq; t0 += kTileQuads) {
 				const uint32_t tn = min((uint32_t)kTileQuads, nq - t0);
 				int m = 0, c2 = 0, st = 0;
@@ -302,12 +327,24 @@ __global__ void __launch_bounds__(kThreads, 2) mesh_batch_kernel(const KernelPar
 		}
 		// E2. transparent stream: crossed plants, 4 quad slots each
 		if (npl != 0 && base_t + nts <= p.cap_t) {
-			__syncwarp();  // S is no longer read: reuse it for the plant prefix
-			uint16_t *cpre = smem_cpre(s);
+			__syncwarp();  // S is no longer read: reuse it for the crossed masks and their prefix
+			uint16_t *Cz = smem_Cz(s), *cpre = smem_cpre(s);
+#pragma unroll 1
+			for (int j = 0; j < 8; j++) {
+				uint32_t cz = 0;
+				if ((crossed_cols >> j) & 1u) {
+					const uint4 v = __ldg(reinterpret_cast<const uint4 *>(chunk) + 32 * j + lane);
+					Col cc;
+					cc.w[0] = v.x; cc.w[1] = v.y; cc.w[2] = v.z; cc.w[3] = v.w;
+					cz = col_crossed(flags, cc);
+				}
+				Cz[32 * j + lane] = (uint16_t)cz;
+			}
+			__syncwarp();
 			uint32_t cnt[8], mine = 0;
 #pragma unroll
 			for (int k = 0; k < 8; k++) {
-				cnt[k] = (uint32_t)__popc((uint32_t)s.Cz[lane * 8 + k]);
+				cnt[k] = (uint32_t)__popc((uint32_t)Cz[lane * 8 + k]);
 				mine += cnt[k];
 			}
 			uint32_t inc = mine;
@@ -323,6 +360,7 @@ __global__ void __launch_bounds__(kThreads, 2) mesh_batch_kernel(const KernelPar
 				ex += cnt[k];
 			}
 			__syncwarp();
+#pragma unroll 1
 			for (uint32_t t0 = 0; t0 < nts; t0 += kTileQuads) {
 				const uint32_t tn = min((uint32_t)kTileQuads, nts - t0);
 				int cell = 0;

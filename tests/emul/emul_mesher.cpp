@@ -64,8 +64,11 @@ extern "C" int emul_mesh_batch(const uint8_t *chunks, const int64_t *offs, uint3
 		const uint8_t *chunk = chunks + (size_t)c * 4096;
 		long long o3[3] = {offs[3 * c], offs[3 * c + 1], offs[3 * c + 2]};
 		for (int lane = 0; lane < kLanes; lane++) phase_pos(s, lane, o3);
+		for (int lane = 0; lane < kLanes; lane++) zero_border(s, lane);
+		memcpy(smem_raw(s), chunk, 4096);  // the bulk async copy of the kernel
+		const uint8_t *raw = smem_raw(s);
 		// A
-		uint32_t anyb = 0;
+		uint32_t anyb = 0, npl = 0;
 		uint32_t crossed_cols[kLanes] = {0};
 		for (int j = 0; j < 8; j++)
 			for (int lane = 0; lane < kLanes; lane++) {
@@ -78,28 +81,21 @@ extern "C" int emul_mesh_batch(const uint8_t *chunks, const int64_t *offs, uint3
 				else memset(nx.w, 0, sizeof(nx.w));
 				uint32_t sum;
 				const uint32_t bz = col_flags(flags, own, sum);
-				s.Bzp[(x + 1) * kBzStride + y + 1] = (uint16_t)bz;
+				smem_Bzp(s)[(x + 1) * kBzStride + y + 1] = (uint16_t)bz;
 				smem_Ey(s)[32 * j + lane] = (uint16_t)eq_mask16(own, ny);
 				smem_Ex(s)[32 * j + lane] = (uint16_t)eq_mask16(own, nx);
 				anyb |= bz;
 				crossed_cols[lane] |= ((sum >> 5) ? 1u : 0u) << j;
+				npl += sum >> 5;
 			}
 		uint32_t anyc = 0;
 		for (int lane = 0; lane < kLanes; lane++) anyc |= crossed_cols[lane];
-		uint32_t nq = 0, npl = 0;
+		uint32_t nq = 0;
+		if (!(anyb | anyc)) npl = 0;
 		if (anyb | anyc) {
 			// B
 			for (int j = 0; j < 8; j++)
-				for (int lane = 0; lane < kLanes; lane++) col_starts(s, tab, chunk, 2 * j + (lane >> 4), lane & 15);
-			if (anyc) {
-				for (int j = 0; j < 8; j++)
-					for (int lane = 0; lane < kLanes; lane++) {
-						const int h = lane >> 4, y = lane & 15, x = 2 * j + h;
-						const uint32_t cz = ((crossed_cols[lane] >> j) & 1u) ? col_crossed(flags, load_col(chunk, x, y)) : 0u;
-						s.Cz[32 * j + lane] = (uint16_t)cz;
-						npl += (uint32_t)popc32(cz);
-					}
-			}
+				for (int lane = 0; lane < kLanes; lane++) col_starts(s, tab, raw, 2 * j + (lane >> 4), lane & 15);
 			// C
 			for (int lane = 0; lane < kLanes; lane++) transpose_blocky(s, lane);
 			uint32_t cnt[kGroups];
@@ -132,11 +128,17 @@ extern "C" int emul_mesh_batch(const uint8_t *chunks, const int64_t *offs, uint3
 		}
 		// E2
 		if (npl && base_t + nts <= cap_t) {
-			uint16_t *cpre = smem_cpre(s);
+			uint16_t *Cz = smem_Cz(s), *cpre = smem_cpre(s);
+			for (int j = 0; j < 8; j++)
+				for (int lane = 0; lane < kLanes; lane++) {
+					const int h = lane >> 4, y = lane & 15, x = 2 * j + h;
+					Cz[32 * j + lane] =
+					    (uint16_t)(((crossed_cols[lane] >> j) & 1u) ? col_crossed(flags, load_col(chunk, x, y)) : 0u);
+				}
 			uint32_t ex = 0;
 			for (int col = 0; col < 256; col++) {
 				cpre[col] = (uint16_t)ex;
-				ex += (uint32_t)popc32(s.Cz[col]);
+				ex += (uint32_t)popc32(Cz[col]);
 			}
 			for (uint32_t t0 = 0; t0 < nts; t0 += kTileQuads) {
 				const uint32_t tn = std::min<uint32_t>(kTileQuads, nts - t0);
