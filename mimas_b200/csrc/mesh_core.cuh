@@ -1,8 +1,8 @@
-// mesh_core.cuh -- per-lane data-path logic of the B200 chunk mesher (kernel v2: one warp per chunk).
+// mesh_core.cuh -- per-lane data-path logic of the B200 chunk mesher (v3: analyse + expand).
 //
 // Everything in this header is written per *logical lane* against an explicit per-warp
 // shared-memory struct; data crosses lanes only through that struct (or through values the
-// caller hands in).  The CUDA kernel (mesh_kernel.cuh) calls these functions with
+// caller hands in).  The CUDA kernels (mesh_kernel.cuh) call these functions with
 // lane = threadIdx.x & 31, real shuffles and __syncwarp() between the phases; tests/emul/
 // compiles the very same functions with g++ and runs the 32 lanes in a loop, so the
 // bit-level logic can be checked on a machine without a GPU.  (That emulation is test
@@ -11,15 +11,20 @@
 // What is computed: mimas-meshgen/lib.rs:231-446 `mesh_for_chunk`
 //   * six run-merging face passes (lib.rs:316-410) -> `intransparent`
 //   * crossed-plant pass (lib.rs:412-440)          -> `transparent`
-// re-formulated for one warp as
+// re-formulated as two kernels.
+// ANALYSE (one warp per chunk):
 //   A. lane <-> column (x, y): 16 block ids along z (one 16-byte load) -> 16-bit "blocky"
 //      mask over z, plus SWAR id-equality masks against the (x, y-1) and (x-1, y) columns
 //   B. visibility and run-start masks of all six passes as bit operations on z-masks
-//   C. 16x16 bit-matrix transposes (in registers) turn the z-masks into masks over the
-//      merge axis, one 16-bit word per row (pass, c1, c2) in the reference's emission order
-//   D. popc + warp scan -> quad counts and offsets; chunk base from the batch-wide prefix
-//   E. lane <-> quad: find the quad's row and start bit, measure the run, expand 216 bytes
-//      into a staging tile that a bulk async copy (TMA) stores to the packed vertex stream.
+//   C. popc of the start masks -> quads per (pass, c1) group, warp scan -> group offsets
+//   D. 16x16 bit-matrix transposes (in registers) turn the z-masks into masks over the
+//      merge axis, one 16-bit word per row (pass, c1, c2) in the reference's emission order;
+//      every run start becomes one 32-bit quad descriptor (block id, start, row, pass, length)
+//      in the chunk's descriptor slot; crossed plants become plant descriptors
+// EXPAND (one warp per tile of 32 quads of the packed stream):
+//   E. exclusive scan of the per-chunk counts (shared memory, redundantly per CTA), quad ->
+//      chunk by binary search, descriptor -> 216 bytes into a staging tile that a bulk async
+//      copy (TMA) stores to the packed vertex stream.
 #pragma once
 #include <stdint.h>
 
@@ -51,8 +56,12 @@ constexpr int kQuadWords = 54;
 constexpr int kPlantQuads = 4;         // 2 x rpush_face_bidi! = 24 vertices = 4 quad slots
 constexpr int kStageBytes = kTileQuads * kQuadBytes;  // 6912, a multiple of 16
 constexpr int kBzStride = 18;          // Bzp is a 18 x 18 array: the 16 x 16 columns plus a zero border
+// Descriptor slots of one chunk (32-bit words): the most quads the six passes can emit
+// (3-D checkerboard of two textures: 6 x 256 rows x 8... bounded by 6 x 4096 / 2) and the most plants.
+constexpr uint32_t kDescStrideI = 12288;
+constexpr uint32_t kDescStrideT = 4096;
 
-// Block-table entry as the kernel sees it (built from mm_block_entry on the host):
+// Block-table entry as the kernels see it (built from mm_block_entry on the host):
 //   x = id_sides | id_top << 16   (for a crossed block: x = crossed texture id)
 //   y = id_bottom | kind << 16    (kind: 0 none, 1 blocky, 2 crossed)
 struct TabEntry {
@@ -67,37 +76,31 @@ struct Col {
 	uint32_t w[4];
 };
 
-// Shared memory of one warp.  Plain struct so that host emulation can allocate it.
-struct alignas(16) WarpSmem {
-	// staging tile: +16 so the tile can be shifted by 8 B to match the 16-B phase of its
-	// destination in the vertex stream (quads are only 8-B aligned: 216 = 8 * 27).
-	// During the analysis phases the same bytes hold the id-equality masks (Ey, Ex: 2 x 512 B)
-	// and the chunk itself (raw, 4096 B at offset 1024, filled by one bulk async copy).
-	alignas(16) unsigned char stage[kStageBytes + 16];
-	// run-start masks.  Phase B writes them over z per column: passes 1,3,4,6 (p = 0,2,3,5) at
-	// [p][x*16 + y], passes 2,5 (p = 1,4) at [p][y*16 + x]; phase C transposes every 16-entry
-	// block in place into [p][c1*16 + c2] = mask over the merge axis of row (c1, c2).
-	// After the intransparent stream is written, S[0..511] is reused for the plants (Cz, cpre).
-	alignas(16) uint16_t S[kPasses * 256 + 16];
+// Shared memory of one analysing warp.  Plain struct so that host emulation can allocate it.
+struct alignas(128) WarpSmem {
+	// the chunk itself, filled by one bulk async copy (TMA)
+	alignas(128) unsigned char raw[4096];
+	// id-equality masks of phase A (Ey: vs column (x, y-1), Ex: vs (x-1, y)), [x*16 + y];
+	// dead after phase B: the same bytes then hold Cz, the crossed mask over z per column
+	alignas(16) uint16_t Ey[256];
+	alignas(16) uint16_t Ex[256];
+	// run-start masks over z per column: passes 1,3,4,6 (p = 0,2,3,5) at [p][x*16 + y],
+	// passes 2,5 (p = 1,4) at [p][y*16 + x]; every 16-entry block [p][c1*16 ..] is one
+	// (pass, c1) group whose 16 x 16 bit transpose gives the masks over the merge axis
+	alignas(16) uint16_t S[kPasses * 256];
 	alignas(16) uint16_t By[256];              // blocky mask over y for row (x, z): [x*16 + z]
 	alignas(16) uint16_t Bx[256];              // blocky mask over x for row (y, z): [y*16 + z]
-	alignas(16) uint16_t gpre[128];            // exclusive quad prefix per group; [96..127] = 0xffff
-	// phases A-C: Bzp = blocky mask over z per column, 18 x 18 with a zero border;
-	// from phase C on: rowpre[m*16 + c2] = run starts of group m before row c2 (<= 240)
-	alignas(16) unsigned char rowpre[kGroups * 16];
-	float pos[3][17];                          // (offs + c) as f32 for c in 0..=16, per axis
+	alignas(16) uint16_t gpre[128];            // exclusive quad prefix per group
+	alignas(16) uint16_t Bzp[kBzStride * kBzStride + 4];  // blocky mask over z per column, zero border
 	alignas(8) unsigned long long mbar;        // mbarrier of the chunk load (device only)
 };
-static_assert(kBzStride * kBzStride * 2 <= kGroups * 16, "Bzp aliases rowpre");
-static_assert(1024 + 4096 <= kStageBytes, "Ey, Ex and the raw chunk alias the staging tile");
 
-MM_HD uint16_t *smem_Ey(WarpSmem &s) { return reinterpret_cast<uint16_t *>(s.stage); }
-MM_HD uint16_t *smem_Ex(WarpSmem &s) { return reinterpret_cast<uint16_t *>(s.stage) + 256; }
-MM_HD unsigned char *smem_raw(WarpSmem &s) { return s.stage + 1024; }
-MM_HD uint16_t *smem_Bzp(WarpSmem &s) { return reinterpret_cast<uint16_t *>(s.rowpre); }
-MM_HD const uint16_t *smem_Bzp(const WarpSmem &s) { return reinterpret_cast<const uint16_t *>(s.rowpre); }
-MM_HD uint16_t *smem_Cz(WarpSmem &s) { return s.S; }           // crossed mask over z per column (plants phase)
-MM_HD uint16_t *smem_cpre(WarpSmem &s) { return s.S + 256; }   // plants before column col
+MM_HD uint16_t *smem_Ey(WarpSmem &s) { return s.Ey; }
+MM_HD uint16_t *smem_Ex(WarpSmem &s) { return s.Ex; }
+MM_HD unsigned char *smem_raw(WarpSmem &s) { return s.raw; }
+MM_HD uint16_t *smem_Bzp(WarpSmem &s) { return s.Bzp; }
+MM_HD const uint16_t *smem_Bzp(const WarpSmem &s) { return s.Bzp; }
+MM_HD uint16_t *smem_Cz(WarpSmem &s) { return s.Ey; }           // crossed mask over z per column (plants phase)
 
 MM_HD int popc32(uint32_t v) {
 #if defined(__CUDA_ARCH__)
@@ -166,12 +169,9 @@ MM_HD uint32_t f2u(float f) {
 MM_HD float zsig(float v) { return v > 0.0f ? 1.0f : (v < 0.0f ? -1.0f : 0.0f); }
 
 // ---- warp set-up ---------------------------------------------------------------------
-// Once per warp: the sentinels of the group prefix.
-MM_HD void init_warp_smem(WarpSmem &s, int lane) { s.gpre[kGroups + lane] = 0xffffu; }
-
-// Once per chunk: the zero border of Bzp (a neighbour outside the chunk never blocks,
-// lib.rs:277-280); the interior is written by phase A.
-MM_HD void zero_border(WarpSmem &s, int lane) {
+// Once per warp: the zero border of Bzp (a neighbour outside the chunk never blocks,
+// lib.rs:277-280); the interior is rewritten by phase A for every chunk.
+MM_HD void init_warp_smem(WarpSmem &s, int lane) {
 	uint16_t *B = smem_Bzp(s);
 	if (lane < kBzStride) {
 		B[lane] = 0;
@@ -180,15 +180,6 @@ MM_HD void zero_border(WarpSmem &s, int lane) {
 	if (lane < 16) {
 		B[(lane + 1) * kBzStride] = 0;
 		B[(lane + 1) * kBzStride + kBzStride - 1] = 0;
-	}
-}
-
-// pos[a][c] = (offs[a] + c) as f32 for c in 0..=16: every `pos.x as f32` the reference
-// evaluates (lib.rs:323-325 etc.), including the sentinel cell 16 (lib.rs:309).
-MM_HD void phase_pos(WarpSmem &s, int lane, const long long *offs3) {
-	if (lane < 17) {
-#pragma unroll
-		for (int a = 0; a < 3; a++) s.pos[a][lane] = i64_to_f32(offs3[a] + (long long)lane);
 	}
 }
 
@@ -339,36 +330,6 @@ MM_HD void transpose16(uint32_t w[8]) {
 	}
 }
 
-// Transposes the 16-entry block at S[m*16 ..] in place, writes the per-row prefix of the
-// group (rowpre) and returns the number of run starts (= quads) in group m = pass*16 + c1.
-// Must not run before every lane has finished transpose_blocky (rowpre aliases Bzp).
-MM_HD uint32_t transpose_group(WarpSmem &s, int m) {
-	uint32_t *p = reinterpret_cast<uint32_t *>(s.S + m * 16);
-	uint32_t w[8];
-	uint32_t any = 0;
-#pragma unroll
-	for (int k = 0; k < 8; k++) {
-		w[k] = p[k];
-		any |= w[k];
-	}
-	if (any == 0) return 0;
-	transpose16(w);
-	uint32_t run = 0;
-	uint32_t pre[4];
-#pragma unroll
-	for (int k = 0; k < 8; k++) {
-		p[k] = w[k];
-		const uint32_t c0 = (uint32_t)popc32(w[k] & 0xffffu), c1 = (uint32_t)popc32(w[k] >> 16);
-		const uint32_t e = run | ((run + c0) << 8);  // exclusive prefixes of rows 2k, 2k+1 (<= 240)
-		if (k & 1) pre[k >> 1] |= e << 16;
-		else pre[k >> 1] = e;
-		run += c0 + c1;
-	}
-	uint32_t *rp = reinterpret_cast<uint32_t *>(s.rowpre + m * 16);
-#pragma unroll
-	for (int k = 0; k < 4; k++) rp[k] = pre[k];
-	return run;
-}
 
 // Blocky masks over the merge axes, from the z-masks: job 0..15 -> By rows of x = job
 // (bits over y), job 16..31 -> Bx rows of y = job - 16 (bits over x).
@@ -390,28 +351,93 @@ MM_HD void transpose_blocky(WarpSmem &s, int job) {
 	for (int k = 0; k < 8; k++) p[k] = w[k];
 }
 
-// ---- phase E: quad lookup ---------------------------------------------------------------
-// Quad q (0 <= q < nq, emission order) -> group m = pass*16 + c1, row c2, start bit st.
-// gpre[m] = number of quads before group m; gpre[96..127] = 0xffff.
-MM_HD void find_quad(const WarpSmem &s, uint32_t q, int &m, int &c2, int &st) {
-	int lo = 0;
+// Number of run starts (= quads) of group m = pass*16 + c1: a transpose moves bits, it does
+// not change how many there are, so the z-masks can be counted as they stand.
+MM_HD uint32_t count_group(const WarpSmem &s, int m) {
+	const uint32_t *p = reinterpret_cast<const uint32_t *>(s.S + m * 16);
+	uint32_t c = 0;
 #pragma unroll
-	for (int step = 64; step >= 1; step >>= 1)
-		if ((uint32_t)s.gpre[lo + step] <= q) lo += step;  // largest m with gpre[m] <= q
-	m = lo;
-	const uint32_t r = q - s.gpre[lo];
-	const unsigned char *rp = s.rowpre + lo * 16;
-	int row = 0;
-#pragma unroll
-	for (int step = 8; step >= 1; step >>= 1)
-		if ((uint32_t)rp[row + step] <= r) row += step;    // largest row with rowpre <= r: it holds quad r
-	c2 = row;
-	uint32_t mask = s.S[lo * 16 + row];
-	for (uint32_t i = r - rp[row]; i > 0; i--) mask &= mask - 1u;  // drop the lower run starts
-	st = ffs32(mask) - 1;
+	for (int k = 0; k < 8; k++) c += (uint32_t)popc32(p[k]);
+	return c;
 }
 
-// ---- quad expansion -----------------------------------------------------------------
+// ---- phase D: quad descriptors --------------------------------------------------------
+// One 32-bit word per quad of the six face passes:
+//   bits 0-7 block id of the run's first cell | 8-11 start (inner coordinate) | 12-15 c2 |
+//   16-19 c1 | 20-22 pass (0..5) | 23-27 run length (1..16)
+MM_HD uint32_t pack_face_desc(uint32_t id, int st, int c2, int m, int len) {
+	return id | ((uint32_t)st << 8) | ((uint32_t)c2 << 12) | ((uint32_t)m << 16) | ((uint32_t)len << 23);
+}
+
+// Writes the descriptors of group m in emission order (rows c2 ascending, runs ascending,
+// lib.rs:294-313) to dst[0..count_group(m)).  The group's 16 z-masks are transposed in
+// registers into masks over the merge axis; a run (lib.rs:244-271) ends where the next one
+// starts or where the face stops being visible.
+MM_HD void emit_group_descs(const WarpSmem &s, int m, uint32_t *dst) {
+	const uint32_t *sp = reinterpret_cast<const uint32_t *>(s.S + m * 16);
+	uint32_t w[8];
+#pragma unroll
+	for (int k = 0; k < 8; k++) w[k] = sp[k];
+	transpose16(w);
+	const int p = m >> 4, c1 = m & 15;
+	const bool xin = (p == 1 || p == 4);
+	// visibility over the merge axis of row (c1, c2) = blocky & ~blocky of the neighbour row
+	// in the pass direction (SURVEY.md 8a pass table); `has_nb` bit c2: that row is inside the chunk
+	const uint16_t *Bm = (xin ? s.Bx : s.By) + c1 * 16;
+	int delta;
+	uint32_t has_nb;
+	if (p == 0) { delta = -1; has_nb = 0xfffeu; }                        // [0,0,-1]
+	else if (p == 3) { delta = 1; has_nb = 0x7fffu; }                    // [0,0,1]
+	else if (p == 1 || p == 2) { delta = -16; has_nb = c1 > 0 ? 0xffffu : 0u; }   // [0,-1,0] / [-1,0,0]
+	else { delta = 16; has_nb = c1 < 15 ? 0xffffu : 0u; }                // [0,1,0] / [1,0,0]
+	const int cell_row = xin ? c1 * 16 : c1 * 256;   // + st*256 (x-inner) or st*16 (y-inner) + c2
+	const int cell_shift = xin ? 8 : 4;
+#pragma unroll
+	for (int k = 0; k < 8; k++) {
+#pragma unroll
+		for (int hf = 0; hf < 2; hf++) {
+			const int c2 = 2 * k + hf;
+			uint32_t rest = hf ? (w[k] >> 16) : (w[k] & 0xffffu);
+			if (rest == 0) continue;
+			const uint32_t b = Bm[c2];
+			const uint32_t nb = ((has_nb >> c2) & 1u) ? (uint32_t)Bm[c2 + delta] : 0u;
+			const uint32_t T = ((rest | ~(b & ~nb)) & 0xffffu) | 0x10000u;  // run boundaries: start | not visible | end of row
+			do {
+				const int st = ffs32(rest) - 1;
+				rest &= rest - 1u;
+				const int len = ffs32(T >> (st + 1));
+				const uint32_t id = s.raw[cell_row + (st << cell_shift) + c2];
+				*dst++ = pack_face_desc(id, st, c2, m, len);
+			} while (rest);
+		}
+	}
+}
+
+// Crossed plants (lib.rs:412-440), x outer, y, z inner = linear cell order.  Cz[col] = crossed
+// mask over z of column col = x*16 + y; this lane covers columns lane*8 .. lane*8+7.
+MM_HD uint32_t count_plants8(const WarpSmem &s, int lane) {
+	const uint32_t *p = reinterpret_cast<const uint32_t *>(s.Ey + lane * 8);
+	uint32_t c = 0;
+#pragma unroll
+	for (int k = 0; k < 4; k++) c += (uint32_t)popc32(p[k]);
+	return c;
+}
+// Plant descriptor: bits 0-7 block id | 8-19 cell index.
+MM_HD void emit_plant_descs(const WarpSmem &s, int lane, uint32_t *dst) {
+#pragma unroll 1
+	for (int k = 0; k < 8; k++) {
+		const int col = lane * 8 + k;
+		uint32_t mask = s.Ey[col];
+		while (mask) {
+			const int z = ffs32(mask) - 1;
+			mask &= mask - 1u;
+			const int cell = col * 16 + z;
+			*dst++ = (uint32_t)s.raw[cell] | ((uint32_t)cell << 8);
+		}
+	}
+}
+
+// ---- phase E: quad expansion -------------------------------------------------------------
 // The argument list of rpush_face! / rpush_face_rev! / rpush_face_bidi!
 // (lib.rs:139-181): base (x,y,z), position deltas (xsd,ysd,yd,zd), texture deltas
 // summed as the macros sum them (us = xstd + ystd, vt = ytd + ztd), direction, tex.
@@ -466,52 +492,41 @@ MM_HD void write_quad(unsigned char *dst, const QuadArgs &a) {
 	}
 }
 
-// One quad of the six face passes (pass table: SURVEY.md §8a A5) from its row and start
-// bit.  `chunk` = the 4096 block ids (global memory), `tab` = texture table.
-MM_HD void expand_face_quad(const WarpSmem &s, const TabEntry *tab, const uint8_t *chunk, int m, int c2, int st,
+// One quad of the six face passes (pass table: SURVEY.md 8a A5) from its descriptor and the
+// chunk origin `offs`.  Every coordinate is `(offs + c) as f32` exactly as the reference
+// evaluates it (lib.rs:323-325; the run end is the sentinel/next cell, lib.rs:249,309).
+MM_HD void expand_face_desc(const TabEntry *tab, long long ox, long long oy, long long oz, uint32_t d,
                             unsigned char *dst) {
-	const int p = m >> 4, c1 = m & 15;
+	const uint32_t id = d & 0xffu;
+	const int st = (int)((d >> 8) & 15u), c2 = (int)((d >> 12) & 15u), c1 = (int)((d >> 16) & 15u);
+	const int p = (int)((d >> 20) & 7u), len = (int)((d >> 23) & 31u);
 	const bool xin = (p == 1 || p == 4);
-	// visibility over the merge axis of this row, to find where the run ends
-	const uint16_t *Bm = xin ? s.Bx : s.By;
-	const uint32_t b = Bm[c1 * 16 + c2];
-	uint32_t nb;
-	if (p == 0) nb = c2 > 0 ? Bm[c1 * 16 + c2 - 1] : 0u;          // [0,0,-1]
-	else if (p == 3) nb = c2 < 15 ? Bm[c1 * 16 + c2 + 1] : 0u;    // [0,0,1]
-	else if (p == 2 || p == 1) nb = c1 > 0 ? Bm[(c1 - 1) * 16 + c2] : 0u;   // [-1,0,0] / [0,-1,0]
-	else nb = c1 < 15 ? Bm[(c1 + 1) * 16 + c2] : 0u;              // [1,0,0] / [0,1,0]
-	const uint32_t T = ((uint32_t)s.S[m * 16 + c2] | ~(b & ~nb)) & 0xffffu;  // run boundary: start | not visible
-	const uint32_t above = T >> (st + 1);
-	const int len = above ? ffs32(above) : 16 - st;
-	const int cell = xin ? (st * 256 + c1 * 16 + c2) : (c1 * 256 + st * 16 + c2);
-	const TabEntry e = tab[chunk[cell]];
+	const TabEntry e = tab[id];
+	const long long oin = xin ? ox : oy, oout = xin ? oy : ox;
+	const float last_v = i64_to_f32(oin + st);
+	const float vlen = fsub(i64_to_f32(oin + st + len), last_v);  // vlen = v - last_v, lib.rs:249,256
+	const float o1 = i64_to_f32(oout + c1), z = i64_to_f32(oz + c2);
 	const float siz = 1.0f;  // lib.rs:314
 	QuadArgs a;
 	if (xin) {  // x-inner: row (y, z); run along x
-		const float last_x = s.pos[0][st];
-		const float xlen = fsub(s.pos[0][st + len], last_x);  // vlen = v - last_v, lib.rs:249,256
-		const float y = s.pos[1][c1], z = s.pos[2][c2];
-		a.x = last_x; a.z = z;
-		a.xsd = xlen; a.ysd = 0.0f; a.yd = 0.0f; a.zd = siz;
+		a.x = last_v; a.z = z;
+		a.xsd = vlen; a.ysd = 0.0f; a.yd = 0.0f; a.zd = siz;
 		a.tex = e.x & 0xffffu;                               // id_sides
-		if (p == 1) { a.y = y; a.rev = true; }               // lib.rs:342
-		else { a.y = fadd(y, siz); a.rev = false; }          // lib.rs:390
+		if (p == 1) { a.y = o1; a.rev = true; }              // lib.rs:342
+		else { a.y = fadd(o1, siz); a.rev = false; }         // lib.rs:390
 	} else {                 // y-inner: row (x, z); run along y
-		const float last_y = s.pos[1][st];
-		const float ylen = fsub(s.pos[1][st + len], last_y);
-		const float x = s.pos[0][c1], z = s.pos[2][c2];
-		a.y = last_y;
+		a.y = last_v;
 		if (p == 0) {        // lib.rs:326  (x, last_y, z), (siz, 0, ylen, 0), id_bottom
-			a.x = x; a.z = z; a.xsd = siz; a.ysd = 0.0f; a.yd = ylen; a.zd = 0.0f;
+			a.x = o1; a.z = z; a.xsd = siz; a.ysd = 0.0f; a.yd = vlen; a.zd = 0.0f;
 			a.tex = e.y & 0xffffu; a.rev = false;
 		} else if (p == 2) { // lib.rs:358  (x, last_y, z), (0, ylen, 0, siz), id_sides
-			a.x = x; a.z = z; a.xsd = 0.0f; a.ysd = ylen; a.yd = 0.0f; a.zd = siz;
+			a.x = o1; a.z = z; a.xsd = 0.0f; a.ysd = vlen; a.yd = 0.0f; a.zd = siz;
 			a.tex = e.x & 0xffffu; a.rev = false;
 		} else if (p == 3) { // lib.rs:374  (x, last_y, z + siz), (siz, 0, ylen, 0), id_top, rev
-			a.x = x; a.z = fadd(z, siz); a.xsd = siz; a.ysd = 0.0f; a.yd = ylen; a.zd = 0.0f;
+			a.x = o1; a.z = fadd(z, siz); a.xsd = siz; a.ysd = 0.0f; a.yd = vlen; a.zd = 0.0f;
 			a.tex = e.x >> 16; a.rev = true;
 		} else {             // lib.rs:406  (x + siz, last_y, z), (0, ylen, 0, siz), id_sides, rev
-			a.x = fadd(x, siz); a.z = z; a.xsd = 0.0f; a.ysd = ylen; a.yd = 0.0f; a.zd = siz;
+			a.x = fadd(o1, siz); a.z = z; a.xsd = 0.0f; a.ysd = vlen; a.yd = 0.0f; a.zd = siz;
 			a.tex = e.x & 0xffffu; a.rev = true;
 		}
 	}
@@ -520,32 +535,19 @@ MM_HD void expand_face_quad(const WarpSmem &s, const TabEntry *tab, const uint8_
 	write_quad(dst, a);
 }
 
-// ---- crossed plants (lib.rs:412-440) ----------------------------------------------------
-// Plant number pl (x outer, y, z inner = linear cell order) -> cell index.
-// cpre[col] = plants before column col = x*16 + y; cpre[256] = 0xffff.
-MM_HD int find_plant(WarpSmem &s, uint32_t pl) {
-	const uint16_t *cpre = smem_cpre(s);
-	int lo = 0;
-#pragma unroll
-	for (int step = 128; step >= 1; step >>= 1)
-		if ((uint32_t)cpre[lo + step] <= pl) lo += step;
-	uint32_t mask = smem_Cz(s)[lo];
-	for (uint32_t i = pl - cpre[lo]; i > 0; i--) mask &= mask - 1u;
-	return lo * 16 + ffs32(mask) - 1;
-}
-
 // Quad slot `part` (0..3) of a crossed plant: lib.rs:426-437.  Parts 0,1 are the
 // forward and reverse halves of the first rpush_face_bidi!, parts 2,3 of the second.
-MM_HD void expand_plant_quad(const WarpSmem &s, const TabEntry *tab, const uint8_t *chunk, int cell, int part,
+MM_HD void expand_plant_desc(const TabEntry *tab, long long ox, long long oy, long long oz, uint32_t d, int part,
                              unsigned char *dst) {
-	const TabEntry e = tab[chunk[cell]];
+	const TabEntry e = tab[d & 0xffu];
+	const int cell = (int)((d >> 8) & 0xfffu);
 	const int cx = cell >> 8, cy = (cell >> 4) & 15, cz = cell & 15;
 	const float siz = 1.0f;
 	const float sq = siz * 1.41421356237309504880168872420969808f * 0.5f;  // lib.rs:428 (exact: *1, *0.5)
 	const float sqh = sq * 0.5f;                                           // lib.rs:429
-	const float x = fadd(s.pos[0][cx], 0.5f * siz);                        // lib.rs:431
-	const float y = fadd(s.pos[1][cy], 0.5f * siz);
-	const float z = s.pos[2][cz];
+	const float x = fadd(i64_to_f32(ox + cx), 0.5f * siz);                 // lib.rs:431
+	const float y = fadd(i64_to_f32(oy + cy), 0.5f * siz);
+	const float z = i64_to_f32(oz + cz);
 	const float tsiz = siz * 0.5f;                                         // lib.rs:433
 	const float h = siz * 0.95f;
 	QuadArgs a;

@@ -1,85 +1,66 @@
-// mesh_kernel.cuh -- the sm_100a batch mesher kernel, v2 (device only).
+// mesh_kernel.cuh -- the sm_100a batch mesher, v3: two kernels per batch (device only).
 //
-// Persistent CTAs of 8 warps; every WARP is an independent chunk worker that draws chunk
-// tickets in order and runs the phases of mesh_core.cuh with its 32 lanes:
-//   A. 8 x (one 16-byte streaming load per lane) = the 4 KiB chunk; blocky masks, id-equality
-//      masks (neighbour columns arrive by warp shuffle)
+// analyse_kernel: persistent CTAs of 8 warps; every WARP is an independent chunk worker that
+// draws chunk tickets and runs phases A-D of mesh_core.cuh with its 32 lanes:
+//   A. one bulk async copy (TMA) brings the 4 KiB chunk into shared memory; blocky masks and
+//      id-equality masks per column
 //   B. visibility / run starts of the six passes as bit operations on 16-bit z-masks
-//   C. in-register 16x16 bit transposes -> row masks in emission order, popc -> counts,
-//      warp shuffle scan -> quad offsets inside the chunk
-//   D. chunk base in the packed streams: every chunk publishes its counts in a status word;
-//      groups of 32 chunks and of 1024 chunks are summed by whichever warp arrives last
-//      (one atomic per chunk on a per-group counter), so a chunk's exclusive prefix is
-//      3 coalesced 32-lane loads (chunks of its group, groups of its super-group, super-groups)
-//      -- single pass, tightly packed, chunk order, no serial chain between chunks
-//   E. lane <-> quad: 216 B per lane into the warp's staging tile, then one cp.async.bulk
-//      (TMA) shared -> global store per tile, overlapped with the search for the next tile
-// No CTA-wide barrier after set-up; no tensor cores: the path is a scan/compaction bound by
-// the vertex-stream writes.
+//   C. popc -> quads per (pass, c1) group, warp shuffle scan -> offsets inside the chunk
+//   D. in-register 16x16 bit transposes -> rows in emission order; one 32-bit descriptor per
+//      quad / per plant into the chunk's descriptor slot, the two counts into the count arrays
+// The analysis never waits for another chunk: no look-back, no spinning.
+//
+// expand_kernel: one persistent CTA of 16 warps per SM.  Every CTA scans the per-chunk counts
+// into shared memory (exclusive prefix = where each chunk starts in the packed streams, chunk
+// order, tightly packed); then each warp takes tiles of 32 consecutive quads of the packed
+// stream: quad -> chunk by binary search in shared memory, descriptor -> 216 B per lane into the
+// warp's staging tile, one cp.async.bulk (TMA) shared -> global store per tile.  Tiles are
+// uniform, so the write-bound part of the job is balanced to one tile per warp.
+// No tensor cores: the path is a scan/compaction bound by the vertex-stream writes.
 #pragma once
 #include <cuda_runtime.h>
 #include "mesh_core.cuh"
 
 namespace mm {
 
-constexpr int kWarpsPerCta = 8;
+constexpr int kWarpsPerCta = 8;                  // analyse_kernel
 constexpr int kThreads = kWarpsPerCta * 32;
-constexpr uint32_t kMaxLaunchChunks = 32768;  // 32 super-groups of 32 groups of 32 chunks
-constexpr size_t kCtaTableBytes = 2048 + 256;
-constexpr size_t kCtaSmemBytes = kCtaTableBytes + kWarpsPerCta * sizeof(WarpSmem);
+constexpr int kExpandWarps = 16;                 // expand_kernel
+constexpr int kExpandThreads = kExpandWarps * 32;
+constexpr uint32_t kMaxLaunchChunks = 8192;      // the prefix of one launch lives in shared memory
+constexpr int kScanPerThread = kMaxLaunchChunks / kExpandThreads;  // 16
+constexpr size_t kAnalyseTableBytes = 2048 + 256;  // block table + flag bytes
+constexpr size_t kAnalyseSmemBytes = kAnalyseTableBytes + kWarpsPerCta * sizeof(WarpSmem);
+// expand: table | prefix_i[8192+4] | prefix_t[8192+4] | warp totals | stage tiles
+constexpr size_t kExpandPrefixWords = kMaxLaunchChunks + 4;
+constexpr size_t kExpandSmemBytes = 2048 + 2 * 4 * kExpandPrefixWords + 256 + kExpandWarps * (size_t)(kStageBytes + 16);
 
-struct KernelParams {
+struct AnalyseParams {
 	const unsigned char *chunks;  // n * 4096
-	const long long *offs;        // n * 3
 	uint32_t n;                   // <= kMaxLaunchChunks
-	uint32_t epoch;               // 1..16383, tags the status words of this launch
 	const TabEntry *table;        // 256 entries
 	const unsigned char *flags;   // 256 flag bytes (kFlagBlocky / kFlagCrossed)
+	uint32_t *desc_i;             // n * kDescStrideI descriptor words
+	uint32_t *desc_t;             // n * kDescStrideT
+	uint32_t *cnt_i;              // quads per chunk
+	uint32_t *cnt_t;              // transparent quad slots per chunk (4 per plant)
+	u64 *ticket;                  // monotonically increasing across launches
+	u64 ticket_base;              // its value at launch
+};
+
+struct ExpandParams {
+	const long long *offs;        // n * 3
+	uint32_t n;
+	const TabEntry *table;
+	const uint32_t *desc_i, *desc_t, *cnt_i, *cnt_t;
 	unsigned char *out_i;         // intransparent vertex stream
 	unsigned char *out_t;         // transparent vertex stream
 	u64 cap_i, cap_t;             // arena capacities in quads (216 B units)
 	Range *ranges_i, *ranges_t;   // n entries each
-	u64 *st_chunk;                // status words: per chunk, per group of 32, per super-group of 1024
-	u64 *st_group;
-	u64 *st_super;
-	uint32_t *cnt_group;          // arrival counters (zero between launches)
-	uint32_t *cnt_super;
-	u64 *ticket;                  // monotonically increasing across launches
-	u64 ticket_base;              // its value at launch
 	const u64 *carry_in;          // quads already in the streams (earlier launches of the batch) or NULL
 	u64 *totals;                  // [0] quads in out_i, [1] quad slots in out_t after this launch
 };
 
-// status word: epoch(14) | t quad slots(25) | i quads(25)
-constexpr u64 kCntMask = (1ull << 25) - 1;
-__device__ __forceinline__ u64 pack_status(uint32_t epoch, uint32_t i, uint32_t t) {
-	return ((u64)epoch << 50) | ((u64)t << 25) | (u64)i;
-}
-__device__ __forceinline__ u64 ld_status(const u64 *p) {
-	u64 v;
-	asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-	return v;
-}
-__device__ __forceinline__ void st_status(u64 *p, u64 v) {
-	asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-// Arrival counter of a group.  Relaxed on purpose: the counter only elects the warp that sums the
-// group; every status word it then reads carries its own epoch tag and is waited for individually.
-__device__ __forceinline__ uint32_t arrive(uint32_t *p) {
-	uint32_t old;
-	asm volatile("atom.relaxed.gpu.global.add.u32 %0, [%1], 1;" : "=r"(old) : "l"(p) : "memory");
-	return old;
-}
-__device__ __forceinline__ u64 wait_status(const u64 *p, uint32_t epoch, uint32_t max_ns) {
-	u64 w = ld_status(p);
-	uint32_t ns = 32;
-	while ((uint32_t)(w >> 50) != epoch) {
-		__nanosleep(ns);
-		if (ns < max_ns) ns <<= 1;
-		w = ld_status(p);
-	}
-	return w;
-}
 __device__ __forceinline__ Col lds_col(const unsigned char *p) {
 	const uint4 v = *reinterpret_cast<const uint4 *>(p);
 	Col c;
@@ -110,6 +91,14 @@ __device__ __forceinline__ void mbar_wait(unsigned long long *mbar, uint32_t par
 	} while (!done);
 }
 __device__ __forceinline__ uint32_t warp_sum(uint32_t v) { return __reduce_add_sync(0xffffffffu, v); }
+__device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, int lane) {
+#pragma unroll
+	for (int d = 1; d < 32; d <<= 1) {
+		const uint32_t o = __shfl_up_sync(0xffffffffu, v, d);
+		if (lane >= d) v += o;
+	}
+	return v;
+}
 
 // ---- TMA bulk store of a staging tile ------------------------------------------------
 __device__ __forceinline__ void fence_proxy_async_smem() {
@@ -126,6 +115,11 @@ __device__ __forceinline__ void bulk_wait_read_all() {
 	asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 }
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+// programmatic dependent launch (sm_90+): let the next kernel of the stream start its
+// prologue early / wait until everything the previous kernel wrote is visible
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 // Called by ONE lane after the tile is complete and fenced.  `g` is the byte address
 // of the tile in the stream (8-byte aligned); `sp` is the tile in shared memory with
@@ -144,81 +138,16 @@ __device__ __forceinline__ void store_tile(unsigned char *g, const unsigned char
 		*reinterpret_cast<uint2 *>(g + head + body) = *reinterpret_cast<const uint2 *>(sp + head + body);
 }
 
-// ---- phase D: publish this chunk's counts, obtain its exclusive prefix --------------------
-__device__ __forceinline__ void sum_status(u64 w, uint32_t &si, uint32_t &st) {
-	si = warp_sum((uint32_t)(w & kCntMask));
-	st = warp_sum((uint32_t)((w >> 25) & kCntMask));
-}
-
-__device__ __forceinline__ void publish_and_prefix(const KernelParams &p, uint32_t c, uint32_t nq, uint32_t nts,
-                                                   int lane, u64 &base_i, u64 &base_t) {
-	const uint32_t max_ns = (nq | nts) ? 256u : 2048u;  // an empty chunk is in no hurry
-	const uint32_t g = c >> 5, r = c & 31u, sg = g >> 5, gs = g & 31u;
-	uint32_t old = 0;
-	if (lane == 0) {
-		st_status(p.st_chunk + c, pack_status(p.epoch, nq, nts));
-		old = arrive(p.cnt_group + g);
-	}
-	old = __shfl_sync(0xffffffffu, old, 0);
-	const uint32_t size1 = min(32u, p.n - (g << 5));
-	if (old == size1 - 1u) {  // last chunk of its group to arrive: publish the group sum
-		const u64 w = (uint32_t)lane < size1 ? wait_status(p.st_chunk + (g << 5) + lane, p.epoch, 64u) : 0ull;
-		uint32_t si, st;
-		sum_status(w, si, st);
-		uint32_t old2 = 0;
-		if (lane == 0) {
-			st_status(p.st_group + g, pack_status(p.epoch, si, st));
-			p.cnt_group[g] = 0;  // ready for the next launch
-			old2 = arrive(p.cnt_super + sg);
-		}
-		old2 = __shfl_sync(0xffffffffu, old2, 0);
-		const uint32_t size2 = min(32u, ((p.n + 31u) >> 5) - (sg << 5));
-		if (old2 == size2 - 1u) {  // last group of its super-group
-			const u64 w2 = (uint32_t)lane < size2 ? wait_status(p.st_group + (sg << 5) + lane, p.epoch, 64u) : 0ull;
-			sum_status(w2, si, st);
-			if (lane == 0) {
-				st_status(p.st_super + sg, pack_status(p.epoch, si, st));
-				p.cnt_super[sg] = 0;
-			}
-		}
-	}
-	// exclusive prefix = earlier chunks of this group + earlier groups of this super-group
-	// + earlier super-groups (each at most 31 words, one per lane)
-	uint32_t ai = 0, at = 0;
-	if ((uint32_t)lane < r) {
-		const u64 w = wait_status(p.st_chunk + (g << 5) + lane, p.epoch, max_ns);
-		ai += (uint32_t)(w & kCntMask);
-		at += (uint32_t)((w >> 25) & kCntMask);
-	}
-	if ((uint32_t)lane < gs) {
-		const u64 w = wait_status(p.st_group + (sg << 5) + lane, p.epoch, max_ns);
-		ai += (uint32_t)(w & kCntMask);
-		at += (uint32_t)((w >> 25) & kCntMask);
-	}
-	if ((uint32_t)lane < sg) {
-		const u64 w = wait_status(p.st_super + lane, p.epoch, max_ns);
-		ai += (uint32_t)(w & kCntMask);
-		at += (uint32_t)((w >> 25) & kCntMask);
-	}
-	u64 ci = 0, ct = 0;
-	if (p.carry_in) {
-		ci = p.carry_in[0];
-		ct = p.carry_in[1];
-	}
-	base_i = ci + warp_sum(ai);
-	base_t = ct + warp_sum(at);
-}
-
-// ---- the kernel -------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads, 2) mesh_batch_kernel(const KernelParams p) {
+// ---- kernel 1: analysis ------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads, 2) analyse_kernel(const AnalyseParams p) {
 	extern __shared__ __align__(128) unsigned char smem_raw_bytes[];
 	TabEntry *tab = reinterpret_cast<TabEntry *>(smem_raw_bytes);
 	unsigned char *flags = smem_raw_bytes + 2048;
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-	WarpSmem &s = *reinterpret_cast<WarpSmem *>(smem_raw_bytes + kCtaTableBytes + (size_t)warp * sizeof(WarpSmem));
+	WarpSmem &s = *reinterpret_cast<WarpSmem *>(smem_raw_bytes + kAnalyseTableBytes + (size_t)warp * sizeof(WarpSmem));
 	const unsigned full = 0xffffffffu;
 
-	// block table + flag bytes -> shared memory, once per CTA
+	pdl_launch_dependents();  // the expand kernel may set itself up while this one works
 	if (tid < 128) reinterpret_cast<uint4 *>(tab)[tid] = __ldg(reinterpret_cast<const uint4 *>(p.table) + tid);
 	if (tid < 16) reinterpret_cast<uint4 *>(flags)[tid] = __ldg(reinterpret_cast<const uint4 *>(p.flags) + tid);
 	init_warp_smem(s, lane);
@@ -231,19 +160,17 @@ __global__ void __launch_bounds__(kThreads, 2) mesh_batch_kernel(const KernelPar
 	const int h = lane >> 4, y = lane & 15;
 	unsigned char *raw = smem_raw(s);
 	uint32_t parity = 0;
+	u64 next = 0;
+	if (lane == 0) next = atomicAdd(p.ticket, 1ull) - p.ticket_base;
 	for (;;) {
-		u64 ticket = 0;
-		if (lane == 0) {
-			bulk_wait_read_all();  // the staging tile (= raw chunk + Ey/Ex) is free once the last bulk store has read it
-			ticket = atomicAdd(p.ticket, 1ull) - p.ticket_base;
-		}
-		ticket = __shfl_sync(full, ticket, 0);  // also orders the previous chunk's smem reads before this one's writes
+		const u64 ticket = __shfl_sync(full, next, 0);  // also orders the previous chunk's smem reads before this one's writes
 		if (ticket >= (u64)p.n) break;
 		const uint32_t c = (uint32_t)ticket;
 		const unsigned char *chunk = p.chunks + (size_t)c * 4096u;
-		if (lane == 0) bulk_load_g2s(raw, chunk, 4096u, &s.mbar);  // TMA: 4 KiB chunk -> shared memory
-		phase_pos(s, lane, p.offs + 3 * (size_t)c);
-		zero_border(s, lane);
+		if (lane == 0) {
+			bulk_load_g2s(raw, chunk, 4096u, &s.mbar);            // TMA: 4 KiB chunk -> shared memory
+			next = atomicAdd(p.ticket, 1ull) - p.ticket_base;     // the next ticket travels while this chunk is analysed
+		}
 		mbar_wait(&s.mbar, parity);
 		parity ^= 1u;
 
@@ -253,8 +180,8 @@ __global__ void __launch_bounds__(kThreads, 2) mesh_batch_kernel(const KernelPar
 		for (int j = 0; j < 8; j++) {
 			const int col = 32 * j + lane;
 			const Col own = lds_col(raw + col * 16);
-			const Col ny = lds_col(raw + (col - 1) * 16);   // (x, y-1); unused garbage for y = 0
-			const Col nx = lds_col(raw + (col - 16) * 16);  // (x-1, y); unused garbage for x = 0
+			const Col ny = lds_col(raw + ((col - 1) & 255) * 16);   // (x, y-1); unused garbage for y = 0
+			const Col nx = lds_col(raw + ((col - 16) & 255) * 16);  // (x-1, y); unused garbage for x = 0
 			uint32_t sum;
 			const uint32_t bz = col_flags(flags, own, sum);
 			smem_Bzp(s)[(2 * j + h + 1) * kBzStride + y + 1] = (uint16_t)bz;
@@ -265,116 +192,169 @@ __global__ void __launch_bounds__(kThreads, 2) mesh_batch_kernel(const KernelPar
 			ncrossed += sum >> 5;
 		}
 		uint32_t nq = 0, npl = 0;
-		if (__any_sync(full, (anyb | crossed_cols) != 0u)) {  // else: nothing drawn (e.g. an all-air chunk)
-			npl = warp_sum(ncrossed);
+		uint32_t *di = p.desc_i + (size_t)c * kDescStrideI;
+		if (__any_sync(full, anyb != 0u)) {  // else: no cube in the chunk (e.g. all air)
 			__syncwarp();
 			// B. run starts over z for the six passes
 #pragma unroll 1
 			for (int j = 0; j < 8; j++) col_starts(s, tab, raw, 2 * j + h, y);
 			__syncwarp();
-			// C. masks over the merge axes; per-group quad counts; scan in emission order
+			// C. blocky masks over the merge axes; quads per group; scan in emission order
 			transpose_blocky(s, lane);
-			__syncwarp();  // Bzp is dead from here on: its bytes become rowpre
-			uint32_t run = 0;
-#pragma unroll 1
-			for (int k = 0; k < 3; k++) {
-				const uint32_t cnt = transpose_group(s, lane + 32 * k);
-				uint32_t inc = cnt;
+			uint32_t cnt[3], run = 0;
 #pragma unroll
-				for (int d = 1; d < 32; d <<= 1) {
-					const uint32_t o = __shfl_up_sync(full, inc, d);
-					if (lane >= d) inc += o;
-				}
-				s.gpre[lane + 32 * k] = (uint16_t)(run + inc - cnt);
+			for (int k = 0; k < 3; k++) {
+				cnt[k] = count_group(s, lane + 32 * k);
+				const uint32_t inc = warp_incl_scan(cnt[k], lane);
+				const uint32_t ex = run + inc - cnt[k];
 				run += __shfl_sync(full, inc, 31);
+				cnt[k] = cnt[k] ? ex : 0xffffffffu;  // from here on: the group's offset, or "empty"
 			}
 			nq = run;
-			__syncwarp();
-		}
-		const uint32_t nts = npl * (uint32_t)kPlantQuads;
-
-		// D. where this chunk's vertices go
-		u64 base_i, base_t;
-		publish_and_prefix(p, c, nq, nts, lane, base_i, base_t);
-		if (lane == 0) {
-			Range ri, rt;
-			ri.first_vertex = base_i * 6ull; ri.vertex_count = nq * 6u; ri.reserved = 0;
-			rt.first_vertex = base_t * 6ull; rt.vertex_count = nts * 6u; rt.reserved = 0;
-			p.ranges_i[c] = ri;
-			p.ranges_t[c] = rt;
-			if (c == p.n - 1) {
-				p.totals[0] = base_i + nq;
-				p.totals[1] = base_t + nts;
-			}
-		}
-
-		// E1. intransparent stream: the six face passes
-		if (nq != 0 && base_i + nq <= p.cap_i) {
+			__syncwarp();  // By / Bx complete
+			// D. descriptors, group by group
 #pragma unroll 1
-			for (uint32_t t0 = 0; t0 < nq; t0 += kTileQuads) {
-				const uint32_t tn = min((uint32_t)kTileQuads, nq - t0);
-				int m = 0, c2 = 0, st = 0;
-				if ((uint32_t)lane < tn) find_quad(s, t0 + lane, m, c2, st);
-				if (lane == 0) bulk_wait_read_all();  // staging tile free again
-				__syncwarp();
-				unsigned char *g = p.out_i + (base_i + t0) * (u64)kQuadBytes;
-				unsigned char *sp = s.stage + ((uintptr_t)g & 8u);
-				if ((uint32_t)lane < tn) expand_face_quad(s, tab, chunk, m, c2, st, sp + lane * kQuadBytes);
-				fence_proxy_async_smem();
-				__syncwarp();
-				if (lane == 0) store_tile(g, sp, tn * kQuadBytes);
+			for (int k = 0; k < 3; k++) {
+				const uint32_t off = k == 0 ? cnt[0] : k == 1 ? cnt[1] : cnt[2];
+				if (off != 0xffffffffu) emit_group_descs(s, lane + 32 * k, di + off);
 			}
 		}
-		// E2. transparent stream: crossed plants, 4 quad slots each
-		if (npl != 0 && base_t + nts <= p.cap_t) {
-			__syncwarp();  // S is no longer read: reuse it for the crossed masks and their prefix
-			uint16_t *Cz = smem_Cz(s), *cpre = smem_cpre(s);
+		if (__any_sync(full, crossed_cols != 0u)) {
+			__syncwarp();  // Ey / Ex are dead (phase B is done): Cz takes their place
+			uint16_t *Cz = smem_Cz(s);
 #pragma unroll 1
 			for (int j = 0; j < 8; j++) {
 				uint32_t cz = 0;
-				if ((crossed_cols >> j) & 1u) {
-					const uint4 v = __ldg(reinterpret_cast<const uint4 *>(chunk) + 32 * j + lane);
-					Col cc;
-					cc.w[0] = v.x; cc.w[1] = v.y; cc.w[2] = v.z; cc.w[3] = v.w;
-					cz = col_crossed(flags, cc);
-				}
+				if ((crossed_cols >> j) & 1u) cz = col_crossed(flags, lds_col(raw + (32 * j + lane) * 16));
 				Cz[32 * j + lane] = (uint16_t)cz;
 			}
 			__syncwarp();
-			uint32_t cnt[8], mine = 0;
-#pragma unroll
-			for (int k = 0; k < 8; k++) {
-				cnt[k] = (uint32_t)__popc((uint32_t)Cz[lane * 8 + k]);
-				mine += cnt[k];
-			}
-			uint32_t inc = mine;
-#pragma unroll
-			for (int d = 1; d < 32; d <<= 1) {
-				const uint32_t o = __shfl_up_sync(full, inc, d);
-				if (lane >= d) inc += o;
-			}
-			uint32_t ex = inc - mine;
-#pragma unroll
-			for (int k = 0; k < 8; k++) {
-				cpre[lane * 8 + k] = (uint16_t)ex;
-				ex += cnt[k];
-			}
-			__syncwarp();
-#pragma unroll 1
-			for (uint32_t t0 = 0; t0 < nts; t0 += kTileQuads) {
-				const uint32_t tn = min((uint32_t)kTileQuads, nts - t0);
-				int cell = 0;
-				if ((uint32_t)lane < tn) cell = find_plant(s, (t0 + lane) >> 2);
-				if (lane == 0) bulk_wait_read_all();
-				__syncwarp();
-				unsigned char *g = p.out_t + (base_t + t0) * (u64)kQuadBytes;
-				unsigned char *sp = s.stage + ((uintptr_t)g & 8u);
-				if ((uint32_t)lane < tn) expand_plant_quad(s, tab, chunk, cell, (int)((t0 + lane) & 3u), sp + lane * kQuadBytes);
-				fence_proxy_async_smem();
-				__syncwarp();
-				if (lane == 0) store_tile(g, sp, tn * kQuadBytes);
-			}
+			const uint32_t mine = count_plants8(s, lane);
+			const uint32_t inc = warp_incl_scan(mine, lane);
+			npl = __shfl_sync(full, inc, 31);
+			if (mine) emit_plant_descs(s, lane, p.desc_t + (size_t)c * kDescStrideT + (inc - mine));
 		}
+		if (lane == 0) {
+			p.cnt_i[c] = nq;
+			p.cnt_t[c] = npl * (uint32_t)kPlantQuads;
+		}
+	}
+}
+
+// ---- kernel 2: expansion -------------------------------------------------------------------
+// Exclusive prefix of cnt[0..n) into pre[0..n], pre[n] = total; pre[k > n] = 0xffffffff so that a
+// fixed-depth binary search never steps past n.  All kExpandThreads threads take part.
+__device__ __forceinline__ void block_scan_counts(const uint32_t *cnt, uint32_t n, uint32_t *pre, uint32_t *warp_tot,
+                                                  int tid) {
+	const int lane = tid & 31, warp = tid >> 5;
+	uint32_t v[kScanPerThread];
+	const uint32_t first = (uint32_t)tid * kScanPerThread;
+	uint32_t sum = 0;
+#pragma unroll
+	for (int k = 0; k < kScanPerThread; k += 4) {
+		uint4 q = make_uint4(0, 0, 0, 0);
+		if (first + k < n) q = *reinterpret_cast<const uint4 *>(cnt + first + k);  // the arrays are padded to kMaxLaunchChunks
+		v[k] = first + k < n ? q.x : 0u;
+		v[k + 1] = first + k + 1 < n ? q.y : 0u;
+		v[k + 2] = first + k + 2 < n ? q.z : 0u;
+		v[k + 3] = first + k + 3 < n ? q.w : 0u;
+		sum += v[k] + v[k + 1] + v[k + 2] + v[k + 3];
+	}
+	const uint32_t inc = warp_incl_scan(sum, lane);
+	if (lane == 31) warp_tot[warp] = inc;
+	__syncthreads();
+	uint32_t wt = lane < kExpandWarps ? warp_tot[lane] : 0u;
+	const uint32_t winc = warp_incl_scan(wt, lane);
+	const uint32_t wbase = __shfl_sync(0xffffffffu, winc - wt, warp);
+	const uint32_t total = __shfl_sync(0xffffffffu, winc, kExpandWarps - 1);
+	uint32_t run = wbase + inc - sum;
+#pragma unroll
+	for (int k = 0; k < kScanPerThread; k++) {
+		const uint32_t i = first + k;
+		pre[i] = i <= n ? run : 0xffffffffu;
+		run += v[k];
+	}
+	if (tid < 4) pre[kMaxLaunchChunks + tid] = (kMaxLaunchChunks + tid) <= n ? total : 0xffffffffu;
+	__syncthreads();
+}
+
+// largest c in [0, n) with pre[c] <= q  (q < pre[n]); `top` = highest power of two <= n
+__device__ __forceinline__ uint32_t find_chunk(const uint32_t *pre, uint32_t q, uint32_t top) {
+	uint32_t lo = 0;
+	for (uint32_t step = top; step >= 1; step >>= 1)
+		if (pre[lo + step] <= q) lo += step;
+	return lo;
+}
+
+__global__ void __launch_bounds__(kExpandThreads, 1) expand_kernel(const ExpandParams p) {
+	extern __shared__ __align__(128) unsigned char smem_raw_bytes[];
+	TabEntry *tab = reinterpret_cast<TabEntry *>(smem_raw_bytes);
+	uint32_t *pre_i = reinterpret_cast<uint32_t *>(smem_raw_bytes + 2048);
+	uint32_t *pre_t = pre_i + kExpandPrefixWords;
+	uint32_t *warp_tot = pre_t + kExpandPrefixWords;
+	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+	unsigned char *stage = smem_raw_bytes + 2048 + 2 * 4 * kExpandPrefixWords + 256 + (size_t)warp * (kStageBytes + 16);
+
+	if (tid < 128) reinterpret_cast<uint4 *>(tab)[tid] = __ldg(reinterpret_cast<const uint4 *>(p.table) + tid);
+	pdl_wait();  // everything the analysis wrote is visible from here on
+	block_scan_counts(p.cnt_i, p.n, pre_i, warp_tot, tid);
+	block_scan_counts(p.cnt_t, p.n, pre_t, warp_tot, tid);
+	const uint32_t tot_i = pre_i[p.n], tot_t = pre_t[p.n];
+	u64 carry_i = 0, carry_t = 0;
+	if (p.carry_in) {
+		carry_i = p.carry_in[0];
+		carry_t = p.carry_in[1];
+	}
+	// per-chunk ranges and the totals: spread over the grid
+	for (uint32_t c = blockIdx.x * kExpandThreads + tid; c < p.n; c += gridDim.x * kExpandThreads) {
+		Range ri, rt;
+		ri.first_vertex = (carry_i + pre_i[c]) * 6ull; ri.vertex_count = (pre_i[c + 1] - pre_i[c]) * 6u; ri.reserved = 0;
+		rt.first_vertex = (carry_t + pre_t[c]) * 6ull; rt.vertex_count = (pre_t[c + 1] - pre_t[c]) * 6u; rt.reserved = 0;
+		p.ranges_i[c] = ri;
+		p.ranges_t[c] = rt;
+	}
+	if (blockIdx.x == 0 && tid == 0) {
+		p.totals[0] = carry_i + tot_i;
+		p.totals[1] = carry_t + tot_t;
+	}
+	uint32_t top = 1;
+	while (top * 2u <= p.n) top *= 2u;
+	if (top == p.n) top >>= 1;  // the steps top, top/2, .., 1 then reach exactly [0, 2*top) >= [0, n)
+
+	const bool fits_i = carry_i + tot_i <= p.cap_i, fits_t = carry_t + tot_t <= p.cap_t;
+	const uint32_t tiles_i = fits_i ? (tot_i + kTileQuads - 1) / kTileQuads : 0u;
+	const uint32_t tiles_t = fits_t ? (tot_t + kTileQuads - 1) / kTileQuads : 0u;
+	const uint32_t gw = blockIdx.x * kExpandWarps + warp, nw = gridDim.x * kExpandWarps;
+#pragma unroll 1
+	for (uint32_t t = gw; t < tiles_i + tiles_t; t += nw) {
+		const bool face = t < tiles_i;
+		const uint32_t q0 = (face ? t : t - tiles_i) * kTileQuads;
+		const uint32_t tot = face ? tot_i : tot_t;
+		const uint32_t tn = min((uint32_t)kTileQuads, tot - q0);
+		const uint32_t q = q0 + (uint32_t)lane;
+		const bool act = (uint32_t)lane < tn;
+		uint32_t d = 0, c = 0;
+		long long ox = 0, oy = 0, oz = 0;
+		if (act) {
+			const uint32_t *pre = face ? pre_i : pre_t;
+			c = find_chunk(pre, q, top);
+			const uint32_t r = q - pre[c];
+			d = face ? __ldg(p.desc_i + (size_t)c * kDescStrideI + r) : __ldg(p.desc_t + (size_t)c * kDescStrideT + (r >> 2));
+			ox = __ldg(p.offs + 3 * (size_t)c);
+			oy = __ldg(p.offs + 3 * (size_t)c + 1);
+			oz = __ldg(p.offs + 3 * (size_t)c + 2);
+		}
+		unsigned char *g = (face ? p.out_i + (carry_i + q0) * (u64)kQuadBytes : p.out_t + (carry_t + q0) * (u64)kQuadBytes);
+		unsigned char *sp = stage + ((uintptr_t)g & 8u);
+		if (lane == 0) bulk_wait_read_all();  // the staging tile is free once the last bulk store has read it
+		__syncwarp();
+		if (act) {
+			if (face) expand_face_desc(tab, ox, oy, oz, d, sp + lane * kQuadBytes);
+			else expand_plant_desc(tab, ox, oy, oz, d, (int)(q & 3u), sp + lane * kQuadBytes);
+		}
+		fence_proxy_async_smem();
+		__syncwarp();
+		if (lane == 0) store_tile(g, sp, tn * kQuadBytes);
 	}
 	if (lane == 0) bulk_wait_all();  // all bulk stores of this warp have landed before it exits
 }

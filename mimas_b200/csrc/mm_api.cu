@@ -7,6 +7,7 @@
 #include <cuda_runtime.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -21,7 +22,8 @@
 static_assert(sizeof(mm_vertex) == 36, "Vertex must be 36 bytes (SURVEY.md 8b)");
 static_assert(sizeof(mm_range) == 16 && sizeof(mm::Range) == 16, "range layout");
 static_assert(sizeof(mm_block_entry) == 12, "block entry layout");
-static_assert(mm::kCtaSmemBytes <= 113 * 1024, "2 CTAs per SM need <= 113 KiB each");
+static_assert(mm::kAnalyseSmemBytes <= 113 * 1024, "2 analysing CTAs per SM need <= 113 KiB each");
+static_assert(mm::kExpandSmemBytes <= 227 * 1024, "the expand CTA must fit the 227 KiB of an SM");
 
 namespace {
 
@@ -88,53 +90,82 @@ int ensure_pinned(mm_ctx *c, unsigned char **p, size_t *have, size_t want) {
 	return MM_OK;
 }
 
-// Sizes of the prefix state for one launch of up to kMaxLaunchChunks chunks.
-constexpr size_t kSyncChunkWords = mm::kMaxLaunchChunks, kSyncGroupWords = mm::kMaxLaunchChunks / 32, kSyncSuperWords = 32;
-constexpr size_t kSyncStatusBytes = 8 * (kSyncChunkWords + kSyncGroupWords + kSyncSuperWords);
-constexpr size_t kSyncBytes = kSyncStatusBytes + 4 * (kSyncGroupWords + kSyncSuperWords);
+// Descriptor slots for launches of up to n chunks (64 KiB per chunk; only the touched lines cost
+// bandwidth, and they are re-read from L2 by the expand kernel).
+int ensure_desc_capacity(mm_ctx *c, uint32_t n) {
+	n = std::min<uint32_t>(n, mm::kMaxLaunchChunks);
+	if (n <= c->cap_desc_chunks) return MM_OK;
+	const uint32_t nc = std::min<uint32_t>(std::max<uint32_t>(n, 256u), mm::kMaxLaunchChunks);
+	MM_CUDA(c, cudaStreamSynchronize(c->stream));
+	cudaFree(c->d_desc_i); cudaFree(c->d_desc_t);
+	c->d_desc_i = c->d_desc_t = nullptr;
+	c->cap_desc_chunks = 0;
+	MM_CUDA(c, cudaMalloc(&c->d_desc_i, sizeof(uint32_t) * (size_t)nc * mm::kDescStrideI));
+	MM_CUDA(c, cudaMalloc(&c->d_desc_t, sizeof(uint32_t) * (size_t)nc * mm::kDescStrideT));
+	c->cap_desc_chunks = nc;
+	return MM_OK;
+}
 
-// Enqueue the mesher for (d_chunks, d_offs, n) on the context's stream: one launch per
-// kMaxLaunchChunks chunks, each continuing the packed streams where the previous one ended.
+// Enqueue the mesher for (d_chunks, d_offs, n) on the context's stream: per kMaxLaunchChunks
+// chunks one analyse + one expand launch, each pair continuing the packed streams where the
+// previous one ended.
 int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, uint32_t n) {
+	int rc;
+	if ((rc = ensure_desc_capacity(c, n))) return rc;
 	MM_CUDA(c, cudaEventRecord(c->ev0, c->stream));
 	const mm::u64 *carry = nullptr;
 	for (uint32_t first = 0; first < n; first += mm::kMaxLaunchChunks) {
 		const uint32_t m = std::min<uint32_t>(n - first, mm::kMaxLaunchChunks);
-		if (++c->epoch >= (1u << 14)) {  // epoch tags wrap: forget every old status word
-			MM_CUDA(c, cudaMemsetAsync(c->d_sync, 0, kSyncStatusBytes, c->stream));
-			c->epoch = 1;
-		}
 		c->totals_slot ^= 1;
-		mm::KernelParams p;
-		p.chunks = d_chunks + (size_t)first * 4096u;
-		p.offs = d_offs + (size_t)first * 3u;
-		p.n = m;
-		p.epoch = c->epoch;
-		p.table = c->d_table;
-		p.flags = c->d_flags;
-		p.out_i = c->d_out_i;
-		p.out_t = c->d_out_t;
-		p.cap_i = c->cap_i;
-		p.cap_t = c->cap_t;
-		p.ranges_i = c->d_ranges_i + first;
-		p.ranges_t = c->d_ranges_t + first;
-		p.st_chunk = c->d_st_chunk;
-		p.st_group = c->d_st_group;
-		p.st_super = c->d_st_super;
-		p.cnt_group = c->d_cnt_group;
-		p.cnt_super = c->d_cnt_super;
-		p.ticket = c->d_ticket;
-		p.ticket_base = c->ticket_base;
-		p.carry_in = carry;
-		p.totals = c->d_ticket + 2 + 2 * c->totals_slot;
+		mm::AnalyseParams a;
+		a.chunks = d_chunks + (size_t)first * 4096u;
+		a.n = m;
+		a.table = c->d_table;
+		a.flags = c->d_flags;
+		a.desc_i = c->d_desc_i;
+		a.desc_t = c->d_desc_t;
+		a.cnt_i = c->d_cnt;
+		a.cnt_t = c->d_cnt + mm::kMaxLaunchChunks;
+		a.ticket = c->d_ticket;
+		a.ticket_base = c->ticket_base;
 		const uint32_t ctas = (m + mm::kWarpsPerCta - 1) / mm::kWarpsPerCta;
 		const uint32_t grid = std::min<uint32_t>(ctas, (uint32_t)(c->sm_count * c->ctas_per_sm));
-		mm::mesh_batch_kernel<<<grid, mm::kThreads, mm::kCtaSmemBytes, c->stream>>>(p);
+		mm::analyse_kernel<<<grid, mm::kThreads, mm::kAnalyseSmemBytes, c->stream>>>(a);
 		MM_CUDA(c, cudaGetLastError());
 		c->ticket_base += (mm::u64)m + (mm::u64)grid * mm::kWarpsPerCta;  // every warp draws exactly one ticket >= m
-		carry = p.totals;
-		c->last_launches++;
-		c->total_launches++;
+
+		mm::ExpandParams e;
+		e.offs = d_offs + (size_t)first * 3u;
+		e.n = m;
+		e.table = c->d_table;
+		e.desc_i = c->d_desc_i;
+		e.desc_t = c->d_desc_t;
+		e.cnt_i = a.cnt_i;
+		e.cnt_t = a.cnt_t;
+		e.out_i = c->d_out_i;
+		e.out_t = c->d_out_t;
+		e.cap_i = c->cap_i;
+		e.cap_t = c->cap_t;
+		e.ranges_i = c->d_ranges_i + first;
+		e.ranges_t = c->d_ranges_t + first;
+		e.carry_in = carry;
+		e.totals = c->d_ticket + 2 + 2 * c->totals_slot;
+		// programmatic dependent launch: the expand CTAs start (table load) while the analysis
+		// drains and wait in griddepcontrol.wait for its results
+		cudaLaunchConfig_t cfg = {};
+		cfg.gridDim = dim3((unsigned)c->expand_grid);
+		cfg.blockDim = dim3(mm::kExpandThreads);
+		cfg.dynamicSmemBytes = mm::kExpandSmemBytes;
+		cfg.stream = c->stream;
+		cudaLaunchAttribute attr[1];
+		attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+		attr[0].val.programmaticStreamSerializationAllowed = c->use_pdl ? 1 : 0;
+		cfg.attrs = attr;
+		cfg.numAttrs = 1;
+		MM_CUDA(c, cudaLaunchKernelEx(&cfg, mm::expand_kernel, e));
+		carry = e.totals;
+		c->last_launches += 2;
+		c->total_launches += 2;
 	}
 	MM_CUDA(c, cudaEventRecord(c->ev1, c->stream));
 	MM_CUDA(c, cudaMemcpyAsync(c->h_totals, carry, 2 * sizeof(mm::u64), cudaMemcpyDeviceToHost, c->stream));
@@ -168,12 +199,19 @@ int mm_ctx_create(int device, mm_ctx **out) {
 		MM_CUDA(c, cudaGetDeviceProperties(&prop, device));
 		if (prop.major < 10) return fail(c, MM_ERR_NO_DEVICE, "device %d is sm_%d%d; this library is built for sm_100a", device, prop.major, prop.minor);
 		c->sm_count = prop.multiProcessorCount;
-		MM_CUDA(c, cudaFuncSetAttribute(mm::mesh_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mm::kCtaSmemBytes));
-		MM_CUDA(c, cudaFuncSetAttribute(mm::mesh_batch_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+		MM_CUDA(c, cudaFuncSetAttribute(mm::analyse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mm::kAnalyseSmemBytes));
+		MM_CUDA(c, cudaFuncSetAttribute(mm::analyse_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+		MM_CUDA(c, cudaFuncSetAttribute(mm::expand_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mm::kExpandSmemBytes));
+		MM_CUDA(c, cudaFuncSetAttribute(mm::expand_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
 		int occ = 0;
-		MM_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mm::mesh_batch_kernel, mm::kThreads, mm::kCtaSmemBytes));
-		if (occ < 1) return fail(c, MM_ERR_CUDA, "mesher kernel does not fit on an SM");
+		MM_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mm::analyse_kernel, mm::kThreads, mm::kAnalyseSmemBytes));
+		if (occ < 1) return fail(c, MM_ERR_CUDA, "analyse kernel does not fit on an SM");
 		c->ctas_per_sm = occ;
+		int occ2 = 0;
+		MM_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, mm::expand_kernel, mm::kExpandThreads, mm::kExpandSmemBytes));
+		if (occ2 < 1) return fail(c, MM_ERR_CUDA, "expand kernel does not fit on an SM");
+		c->expand_grid = c->sm_count * occ2;
+		c->use_pdl = getenv("MM_NO_PDL") == nullptr;
 		MM_CUDA(c, cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
 		c->stream = c->own_stream;
 		MM_CUDA(c, cudaEventCreate(&c->ev0));
@@ -182,13 +220,8 @@ int mm_ctx_create(int device, mm_ctx **out) {
 		MM_CUDA(c, cudaMalloc(&c->d_ticket, sizeof(mm::u64) * 8));
 		MM_CUDA(c, cudaMemset(c->d_ticket, 0, sizeof(mm::u64) * 8));
 		MM_CUDA(c, cudaMalloc(&c->d_flags, 256));
-		MM_CUDA(c, cudaMalloc(&c->d_sync, kSyncBytes));
-		MM_CUDA(c, cudaMemset(c->d_sync, 0, kSyncBytes));
-		c->d_st_chunk = reinterpret_cast<mm::u64 *>(c->d_sync);
-		c->d_st_group = c->d_st_chunk + kSyncChunkWords;
-		c->d_st_super = c->d_st_group + kSyncGroupWords;
-		c->d_cnt_group = reinterpret_cast<uint32_t *>(c->d_st_super + kSyncSuperWords);
-		c->d_cnt_super = c->d_cnt_group + kSyncGroupWords;
+		MM_CUDA(c, cudaMalloc(&c->d_cnt, sizeof(uint32_t) * 2 * mm::kMaxLaunchChunks));
+		MM_CUDA(c, cudaMemset(c->d_cnt, 0, sizeof(uint32_t) * 2 * mm::kMaxLaunchChunks));
 		MM_CUDA(c, cudaHostAlloc(&c->h_totals, sizeof(mm::u64) * 2, cudaHostAllocDefault));
 		return MM_OK;
 	};
@@ -207,7 +240,7 @@ int mm_ctx_destroy(mm_ctx *c) {
 	cudaSetDevice(c->device);
 	if (c->own_stream) cudaStreamSynchronize(c->own_stream);
 	cudaFree(c->d_table); cudaFree(c->d_out_i); cudaFree(c->d_out_t); cudaFree(c->d_ranges_i);
-	cudaFree(c->d_ranges_t); cudaFree(c->d_sync); cudaFree(c->d_flags); cudaFree(c->d_ticket);
+	cudaFree(c->d_ranges_t); cudaFree(c->d_cnt); cudaFree(c->d_desc_i); cudaFree(c->d_desc_t); cudaFree(c->d_flags); cudaFree(c->d_ticket);
 	cudaFree(c->d_in_chunks); cudaFree(c->d_in_offs);
 	if (c->h_totals) cudaFreeHost(c->h_totals);
 	if (c->h_in) cudaFreeHost(c->h_in);

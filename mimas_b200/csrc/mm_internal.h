@@ -24,12 +24,12 @@ struct mm_ctx {
 	// per-chunk arrays
 	uint32_t cap_chunks = 0;
 	mm::Range *d_ranges_i = nullptr, *d_ranges_t = nullptr;
-	// batch-wide prefix state (mesh_kernel.cuh phase D): status words tagged with the launch epoch,
-	// arrival counters that every launch leaves at zero
-	unsigned char *d_sync = nullptr;  // one allocation holding all of the below
-	mm::u64 *d_st_chunk = nullptr, *d_st_group = nullptr, *d_st_super = nullptr;
-	uint32_t *d_cnt_group = nullptr, *d_cnt_super = nullptr;
-	uint32_t epoch = 0;               // of the last launch; 1..16383, status words are cleared on wrap
+	// analysis -> expansion hand-over (mesh_kernel.cuh): per-chunk descriptor slots and counts
+	uint32_t *d_desc_i = nullptr, *d_desc_t = nullptr;  // cap_desc_chunks * kDescStrideI / kDescStrideT words
+	uint32_t cap_desc_chunks = 0;
+	uint32_t *d_cnt = nullptr;        // cnt_i[kMaxLaunchChunks] then cnt_t[kMaxLaunchChunks]
+	int expand_grid = 0;
+	bool use_pdl = true;
 	mm::u64 *d_ticket = nullptr;      // [0] ticket counter, [2..3] and [4..5] alternating totals slots
 	int totals_slot = 0;              // slot the last launch wrote
 	mm::u64 ticket_base = 0;

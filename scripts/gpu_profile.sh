@@ -8,6 +8,6 @@ $CMD > gpurun_out/${tag}_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${tag}_launches.csv $CMD > gpurun_out/${tag}_ncu_list.log 2>&1
 echo "launch list exit $?"
 $CMD > gpurun_out/${tag}_plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:mesh_batch_kernel -s 8 -c 3 -f -o gpurun_out/${tag}_prof $CMD > gpurun_out/${tag}_ncu_full.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:analyse_kernel\|expand_kernel -s 16 -c 4 -f -o gpurun_out/${tag}_prof $CMD > gpurun_out/${tag}_ncu_full.log 2>&1
 echo "full capture exit $?"
 ls -la gpurun_out/

@@ -9,6 +9,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <vector>
 
 #include "../../mimas_b200/csrc/mesh_core.cuh"
 
@@ -59,101 +60,99 @@ extern "C" int emul_mesh_batch(const uint8_t *chunks, const int64_t *offs, uint3
 		flags[i] = kind == 1 ? kFlagBlocky : kind == 2 ? kFlagCrossed : 0;
 	}
 	for (int lane = 0; lane < kLanes; lane++) init_warp_smem(s, lane);
-	uint64_t run_q = 0, run_t = 0;
+	// ---- analyse kernel: one warp per chunk -> counts + descriptors ----------------------
+	std::vector<uint32_t> desc_i((size_t)n * kDescStrideI, 0xDEADBEEFu), desc_t((size_t)n * kDescStrideT, 0xDEADBEEFu);
+	std::vector<uint32_t> cnt_i(n), cnt_t(n);
 	for (uint32_t c = 0; c < n; c++) {
 		const uint8_t *chunk = chunks + (size_t)c * 4096;
-		long long o3[3] = {offs[3 * c], offs[3 * c + 1], offs[3 * c + 2]};
-		for (int lane = 0; lane < kLanes; lane++) phase_pos(s, lane, o3);
-		for (int lane = 0; lane < kLanes; lane++) zero_border(s, lane);
 		memcpy(smem_raw(s), chunk, 4096);  // the bulk async copy of the kernel
 		const uint8_t *raw = smem_raw(s);
 		// A
-		uint32_t anyb = 0, npl = 0;
+		uint32_t anyb = 0;
 		uint32_t crossed_cols[kLanes] = {0};
 		for (int j = 0; j < 8; j++)
 			for (int lane = 0; lane < kLanes; lane++) {
-				const int h = lane >> 4, y = lane & 15, x = 2 * j + h;
-				const Col own = load_col(chunk, x, y);
-				// what the shuffles deliver: lane-1 (wraps to garbage at y = 0) and the (x-1, y) column
-				Col ny = y > 0 ? load_col(chunk, x, y - 1) : own;
-				Col nx;
-				if (x > 0) nx = load_col(chunk, x - 1, y);
-				else memset(nx.w, 0, sizeof(nx.w));
+				const int col = 32 * j + lane, h = lane >> 4, y = lane & 15, x = 2 * j + h;
+				const Col own = load_col(raw, x, y);
+				Col ny, nx;  // what the kernel loads: wrapped-around garbage at y = 0 / x = 0
+				memcpy(ny.w, raw + ((col - 1) & 255) * 16, 16);
+				memcpy(nx.w, raw + ((col - 16) & 255) * 16, 16);
 				uint32_t sum;
 				const uint32_t bz = col_flags(flags, own, sum);
 				smem_Bzp(s)[(x + 1) * kBzStride + y + 1] = (uint16_t)bz;
-				smem_Ey(s)[32 * j + lane] = (uint16_t)eq_mask16(own, ny);
-				smem_Ex(s)[32 * j + lane] = (uint16_t)eq_mask16(own, nx);
+				smem_Ey(s)[col] = (uint16_t)eq_mask16(own, ny);
+				smem_Ex(s)[col] = (uint16_t)eq_mask16(own, nx);
 				anyb |= bz;
 				crossed_cols[lane] |= ((sum >> 5) ? 1u : 0u) << j;
-				npl += sum >> 5;
 			}
 		uint32_t anyc = 0;
 		for (int lane = 0; lane < kLanes; lane++) anyc |= crossed_cols[lane];
-		uint32_t nq = 0;
-		if (!(anyb | anyc)) npl = 0;
-		if (anyb | anyc) {
+		uint32_t nq = 0, npl = 0;
+		uint32_t *di = desc_i.data() + (size_t)c * kDescStrideI;
+		if (anyb) {
 			// B
 			for (int j = 0; j < 8; j++)
 				for (int lane = 0; lane < kLanes; lane++) col_starts(s, tab, raw, 2 * j + (lane >> 4), lane & 15);
 			// C
 			for (int lane = 0; lane < kLanes; lane++) transpose_blocky(s, lane);
-			uint32_t cnt[kGroups];
-			for (int k = 0; k < 3; k++)
-				for (int lane = 0; lane < kLanes; lane++) cnt[lane + 32 * k] = transpose_group(s, lane + 32 * k);
+			uint32_t gofs[kGroups];
 			for (int m = 0; m < kGroups; m++) {
-				s.gpre[m] = (uint16_t)nq;
-				nq += cnt[m];
+				gofs[m] = nq;
+				nq += count_group(s, m);
 			}
+			// D
+			for (int m = 0; m < kGroups; m++)
+				if (count_group(s, m)) emit_group_descs(s, m, di + gofs[m]);
 		}
-		const uint32_t nts = npl * kPlantQuads;
-		// D
-		const uint64_t base_q = run_q, base_t = run_t;
-		run_q += nq;
-		run_t += nts;
-		ranges_i[c].first_vertex = base_q * 6; ranges_i[c].vertex_count = nq * 6; ranges_i[c].reserved = 0;
-		ranges_t[c].first_vertex = base_t * 6; ranges_t[c].vertex_count = nts * 6; ranges_t[c].reserved = 0;
-		// E1
-		if (nq && base_q + nq <= cap_i) {
-			for (uint32_t t0 = 0; t0 < nq; t0 += kTileQuads) {
-				const uint32_t tn = std::min<uint32_t>(kTileQuads, nq - t0);
-				int m[kLanes], c2[kLanes], st[kLanes];
-				for (uint32_t lane = 0; lane < tn; lane++) find_quad(s, t0 + lane, m[lane], c2[lane], st[lane]);
-				unsigned char *g = out_i + (base_q + t0) * (uint64_t)kQuadBytes;
-				unsigned char *stg = s.stage + ((uintptr_t)g & 8u);
-				for (uint32_t lane = 0; lane < tn; lane++)
-					expand_face_quad(s, tab, chunk, m[lane], c2[lane], st[lane], stg + lane * kQuadBytes);
-				store_tile(g, stg, tn * kQuadBytes);
-			}
-		}
-		// E2
-		if (npl && base_t + nts <= cap_t) {
-			uint16_t *Cz = smem_Cz(s), *cpre = smem_cpre(s);
+		if (anyc) {
+			uint16_t *Cz = smem_Cz(s);
 			for (int j = 0; j < 8; j++)
 				for (int lane = 0; lane < kLanes; lane++) {
 					const int h = lane >> 4, y = lane & 15, x = 2 * j + h;
 					Cz[32 * j + lane] =
-					    (uint16_t)(((crossed_cols[lane] >> j) & 1u) ? col_crossed(flags, load_col(chunk, x, y)) : 0u);
+					    (uint16_t)(((crossed_cols[lane] >> j) & 1u) ? col_crossed(flags, load_col(raw, x, y)) : 0u);
 				}
-			uint32_t ex = 0;
-			for (int col = 0; col < 256; col++) {
-				cpre[col] = (uint16_t)ex;
-				ex += (uint32_t)popc32(Cz[col]);
-			}
-			for (uint32_t t0 = 0; t0 < nts; t0 += kTileQuads) {
-				const uint32_t tn = std::min<uint32_t>(kTileQuads, nts - t0);
-				int cell[kLanes];
-				for (uint32_t lane = 0; lane < tn; lane++) cell[lane] = find_plant(s, (t0 + lane) >> 2);
-				unsigned char *g = out_t + (base_t + t0) * (uint64_t)kQuadBytes;
-				unsigned char *stg = s.stage + ((uintptr_t)g & 8u);
-				for (uint32_t lane = 0; lane < tn; lane++)
-					expand_plant_quad(s, tab, chunk, cell[lane], (int)((t0 + lane) & 3u), stg + lane * kQuadBytes);
-				store_tile(g, stg, tn * kQuadBytes);
+			for (int lane = 0; lane < kLanes; lane++) {
+				const uint32_t mine = count_plants8(s, lane);
+				if (mine) emit_plant_descs(s, lane, desc_t.data() + (size_t)c * kDescStrideT + npl);
+				npl += mine;
 			}
 		}
+		cnt_i[c] = nq;
+		cnt_t[c] = npl * kPlantQuads;
 	}
-	totals[0] = run_q;
-	totals[1] = run_t;
 	delete sp;
+	// ---- expand kernel: scan, then tiles of 32 quads of the packed streams -----------------
+	std::vector<uint32_t> pre_i(n + 1), pre_t(n + 1);
+	pre_i[0] = pre_t[0] = 0;
+	for (uint32_t c = 0; c < n; c++) {
+		pre_i[c + 1] = pre_i[c] + cnt_i[c];
+		pre_t[c + 1] = pre_t[c] + cnt_t[c];
+		ranges_i[c].first_vertex = (uint64_t)pre_i[c] * 6; ranges_i[c].vertex_count = cnt_i[c] * 6; ranges_i[c].reserved = 0;
+		ranges_t[c].first_vertex = (uint64_t)pre_t[c] * 6; ranges_t[c].vertex_count = cnt_t[c] * 6; ranges_t[c].reserved = 0;
+	}
+	totals[0] = pre_i[n];
+	totals[1] = pre_t[n];
+	alignas(16) unsigned char stage[kStageBytes + 16];
+	for (int face = 1; face >= 0; face--) {
+		const std::vector<uint32_t> &pre = face ? pre_i : pre_t;
+		const uint32_t tot = pre[n];
+		unsigned char *out = face ? out_i : out_t;
+		if (tot > (face ? cap_i : cap_t)) continue;
+		for (uint32_t q0 = 0; q0 < tot; q0 += kTileQuads) {
+			const uint32_t tn = std::min<uint32_t>(kTileQuads, tot - q0);
+			unsigned char *g = out + (uint64_t)q0 * kQuadBytes;
+			unsigned char *stg = stage + ((uintptr_t)g & 8u);
+			for (uint32_t lane = 0; lane < tn; lane++) {
+				const uint32_t q = q0 + lane;
+				const uint32_t c = (uint32_t)(std::upper_bound(pre.begin(), pre.begin() + n, q) - pre.begin()) - 1;  // largest c with pre[c] <= q
+				const uint32_t r = q - pre[c];
+				const long long ox = offs[3 * c], oy = offs[3 * c + 1], oz = offs[3 * c + 2];
+				if (face) expand_face_desc(tab, ox, oy, oz, desc_i[(size_t)c * kDescStrideI + r], stg + lane * kQuadBytes);
+				else expand_plant_desc(tab, ox, oy, oz, desc_t[(size_t)c * kDescStrideT + (r >> 2)], (int)(q & 3u), stg + lane * kQuadBytes);
+			}
+			store_tile(g, stg, tn * kQuadBytes);
+		}
+	}
 	return 0;
 }
