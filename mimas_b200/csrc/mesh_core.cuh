@@ -67,9 +67,12 @@ constexpr uint32_t kDescStrideT = 4096;
 struct TabEntry {
 	uint32_t x, y;
 };
-// Per-id flag byte derived from the table: bit 0 = blocky, bit 5 = crossed.  Summed over the
-// 16 cells of a column the low 5 bits count blocky cells and bits 5.. count crossed cells.
-constexpr uint32_t kFlagBlocky = 1u, kFlagCrossed = 32u;
+// Per-id flag byte derived from the table (build_flags): bit 0 = blocky, bit 1 = crossed, bits 2..4 =
+// this blocky id shares its sides / top / bottom texture with a *different* blocky id.  Where no cell
+// of a chunk has such a bit, "different block ids" already means "different textures" and the run
+// merging never needs to look a texture up.
+constexpr uint32_t kFlagBlocky = 1u, kFlagCrossed = 2u, kFlagAmbSides = 4u, kFlagAmbTop = 8u, kFlagAmbBottom = 16u;
+constexpr uint32_t kFlagAmbAny = kFlagAmbSides | kFlagAmbTop | kFlagAmbBottom;
 
 // 16 block ids of one column (x, y), z = 0..15: byte z&3 of word z>>2 (map.rs:83-86).
 struct Col {
@@ -80,17 +83,18 @@ struct Col {
 struct alignas(128) WarpSmem {
 	// the chunk itself, filled by one bulk async copy (TMA)
 	alignas(128) unsigned char raw[4096];
-	// id-equality masks of phase A (Ey: vs column (x, y-1), Ex: vs (x-1, y)), [x*16 + y];
-	// dead after phase B: the same bytes then hold Cz, the crossed mask over z per column
+	// phases A-B: id-equality masks (Ey: vs column (x, y-1), Ex: vs (x-1, y)), [x*16 + y];
+	// phase D: the same bytes hold wl, the list of non-empty 32-bit words of S (two rows each);
+	// plants: Cz, the crossed mask over z per column
 	alignas(16) uint16_t Ey[256];
 	alignas(16) uint16_t Ex[256];
+	uint16_t wl_tail[256];                     // wl = Ey | Ex | wl_tail: 768 entries
 	// run-start masks over z per column: passes 1,3,4,6 (p = 0,2,3,5) at [p][x*16 + y],
 	// passes 2,5 (p = 1,4) at [p][y*16 + x]; every 16-entry block [p][c1*16 ..] is one
 	// (pass, c1) group whose 16 x 16 bit transpose gives the masks over the merge axis
 	alignas(16) uint16_t S[kPasses * 256];
 	alignas(16) uint16_t By[256];              // blocky mask over y for row (x, z): [x*16 + z]
 	alignas(16) uint16_t Bx[256];              // blocky mask over x for row (y, z): [y*16 + z]
-	alignas(16) uint16_t gpre[128];            // exclusive quad prefix per group
 	alignas(16) uint16_t Bzp[kBzStride * kBzStride + 4];  // blocky mask over z per column, zero border
 	alignas(8) unsigned long long mbar;        // mbarrier of the chunk load (device only)
 };
@@ -101,6 +105,9 @@ MM_HD unsigned char *smem_raw(WarpSmem &s) { return s.raw; }
 MM_HD uint16_t *smem_Bzp(WarpSmem &s) { return s.Bzp; }
 MM_HD const uint16_t *smem_Bzp(const WarpSmem &s) { return s.Bzp; }
 MM_HD uint16_t *smem_Cz(WarpSmem &s) { return s.Ey; }           // crossed mask over z per column (plants phase)
+MM_HD uint16_t *smem_wl(WarpSmem &s) { return s.Ey; }           // non-empty words of S in emission order (phase D)
+MM_HD const uint16_t *smem_wl(const WarpSmem &s) { return s.Ey; }
+static_assert(sizeof(uint16_t) * (256 + 256 + 256) == 1536, "wl spans Ey, Ex and wl_tail");
 
 MM_HD int popc32(uint32_t v) {
 #if defined(__CUDA_ARCH__)
@@ -168,6 +175,22 @@ MM_HD uint32_t f2u(float f) {
 // mimas-meshgen/lib.rs:123-131 `zsig` (NOT signum: +-0 -> +0)
 MM_HD float zsig(float v) { return v > 0.0f ? 1.0f : (v < 0.0f ? -1.0f : 0.0f); }
 
+// Flag bytes of a 256-entry table (host side of mm_set_block_table; also used by the emulation).
+static inline void build_flags(const TabEntry *tab, uint8_t *flags) {
+	for (int i = 0; i < 256; i++) {
+		const uint32_t kind = tab[i].y >> 16;
+		uint32_t f = kind == 1 ? kFlagBlocky : kind == 2 ? kFlagCrossed : 0u;
+		if (kind == 1)
+			for (int j = 0; j < 256; j++) {
+				if (j == i || (tab[j].y >> 16) != 1) continue;
+				if ((tab[i].x & 0xffffu) == (tab[j].x & 0xffffu)) f |= kFlagAmbSides;
+				if ((tab[i].x >> 16) == (tab[j].x >> 16)) f |= kFlagAmbTop;
+				if ((tab[i].y & 0xffffu) == (tab[j].y & 0xffffu)) f |= kFlagAmbBottom;
+			}
+		flags[i] = (uint8_t)f;
+	}
+}
+
 // ---- warp set-up ---------------------------------------------------------------------
 // Once per warp: the zero border of Bzp (a neighbour outside the chunk never blocks,
 // lib.rs:277-280); the interior is rewritten by phase A for every chunk.
@@ -185,20 +208,21 @@ MM_HD void init_warp_smem(WarpSmem &s, int lane) {
 
 // ---- phase A: one column (x, y) ------------------------------------------------------
 // Blocky mask over z (bit z <=> cell (x, y, z) is drawn as a cube, i.e. get_bl_tex_ids is
-// Some, lib.rs:105-109) in the return value; `sum` receives the flag sum of the column
-// (sum >> 5 = number of crossed cells).  flags = 256-entry byte table (see kFlagBlocky).
-MM_HD uint32_t col_flags(const uint8_t *flags, const Col &c, uint32_t &sum) {
-	uint32_t acc = 0, sm = 0;
+// Some, lib.rs:105-109) in the return value; `orf` receives the OR of the column's flag bytes.
+// flags = 256-entry byte table (see kFlagBlocky).
+MM_HD uint32_t col_flags(const uint8_t *flags, const Col &c, uint32_t &orf) {
+	uint32_t acc = 0, o = 0;
 #pragma unroll
 	for (int k = 0; k < 4; k++) {
 #pragma unroll
-		for (int b = 0; b < 4; b++) {
-			const uint32_t f = flags[(c.w[k] >> (8 * b)) & 0xffu];
-			acc = funnel_r1(acc, f);  // bit 0 of f enters at bit 31
-			sm += f;
+		for (int b = 0; b < 4; b += 2) {
+			const uint32_t f0 = flags[(c.w[k] >> (8 * b)) & 0xffu], f1 = flags[(c.w[k] >> (8 * b + 8)) & 0xffu];
+			acc = funnel_r1(acc, f0);  // bit 0 of f enters at bit 31
+			acc = funnel_r1(acc, f1);
+			o |= f0 | f1;
 		}
 	}
-	sum = sm;
+	orf = o;
 	return acc >> 16;
 }
 
@@ -237,7 +261,7 @@ MM_HD uint32_t col_crossed(const uint8_t *flags, const Col &c) {
 	uint32_t m = 0;
 #pragma unroll
 	for (int z = 0; z < 16; z++)
-		m |= ((flags[(c.w[z >> 2] >> (8 * (z & 3))) & 0xffu] >> 5) & 1u) << z;
+		m |= ((flags[(c.w[z >> 2] >> (8 * (z & 3))) & 0xffu] >> 1) & 1u) << z;
 	return m;
 }
 
@@ -263,7 +287,8 @@ MM_HD uint32_t fix_equal(const TabEntry *tab, const uint8_t *chunk, uint32_t d, 
 	return eq;
 }
 
-MM_HD void col_starts(WarpSmem &s, const TabEntry *tab, const uint8_t *chunk, int x, int y) {
+// `amb` = OR of the flag bytes of every cell of the chunk.
+MM_HD void col_starts(WarpSmem &s, const TabEntry *tab, const uint8_t *chunk, int x, int y, uint32_t amb) {
 	const uint16_t *B = smem_Bzp(s) + (x + 1) * kBzStride + (y + 1);
 	const uint32_t b = B[0];
 	const uint32_t bym = B[-1], byp = B[1], bxm = B[-kBzStride], bxp = B[kBzStride];
@@ -280,13 +305,16 @@ MM_HD void col_starts(WarpSmem &s, const TabEntry *tab, const uint8_t *chunk, in
 	const uint32_t Q3 = V3 & bym & ~bmm, Q6 = V6 & bym & ~bpm;
 	const uint32_t Q2 = V2 & bxm & ~bmm, Q5 = V5 & bxm & ~bmp;
 	uint32_t e1 = ey, e3 = ey, e4 = ey, e6 = ey, e2 = ex, e5 = ex;
-	if (((Q1 | Q3 | Q4 | Q6) & ~ey) | ((Q2 | Q5) & ~ex)) {  // rare: visible neighbours with different ids
-		e1 |= fix_equal(tab, chunk, Q1 & ~ey, x, y, x, y - 1, 2);  // id_bottom, lib.rs:329
-		e3 |= fix_equal(tab, chunk, Q3 & ~ey, x, y, x, y - 1, 0);  // id_sides,  lib.rs:361
-		e4 |= fix_equal(tab, chunk, Q4 & ~ey, x, y, x, y - 1, 1);  // id_top,    lib.rs:377
-		e6 |= fix_equal(tab, chunk, Q6 & ~ey, x, y, x, y - 1, 0);  // id_sides,  lib.rs:409
-		e2 |= fix_equal(tab, chunk, Q2 & ~ex, x, y, x - 1, y, 0);  // id_sides,  lib.rs:345
-		e5 |= fix_equal(tab, chunk, Q5 & ~ex, x, y, x - 1, y, 0);  // id_sides,  lib.rs:393
+	// rare: visible neighbours with different ids in a chunk where different ids may share a texture
+	if ((amb & kFlagAmbAny) && (((Q1 | Q3 | Q4 | Q6) & ~ey) | ((Q2 | Q5) & ~ex))) {
+		if (amb & kFlagAmbBottom) e1 |= fix_equal(tab, chunk, Q1 & ~ey, x, y, x, y - 1, 2);  // id_bottom, lib.rs:329
+		if (amb & kFlagAmbTop) e4 |= fix_equal(tab, chunk, Q4 & ~ey, x, y, x, y - 1, 1);     // id_top,    lib.rs:377
+		if (amb & kFlagAmbSides) {
+			e3 |= fix_equal(tab, chunk, Q3 & ~ey, x, y, x, y - 1, 0);  // id_sides,  lib.rs:361
+			e6 |= fix_equal(tab, chunk, Q6 & ~ey, x, y, x, y - 1, 0);  // id_sides,  lib.rs:409
+			e2 |= fix_equal(tab, chunk, Q2 & ~ex, x, y, x - 1, y, 0);  // id_sides,  lib.rs:345
+			e5 |= fix_equal(tab, chunk, Q5 & ~ex, x, y, x - 1, y, 0);  // id_sides,  lib.rs:393
+		}
 	}
 	const int row = y * 16 + x;
 	s.S[0 * 256 + col] = (uint16_t)(V1 & ~(Q1 & e1));
@@ -351,66 +379,72 @@ MM_HD void transpose_blocky(WarpSmem &s, int job) {
 	for (int k = 0; k < 8; k++) p[k] = w[k];
 }
 
-// Number of run starts (= quads) of group m = pass*16 + c1: a transpose moves bits, it does
-// not change how many there are, so the z-masks can be counted as they stand.
-MM_HD uint32_t count_group(const WarpSmem &s, int m) {
-	const uint32_t *p = reinterpret_cast<const uint32_t *>(s.S + m * 16);
-	uint32_t c = 0;
+// Transposes the 16-entry block at S[m*16 ..] in place: from masks over z per column to masks
+// over the merge axis per row c2, i.e. word k of the block = rows 2k (low half) and 2k+1 (high
+// half) of group m = pass*16 + c1 in emission order.  Returns quads | non-empty words << 16.
+MM_HD uint32_t transpose_group(WarpSmem &s, int m) {
+	uint32_t *p = reinterpret_cast<uint32_t *>(s.S + m * 16);
+	uint32_t w[8];
+	uint32_t any = 0;
 #pragma unroll
-	for (int k = 0; k < 8; k++) c += (uint32_t)popc32(p[k]);
-	return c;
+	for (int k = 0; k < 8; k++) {
+		w[k] = p[k];
+		any |= w[k];
+	}
+	if (any == 0) return 0;
+	transpose16(w);
+	uint32_t r = 0;
+#pragma unroll
+	for (int k = 0; k < 8; k++) {
+		p[k] = w[k];
+		r += (uint32_t)popc32(w[k]) + (w[k] ? 0x10000u : 0u);
+	}
+	return r;
+}
+
+// Appends the indices (m*8 + k) of the non-empty words of group m to wl, starting at entry o.
+MM_HD void list_group_words(WarpSmem &s, int m, uint32_t o) {
+	const uint32_t *p = reinterpret_cast<const uint32_t *>(s.S + m * 16);
+	uint16_t *wl = smem_wl(s);
+#pragma unroll
+	for (int k = 0; k < 8; k++) {
+		if (p[k]) wl[o++] = (uint16_t)(m * 8 + k);
+	}
 }
 
 // ---- phase D: quad descriptors --------------------------------------------------------
 // One 32-bit word per quad of the six face passes:
 //   bits 0-7 block id of the run's first cell | 8-11 start (inner coordinate) | 12-15 c2 |
 //   16-19 c1 | 20-22 pass (0..5) | 23-27 run length (1..16)
-MM_HD uint32_t pack_face_desc(uint32_t id, int st, int c2, int m, int len) {
-	return id | ((uint32_t)st << 8) | ((uint32_t)c2 << 12) | ((uint32_t)m << 16) | ((uint32_t)len << 23);
-}
-
-// Writes the descriptors of group m in emission order (rows c2 ascending, runs ascending,
-// lib.rs:294-313) to dst[0..count_group(m)).  The group's 16 z-masks are transposed in
-// registers into masks over the merge axis; a run (lib.rs:244-271) ends where the next one
-// starts or where the face stops being visible.
-MM_HD void emit_group_descs(const WarpSmem &s, int m, uint32_t *dst) {
-	const uint32_t *sp = reinterpret_cast<const uint32_t *>(s.S + m * 16);
-	uint32_t w[8];
-#pragma unroll
-	for (int k = 0; k < 8; k++) w[k] = sp[k];
-	transpose16(w);
+// Writes the descriptors of the runs starting in word `widx` of S (rows c2 = 2k and 2k+1 of
+// group m, widx = m*8 + k; `word` = that word, non-zero) in emission order (rows ascending,
+// runs ascending, lib.rs:294-313) to dst[0..popc(word)).  A run (lib.rs:244-271) ends where
+// the next one starts, where the face stops being visible, or at the end of the row.
+MM_HD void emit_word_descs(const WarpSmem &s, uint32_t widx, uint32_t word, uint32_t *dst) {
+	const int m = (int)(widx >> 3), c2lo = (int)(widx & 7u) * 2;
 	const int p = m >> 4, c1 = m & 15;
 	const bool xin = (p == 1 || p == 4);
-	// visibility over the merge axis of row (c1, c2) = blocky & ~blocky of the neighbour row
-	// in the pass direction (SURVEY.md 8a pass table); `has_nb` bit c2: that row is inside the chunk
-	const uint16_t *Bm = (xin ? s.Bx : s.By) + c1 * 16;
-	int delta;
-	uint32_t has_nb;
-	if (p == 0) { delta = -1; has_nb = 0xfffeu; }                        // [0,0,-1]
-	else if (p == 3) { delta = 1; has_nb = 0x7fffu; }                    // [0,0,1]
-	else if (p == 1 || p == 2) { delta = -16; has_nb = c1 > 0 ? 0xffffu : 0u; }   // [0,-1,0] / [-1,0,0]
-	else { delta = 16; has_nb = c1 < 15 ? 0xffffu : 0u; }                // [0,1,0] / [1,0,0]
-	const int cell_row = xin ? c1 * 16 : c1 * 256;   // + st*256 (x-inner) or st*16 (y-inner) + c2
-	const int cell_shift = xin ? 8 : 4;
-#pragma unroll
-	for (int k = 0; k < 8; k++) {
-#pragma unroll
-		for (int hf = 0; hf < 2; hf++) {
-			const int c2 = 2 * k + hf;
-			uint32_t rest = hf ? (w[k] >> 16) : (w[k] & 0xffffu);
-			if (rest == 0) continue;
-			const uint32_t b = Bm[c2];
-			const uint32_t nb = ((has_nb >> c2) & 1u) ? (uint32_t)Bm[c2 + delta] : 0u;
-			const uint32_t T = ((rest | ~(b & ~nb)) & 0xffffu) | 0x10000u;  // run boundaries: start | not visible | end of row
-			do {
-				const int st = ffs32(rest) - 1;
-				rest &= rest - 1u;
-				const int len = ffs32(T >> (st + 1));
-				const uint32_t id = s.raw[cell_row + (st << cell_shift) + c2];
-				*dst++ = pack_face_desc(id, st, c2, m, len);
-			} while (rest);
-		}
-	}
+	// visibility over the merge axis of row (c1, c2) = blocky & ~blocky of the neighbour row in the
+	// pass direction (SURVEY.md 8a pass table), for the two rows of the word at once
+	const uint16_t *Bm = (xin ? s.Bx : s.By) + c1 * 16 + c2lo;
+	const uint32_t b = *reinterpret_cast<const uint32_t *>(Bm);
+	uint32_t nb;
+	if (p == 0) nb = (b << 16) | (c2lo > 0 ? (uint32_t)Bm[-1] : 0u);                   // [0,0,-1]: row c2-1
+	else if (p == 3) nb = (b >> 16) | (c2lo < 14 ? (uint32_t)Bm[2] << 16 : 0u);        // [0,0,1]:  row c2+1
+	else if (p == 1 || p == 2) nb = c1 > 0 ? *reinterpret_cast<const uint32_t *>(Bm - 16) : 0u;   // [0,-1,0] / [-1,0,0]
+	else nb = c1 < 15 ? *reinterpret_cast<const uint32_t *>(Bm + 16) : 0u;             // [0,1,0] / [1,0,0]
+	const uint32_t T = (word | ~(b & ~nb) | 0x10000u) >> 1;  // run boundaries: start | not visible | end of the low row
+	const uint32_t base = ((uint32_t)m << 16) | ((uint32_t)c2lo << 12);
+	const int cell0 = (xin ? c1 * 16 : c1 * 256) + c2lo;   // + st*256 (x-inner) or st*16 (y-inner) + (c2 & 1)
+	const int sh = xin ? 8 : 4;
+	uint32_t rest = word;
+	do {
+		const int bit = ffs32(rest) - 1;  // = (c2 & 1) * 16 + st
+		rest &= rest - 1u;
+		const int len = ffs32((T >> bit) | (0x80000000u >> bit));  // .. | end of the high row
+		const uint32_t id = s.raw[cell0 + ((bit & 15) << sh) + (bit >> 4)];
+		*dst++ = base | ((uint32_t)bit << 8) | ((uint32_t)len << 23) | id;
+	} while (rest);
 }
 
 // Crossed plants (lib.rs:412-440), x outer, y, z inner = linear cell order.  Cz[col] = crossed

@@ -175,52 +175,66 @@ __global__ void __launch_bounds__(kThreads, 2) analyse_kernel(const AnalyseParam
 		parity ^= 1u;
 
 		// A. lane (h, y) owns columns (x = 2j + h, y), j = 0..7: blocky masks and id-equality masks
-		uint32_t anyb = 0, crossed_cols = 0, ncrossed = 0;
+		uint32_t anyb = 0, crossed_cols = 0, amb = 0;
 #pragma unroll 2
 		for (int j = 0; j < 8; j++) {
 			const int col = 32 * j + lane;
 			const Col own = lds_col(raw + col * 16);
 			const Col ny = lds_col(raw + ((col - 1) & 255) * 16);   // (x, y-1); unused garbage for y = 0
 			const Col nx = lds_col(raw + ((col - 16) & 255) * 16);  // (x-1, y); unused garbage for x = 0
-			uint32_t sum;
-			const uint32_t bz = col_flags(flags, own, sum);
+			uint32_t orf;
+			const uint32_t bz = col_flags(flags, own, orf);
 			smem_Bzp(s)[(2 * j + h + 1) * kBzStride + y + 1] = (uint16_t)bz;
 			smem_Ey(s)[col] = (uint16_t)eq_mask16(own, ny);
 			smem_Ex(s)[col] = (uint16_t)eq_mask16(own, nx);
 			anyb |= bz;
-			crossed_cols |= ((sum >> 5) ? 1u : 0u) << j;
-			ncrossed += sum >> 5;
+			crossed_cols |= ((orf >> 1) & 1u) << j;
+			amb |= orf;
 		}
+		amb = __reduce_or_sync(full, amb);
 		uint32_t nq = 0, npl = 0;
-		uint32_t *di = p.desc_i + (size_t)c * kDescStrideI;
-		if (__any_sync(full, anyb != 0u)) {  // else: no cube in the chunk (e.g. all air)
+		if (amb & kFlagBlocky) {  // else: no cube in the chunk (e.g. all air)
+			uint32_t *di = p.desc_i + (size_t)c * kDescStrideI;
 			__syncwarp();
 			// B. run starts over z for the six passes
 #pragma unroll 1
-			for (int j = 0; j < 8; j++) col_starts(s, tab, raw, 2 * j + h, y);
+			for (int j = 0; j < 8; j++) col_starts(s, tab, raw, 2 * j + h, y, amb);
 			__syncwarp();
-			// C. blocky masks over the merge axes; quads per group; scan in emission order
+			// C. masks over the merge axes; quads and non-empty words per group; scans in emission order
 			transpose_blocky(s, lane);
-			uint32_t cnt[3], run = 0;
+			uint32_t tc[3], wofs[3], run = 0;
 #pragma unroll
 			for (int k = 0; k < 3; k++) {
-				cnt[k] = count_group(s, lane + 32 * k);
-				const uint32_t inc = warp_incl_scan(cnt[k], lane);
-				const uint32_t ex = run + inc - cnt[k];
+				tc[k] = transpose_group(s, lane + 32 * k);
+				const uint32_t inc = warp_incl_scan(tc[k], lane);  // quads (low half) and words (high half) at once
+				wofs[k] = (run + inc - tc[k]) >> 16;
 				run += __shfl_sync(full, inc, 31);
-				cnt[k] = cnt[k] ? ex : 0xffffffffu;  // from here on: the group's offset, or "empty"
 			}
-			nq = run;
-			__syncwarp();  // By / Bx complete
-			// D. descriptors, group by group
+			nq = run & 0xffffu;
+			const uint32_t nwords = run >> 16;
+			__syncwarp();  // Ey / Ex are dead: wl takes their place
+#pragma unroll
+			for (int k = 0; k < 3; k++)
+				if (tc[k]) list_group_words(s, lane + 32 * k, wofs[k]);
+			__syncwarp();
+			// D. descriptors: lane <-> non-empty word (two rows), 32 words at a time
+			uint32_t qbase = 0;
 #pragma unroll 1
-			for (int k = 0; k < 3; k++) {
-				const uint32_t off = k == 0 ? cnt[0] : k == 1 ? cnt[1] : cnt[2];
-				if (off != 0xffffffffu) emit_group_descs(s, lane + 32 * k, di + off);
+			for (uint32_t i0 = 0; i0 < nwords; i0 += 32) {
+				const uint32_t i = i0 + (uint32_t)lane;
+				uint32_t widx = 0, word = 0;
+				if (i < nwords) {
+					widx = smem_wl(s)[i];
+					word = reinterpret_cast<const uint32_t *>(s.S)[widx];
+				}
+				const uint32_t cnt = (uint32_t)__popc(word);
+				const uint32_t inc = warp_incl_scan(cnt, lane);
+				if (word) emit_word_descs(s, widx, word, di + qbase + inc - cnt);
+				qbase += __shfl_sync(full, inc, 31);
 			}
 		}
-		if (__any_sync(full, crossed_cols != 0u)) {
-			__syncwarp();  // Ey / Ex are dead (phase B is done): Cz takes their place
+		if (amb & kFlagCrossed) {
+			__syncwarp();  // wl is dead: Cz takes its place
 			uint16_t *Cz = smem_Cz(s);
 #pragma unroll 1
 			for (int j = 0; j < 8; j++) {

@@ -326,8 +326,8 @@ int mm_set_block_table(mm_ctx *c, const mm_block_entry table[MM_TABLE_ENTRIES]) 
 		else t[i].x = (uint32_t)e.id_sides | ((uint32_t)e.id_top << 16);
 		t[i].y = (uint32_t)e.id_bottom | ((uint32_t)e.kind << 16);
 		if (e.kind == MM_KIND_NONE) { t[i].x = 0; t[i].y = 0; }
-		fl[i] = e.kind == MM_KIND_BLOCKY ? mm::kFlagBlocky : e.kind == MM_KIND_CROSSED ? mm::kFlagCrossed : 0;
 	}
+	mm::build_flags(t, fl);
 	MM_CUDA(c, cudaStreamSynchronize(c->stream));
 	MM_CUDA(c, cudaMemcpy(c->d_table, t, sizeof(t), cudaMemcpyHostToDevice));
 	MM_CUDA(c, cudaMemcpy(c->d_flags, fl, sizeof(fl), cudaMemcpyHostToDevice));

@@ -55,10 +55,7 @@ extern "C" int emul_mesh_batch(const uint8_t *chunks, const int64_t *offs, uint3
 	WarpSmem &s = *sp;
 	memset(&s, 0xA5, sizeof(s));  // nothing may depend on stale shared memory
 	uint8_t flags[256];
-	for (int i = 0; i < 256; i++) {
-		const uint32_t kind = tab[i].y >> 16;
-		flags[i] = kind == 1 ? kFlagBlocky : kind == 2 ? kFlagCrossed : 0;
-	}
+	build_flags(tab, flags);
 	for (int lane = 0; lane < kLanes; lane++) init_warp_smem(s, lane);
 	// ---- analyse kernel: one warp per chunk -> counts + descriptors ----------------------
 	std::vector<uint32_t> desc_i((size_t)n * kDescStrideI, 0xDEADBEEFu), desc_t((size_t)n * kDescStrideT, 0xDEADBEEFu);
@@ -68,7 +65,7 @@ extern "C" int emul_mesh_batch(const uint8_t *chunks, const int64_t *offs, uint3
 		memcpy(smem_raw(s), chunk, 4096);  // the bulk async copy of the kernel
 		const uint8_t *raw = smem_raw(s);
 		// A
-		uint32_t anyb = 0;
+		uint32_t amb = 0;
 		uint32_t crossed_cols[kLanes] = {0};
 		for (int j = 0; j < 8; j++)
 			for (int lane = 0; lane < kLanes; lane++) {
@@ -77,34 +74,41 @@ extern "C" int emul_mesh_batch(const uint8_t *chunks, const int64_t *offs, uint3
 				Col ny, nx;  // what the kernel loads: wrapped-around garbage at y = 0 / x = 0
 				memcpy(ny.w, raw + ((col - 1) & 255) * 16, 16);
 				memcpy(nx.w, raw + ((col - 16) & 255) * 16, 16);
-				uint32_t sum;
-				const uint32_t bz = col_flags(flags, own, sum);
+				uint32_t orf;
+				const uint32_t bz = col_flags(flags, own, orf);
 				smem_Bzp(s)[(x + 1) * kBzStride + y + 1] = (uint16_t)bz;
 				smem_Ey(s)[col] = (uint16_t)eq_mask16(own, ny);
 				smem_Ex(s)[col] = (uint16_t)eq_mask16(own, nx);
-				anyb |= bz;
-				crossed_cols[lane] |= ((sum >> 5) ? 1u : 0u) << j;
+				crossed_cols[lane] |= ((orf >> 1) & 1u) << j;
+				amb |= orf;
 			}
-		uint32_t anyc = 0;
-		for (int lane = 0; lane < kLanes; lane++) anyc |= crossed_cols[lane];
 		uint32_t nq = 0, npl = 0;
 		uint32_t *di = desc_i.data() + (size_t)c * kDescStrideI;
-		if (anyb) {
+		if (amb & kFlagBlocky) {
 			// B
 			for (int j = 0; j < 8; j++)
-				for (int lane = 0; lane < kLanes; lane++) col_starts(s, tab, raw, 2 * j + (lane >> 4), lane & 15);
+				for (int lane = 0; lane < kLanes; lane++) col_starts(s, tab, raw, 2 * j + (lane >> 4), lane & 15, amb);
 			// C
 			for (int lane = 0; lane < kLanes; lane++) transpose_blocky(s, lane);
-			uint32_t gofs[kGroups];
+			uint32_t tc[kGroups], wofs[kGroups], nwords = 0;
+			for (int m = 0; m < kGroups; m++) tc[m] = transpose_group(s, m);
 			for (int m = 0; m < kGroups; m++) {
-				gofs[m] = nq;
-				nq += count_group(s, m);
+				wofs[m] = nwords;
+				nq += tc[m] & 0xffffu;
+				nwords += tc[m] >> 16;
 			}
-			// D
 			for (int m = 0; m < kGroups; m++)
-				if (count_group(s, m)) emit_group_descs(s, m, di + gofs[m]);
+				if (tc[m]) list_group_words(s, m, wofs[m]);
+			// D
+			uint32_t qbase = 0;
+			for (uint32_t i = 0; i < nwords; i++) {
+				const uint32_t widx = smem_wl(s)[i];
+				const uint32_t word = reinterpret_cast<const uint32_t *>(s.S)[widx];
+				emit_word_descs(s, widx, word, di + qbase);
+				qbase += (uint32_t)popc32(word);
+			}
 		}
-		if (anyc) {
+		if (amb & kFlagCrossed) {
 			uint16_t *Cz = smem_Cz(s);
 			for (int j = 0; j < 8; j++)
 				for (int lane = 0; lane < kLanes; lane++) {
