@@ -79,16 +79,15 @@ struct Col {
 	uint32_t w[4];
 };
 
-// Shared memory of one analysing warp.  Plain struct so that host emulation can allocate it.
-struct alignas(128) WarpSmem {
+// Shared memory of one analysing CTA (= one chunk in flight).  Plain struct so that host
+// emulation can allocate it.
+struct alignas(128) ChunkSmem {
 	// the chunk itself, filled by one bulk async copy (TMA)
 	alignas(128) unsigned char raw[4096];
-	// phases A-B: id-equality masks (Ey: vs column (x, y-1), Ex: vs (x-1, y)), [x*16 + y];
-	// phase D: the same bytes hold wl, the list of non-empty 32-bit words of S (two rows each);
+	// phases A-B: id-equality masks Ey (vs column (x, y-1)) and Ex (vs (x-1, y)), [x*16 + y], 2 x 512 B;
+	// phase D: wl, the list of non-empty 32-bit words of S (two rows each) with their quad offsets;
 	// plants: Cz, the crossed mask over z per column
-	alignas(16) uint16_t Ey[256];
-	alignas(16) uint16_t Ex[256];
-	uint16_t wl_tail[256];                     // wl = Ey | Ex | wl_tail: 768 entries
+	alignas(16) uint32_t u[768];
 	// run-start masks over z per column: passes 1,3,4,6 (p = 0,2,3,5) at [p][x*16 + y],
 	// passes 2,5 (p = 1,4) at [p][y*16 + x]; every 16-entry block [p][c1*16 ..] is one
 	// (pass, c1) group whose 16 x 16 bit transpose gives the masks over the merge axis
@@ -96,18 +95,23 @@ struct alignas(128) WarpSmem {
 	alignas(16) uint16_t By[256];              // blocky mask over y for row (x, z): [x*16 + z]
 	alignas(16) uint16_t Bx[256];              // blocky mask over x for row (y, z): [y*16 + z]
 	alignas(16) uint16_t Bzp[kBzStride * kBzStride + 4];  // blocky mask over z per column, zero border
+	alignas(16) uint32_t gcnt[kGroups];        // per group: quads | non-empty words << 16; then the exclusive prefix of that
+	uint32_t nq, nwords, npl;                  // totals of the chunk
+	uint32_t amb[2];                           // OR of the flag bytes of the chunk's cells (double buffered)
+	uint32_t ticket[2];                        // chunk index of this / the next round (double buffered)
 	alignas(8) unsigned long long mbar;        // mbarrier of the chunk load (device only)
 };
 
-MM_HD uint16_t *smem_Ey(WarpSmem &s) { return s.Ey; }
-MM_HD uint16_t *smem_Ex(WarpSmem &s) { return s.Ex; }
-MM_HD unsigned char *smem_raw(WarpSmem &s) { return s.raw; }
-MM_HD uint16_t *smem_Bzp(WarpSmem &s) { return s.Bzp; }
-MM_HD const uint16_t *smem_Bzp(const WarpSmem &s) { return s.Bzp; }
-MM_HD uint16_t *smem_Cz(WarpSmem &s) { return s.Ey; }           // crossed mask over z per column (plants phase)
-MM_HD uint16_t *smem_wl(WarpSmem &s) { return s.Ey; }           // non-empty words of S in emission order (phase D)
-MM_HD const uint16_t *smem_wl(const WarpSmem &s) { return s.Ey; }
-static_assert(sizeof(uint16_t) * (256 + 256 + 256) == 1536, "wl spans Ey, Ex and wl_tail");
+MM_HD uint16_t *smem_Ey(ChunkSmem &s) { return reinterpret_cast<uint16_t *>(s.u); }
+MM_HD uint16_t *smem_Ex(ChunkSmem &s) { return reinterpret_cast<uint16_t *>(s.u) + 256; }
+MM_HD unsigned char *smem_raw(ChunkSmem &s) { return s.raw; }
+MM_HD uint16_t *smem_Bzp(ChunkSmem &s) { return s.Bzp; }
+MM_HD const uint16_t *smem_Bzp(const ChunkSmem &s) { return s.Bzp; }
+MM_HD uint16_t *smem_Cz(ChunkSmem &s) { return reinterpret_cast<uint16_t *>(s.u); }   // crossed mask over z per column
+MM_HD const uint16_t *smem_Cz(const ChunkSmem &s) { return reinterpret_cast<const uint16_t *>(s.u); }
+// wl entry: index of a non-empty word of S (m*8 + k, 10 bits) | quads of the chunk before it << 10
+MM_HD uint32_t *smem_wl(ChunkSmem &s) { return s.u; }
+MM_HD const uint32_t *smem_wl(const ChunkSmem &s) { return s.u; }
 
 MM_HD int popc32(uint32_t v) {
 #if defined(__CUDA_ARCH__)
@@ -192,9 +196,9 @@ static inline void build_flags(const TabEntry *tab, uint8_t *flags) {
 }
 
 // ---- warp set-up ---------------------------------------------------------------------
-// Once per warp: the zero border of Bzp (a neighbour outside the chunk never blocks,
+// Once per CTA (lane = 0..31 of one warp): the zero border of Bzp (a neighbour outside the chunk never blocks,
 // lib.rs:277-280); the interior is rewritten by phase A for every chunk.
-MM_HD void init_warp_smem(WarpSmem &s, int lane) {
+MM_HD void init_warp_smem(ChunkSmem &s, int lane) {
 	uint16_t *B = smem_Bzp(s);
 	if (lane < kBzStride) {
 		B[lane] = 0;
@@ -288,7 +292,7 @@ MM_HD uint32_t fix_equal(const TabEntry *tab, const uint8_t *chunk, uint32_t d, 
 }
 
 // `amb` = OR of the flag bytes of every cell of the chunk.
-MM_HD void col_starts(WarpSmem &s, const TabEntry *tab, const uint8_t *chunk, int x, int y, uint32_t amb) {
+MM_HD void col_starts(ChunkSmem &s, const TabEntry *tab, const uint8_t *chunk, int x, int y, uint32_t amb) {
 	const uint16_t *B = smem_Bzp(s) + (x + 1) * kBzStride + (y + 1);
 	const uint32_t b = B[0];
 	const uint32_t bym = B[-1], byp = B[1], bxm = B[-kBzStride], bxp = B[kBzStride];
@@ -361,7 +365,7 @@ MM_HD void transpose16(uint32_t w[8]) {
 
 // Blocky masks over the merge axes, from the z-masks: job 0..15 -> By rows of x = job
 // (bits over y), job 16..31 -> Bx rows of y = job - 16 (bits over x).
-MM_HD void transpose_blocky(WarpSmem &s, int job) {
+MM_HD void transpose_blocky(ChunkSmem &s, int job) {
 	uint32_t w[8];
 	const bool over_y = job < 16;
 	const int f = job & 15;
@@ -382,7 +386,7 @@ MM_HD void transpose_blocky(WarpSmem &s, int job) {
 // Transposes the 16-entry block at S[m*16 ..] in place: from masks over z per column to masks
 // over the merge axis per row c2, i.e. word k of the block = rows 2k (low half) and 2k+1 (high
 // half) of group m = pass*16 + c1 in emission order.  Returns quads | non-empty words << 16.
-MM_HD uint32_t transpose_group(WarpSmem &s, int m) {
+MM_HD uint32_t transpose_group(ChunkSmem &s, int m) {
 	uint32_t *p = reinterpret_cast<uint32_t *>(s.S + m * 16);
 	uint32_t w[8];
 	uint32_t any = 0;
@@ -402,13 +406,18 @@ MM_HD uint32_t transpose_group(WarpSmem &s, int m) {
 	return r;
 }
 
-// Appends the indices (m*8 + k) of the non-empty words of group m to wl, starting at entry o.
-MM_HD void list_group_words(WarpSmem &s, int m, uint32_t o) {
+// Appends the non-empty words of group m to wl.  `pre` = quads | words << 16 of the groups before m.
+MM_HD void list_group_words(ChunkSmem &s, int m, uint32_t pre) {
 	const uint32_t *p = reinterpret_cast<const uint32_t *>(s.S + m * 16);
-	uint16_t *wl = smem_wl(s);
+	uint32_t *wl = smem_wl(s);
+	uint32_t o = pre >> 16, q = pre & 0xffffu;
 #pragma unroll
 	for (int k = 0; k < 8; k++) {
-		if (p[k]) wl[o++] = (uint16_t)(m * 8 + k);
+		const uint32_t w = p[k];
+		if (w) {
+			wl[o++] = (uint32_t)(m * 8 + k) | (q << 10);
+			q += (uint32_t)popc32(w);
+		}
 	}
 }
 
@@ -420,7 +429,7 @@ MM_HD void list_group_words(WarpSmem &s, int m, uint32_t o) {
 // group m, widx = m*8 + k; `word` = that word, non-zero) in emission order (rows ascending,
 // runs ascending, lib.rs:294-313) to dst[0..popc(word)).  A run (lib.rs:244-271) ends where
 // the next one starts, where the face stops being visible, or at the end of the row.
-MM_HD void emit_word_descs(const WarpSmem &s, uint32_t widx, uint32_t word, uint32_t *dst) {
+MM_HD void emit_word_descs(const ChunkSmem &s, uint32_t widx, uint32_t word, uint32_t *dst) {
 	const int m = (int)(widx >> 3), c2lo = (int)(widx & 7u) * 2;
 	const int p = m >> 4, c1 = m & 15;
 	const bool xin = (p == 1 || p == 4);
@@ -449,19 +458,19 @@ MM_HD void emit_word_descs(const WarpSmem &s, uint32_t widx, uint32_t word, uint
 
 // Crossed plants (lib.rs:412-440), x outer, y, z inner = linear cell order.  Cz[col] = crossed
 // mask over z of column col = x*16 + y; this lane covers columns lane*8 .. lane*8+7.
-MM_HD uint32_t count_plants8(const WarpSmem &s, int lane) {
-	const uint32_t *p = reinterpret_cast<const uint32_t *>(s.Ey + lane * 8);
+MM_HD uint32_t count_plants8(const ChunkSmem &s, int lane) {
+	const uint32_t *p = reinterpret_cast<const uint32_t *>(smem_Cz(s) + lane * 8);
 	uint32_t c = 0;
 #pragma unroll
 	for (int k = 0; k < 4; k++) c += (uint32_t)popc32(p[k]);
 	return c;
 }
 // Plant descriptor: bits 0-7 block id | 8-19 cell index.
-MM_HD void emit_plant_descs(const WarpSmem &s, int lane, uint32_t *dst) {
+MM_HD void emit_plant_descs(const ChunkSmem &s, int lane, uint32_t *dst) {
 #pragma unroll 1
 	for (int k = 0; k < 8; k++) {
 		const int col = lane * 8 + k;
-		uint32_t mask = s.Ey[col];
+		uint32_t mask = smem_Cz(s)[col];
 		while (mask) {
 			const int z = ffs32(mask) - 1;
 			mask &= mask - 1u;

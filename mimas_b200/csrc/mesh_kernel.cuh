@@ -23,15 +23,14 @@
 
 namespace mm {
 
-constexpr int kWarpsPerCta = 8;                  // analyse_kernel
+constexpr int kWarpsPerCta = 4;                  // analyse_kernel: one CTA per chunk in flight
 constexpr int kThreads = kWarpsPerCta * 32;
+constexpr int kAnalyseCtasPerSm = 8;
+static_assert(kThreads == 128, "phase C hands one of 32 + 96 jobs to every thread");
 constexpr int kExpandWarps = 16;                 // expand_kernel
 constexpr int kExpandThreads = kExpandWarps * 32;
-constexpr uint32_t kMaxLaunchChunks = 8192;      // the prefix of one launch lives in shared memory
-constexpr int kScanPerThread = kMaxLaunchChunks / kExpandThreads;  // 16
-constexpr size_t kAnalyseTableBytes = 2048 + 256;  // block table + flag bytes
-constexpr size_t kAnalyseSmemBytes = kAnalyseTableBytes + kWarpsPerCta * sizeof(WarpSmem);
-// expand: table | prefix_i[8192+4] | prefix_t[8192+4] | warp totals | stage tiles
+constexpr uint32_t kMaxLaunchChunks = 4096;      // the prefix of one launch lives in shared memory
+// expand: table | prefix_i[4096+4] | prefix_t[4096+4] | warp totals | stage tiles
 constexpr size_t kExpandPrefixWords = kMaxLaunchChunks + 4;
 constexpr size_t kExpandSmemBytes = 2048 + 2 * 4 * kExpandPrefixWords + 256 + kExpandWarps * (size_t)(kStageBytes + 16);
 
@@ -139,156 +138,198 @@ __device__ __forceinline__ void store_tile(unsigned char *g, const unsigned char
 }
 
 // ---- kernel 1: analysis ------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads, 2) analyse_kernel(const AnalyseParams p) {
-	extern __shared__ __align__(128) unsigned char smem_raw_bytes[];
-	TabEntry *tab = reinterpret_cast<TabEntry *>(smem_raw_bytes);
-	unsigned char *flags = smem_raw_bytes + 2048;
+// One CTA of kThreads threads per chunk in flight; CTAs are persistent and draw chunk tickets.
+__global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(const AnalyseParams p) {
+	__shared__ ChunkSmem s;
+	__shared__ __align__(16) unsigned char flags[256];
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-	WarpSmem &s = *reinterpret_cast<WarpSmem *>(smem_raw_bytes + kAnalyseTableBytes + (size_t)warp * sizeof(WarpSmem));
 	const unsigned full = 0xffffffffu;
 
 	pdl_launch_dependents();  // the expand kernel may set itself up while this one works
-	if (tid < 128) reinterpret_cast<uint4 *>(tab)[tid] = __ldg(reinterpret_cast<const uint4 *>(p.table) + tid);
 	if (tid < 16) reinterpret_cast<uint4 *>(flags)[tid] = __ldg(reinterpret_cast<const uint4 *>(p.flags) + tid);
-	init_warp_smem(s, lane);
-	if (lane == 0) {
+	if (warp == 1) init_warp_smem(s, lane);
+	if (tid == 0) {
 		mbar_init(&s.mbar);
 		fence_proxy_async_smem();  // the barrier is visible to the bulk-copy engine
+		s.ticket[0] = (uint32_t)min(atomicAdd(p.ticket, 1ull) - p.ticket_base, (u64)0xffffffffu);
+		s.amb[0] = 0;
 	}
-	__syncthreads();
-
-	const int h = lane >> 4, y = lane & 15;
 	unsigned char *raw = smem_raw(s);
-	uint32_t parity = 0;
-	u64 next = 0;
-	if (lane == 0) next = atomicAdd(p.ticket, 1ull) - p.ticket_base;
-	for (;;) {
-		const u64 ticket = __shfl_sync(full, next, 0);  // also orders the previous chunk's smem reads before this one's writes
-		if (ticket >= (u64)p.n) break;
-		const uint32_t c = (uint32_t)ticket;
-		const unsigned char *chunk = p.chunks + (size_t)c * 4096u;
-		if (lane == 0) {
-			bulk_load_g2s(raw, chunk, 4096u, &s.mbar);            // TMA: 4 KiB chunk -> shared memory
-			next = atomicAdd(p.ticket, 1ull) - p.ticket_base;     // the next ticket travels while this chunk is analysed
+	const TabEntry *tab = p.table;  // only read for chunks with ambiguous ids (fix_equal)
+	uint32_t par = 0;
+	for (;; par ^= 1u) {
+		__syncthreads();  // the previous chunk is done with shared memory; this round's ticket is visible
+		const uint32_t c = s.ticket[par];
+		if (c >= p.n) break;
+		if (tid == 0) {
+			bulk_load_g2s(raw, p.chunks + (size_t)c * 4096u, 4096u, &s.mbar);  // TMA: 4 KiB chunk -> shared memory
+			// the next ticket travels while this chunk is analysed
+			s.ticket[par ^ 1u] = (uint32_t)min(atomicAdd(p.ticket, 1ull) - p.ticket_base, (u64)0xffffffffu);
+			s.amb[par ^ 1u] = 0;
 		}
-		mbar_wait(&s.mbar, parity);
-		parity ^= 1u;
+		mbar_wait(&s.mbar, par);
 
-		// A. lane (h, y) owns columns (x = 2j + h, y), j = 0..7: blocky masks and id-equality masks
-		uint32_t anyb = 0, crossed_cols = 0, amb = 0;
-#pragma unroll 2
-		for (int j = 0; j < 8; j++) {
-			const int col = 32 * j + lane;
+		// A. thread <-> columns col = tid, tid + 128 (col = x*16 + y): blocky masks and id-equality masks
+		uint32_t crossed_cols = 0, amb = 0;
+#pragma unroll
+		for (int j = 0; j < 256 / kThreads; j++) {
+			const int col = kThreads * j + tid;
 			const Col own = lds_col(raw + col * 16);
 			const Col ny = lds_col(raw + ((col - 1) & 255) * 16);   // (x, y-1); unused garbage for y = 0
 			const Col nx = lds_col(raw + ((col - 16) & 255) * 16);  // (x-1, y); unused garbage for x = 0
 			uint32_t orf;
 			const uint32_t bz = col_flags(flags, own, orf);
-			smem_Bzp(s)[(2 * j + h + 1) * kBzStride + y + 1] = (uint16_t)bz;
+			smem_Bzp(s)[((col >> 4) + 1) * kBzStride + (col & 15) + 1] = (uint16_t)bz;
 			smem_Ey(s)[col] = (uint16_t)eq_mask16(own, ny);
 			smem_Ex(s)[col] = (uint16_t)eq_mask16(own, nx);
-			anyb |= bz;
 			crossed_cols |= ((orf >> 1) & 1u) << j;
 			amb |= orf;
 		}
 		amb = __reduce_or_sync(full, amb);
-		uint32_t nq = 0, npl = 0;
+		if (lane == 0 && amb) atomicOr(&s.amb[par], amb);
+		__syncthreads();
+		amb = s.amb[par];
 		if (amb & kFlagBlocky) {  // else: no cube in the chunk (e.g. all air)
 			uint32_t *di = p.desc_i + (size_t)c * kDescStrideI;
-			__syncwarp();
 			// B. run starts over z for the six passes
 #pragma unroll 1
-			for (int j = 0; j < 8; j++) col_starts(s, tab, raw, 2 * j + h, y, amb);
-			__syncwarp();
-			// C. masks over the merge axes; quads and non-empty words per group; scans in emission order
-			transpose_blocky(s, lane);
-			uint32_t tc[3], wofs[3], run = 0;
-#pragma unroll
-			for (int k = 0; k < 3; k++) {
-				tc[k] = transpose_group(s, lane + 32 * k);
-				const uint32_t inc = warp_incl_scan(tc[k], lane);  // quads (low half) and words (high half) at once
-				wofs[k] = (run + inc - tc[k]) >> 16;
-				run += __shfl_sync(full, inc, 31);
+			for (int j = 0; j < 256 / kThreads; j++) {
+				const int col = kThreads * j + tid;
+				col_starts(s, tab, raw, col >> 4, col & 15, amb);
 			}
-			nq = run & 0xffffu;
-			const uint32_t nwords = run >> 16;
-			__syncwarp();  // Ey / Ex are dead: wl takes their place
+			__syncthreads();
+			// C. masks over the merge axes: 32 blocky jobs + 96 groups = one job per thread
+			if (tid < 32) transpose_blocky(s, tid);
+			else s.gcnt[tid - 32] = transpose_group(s, tid - 32);
+			__syncthreads();
+			if (warp == 0) {  // exclusive scan of quads (low half) and non-empty words (high half) over the groups
+				uint32_t run = 0;
 #pragma unroll
-			for (int k = 0; k < 3; k++)
-				if (tc[k]) list_group_words(s, lane + 32 * k, wofs[k]);
-			__syncwarp();
-			// D. descriptors: lane <-> non-empty word (two rows), 32 words at a time
-			uint32_t qbase = 0;
-#pragma unroll 1
-			for (uint32_t i0 = 0; i0 < nwords; i0 += 32) {
-				const uint32_t i = i0 + (uint32_t)lane;
-				uint32_t widx = 0, word = 0;
-				if (i < nwords) {
-					widx = smem_wl(s)[i];
-					word = reinterpret_cast<const uint32_t *>(s.S)[widx];
+				for (int k = 0; k < 3; k++) {
+					const uint32_t v = s.gcnt[lane + 32 * k];
+					const uint32_t inc = warp_incl_scan(v, lane);
+					s.gcnt[lane + 32 * k] = run + inc - v;
+					run += __shfl_sync(full, inc, 31);
 				}
-				const uint32_t cnt = (uint32_t)__popc(word);
-				const uint32_t inc = warp_incl_scan(cnt, lane);
-				if (word) emit_word_descs(s, widx, word, di + qbase + inc - cnt);
-				qbase += __shfl_sync(full, inc, 31);
+				if (lane == 0) {
+					s.nq = run & 0xffffu;
+					s.nwords = run >> 16;
+				}
 			}
+			__syncthreads();  // also: Ey / Ex are dead, wl takes their place
+			if (tid >= 32) list_group_words(s, tid - 32, s.gcnt[tid - 32]);
+			__syncthreads();
+			// D. descriptors: thread <-> non-empty word (two rows)
+			const uint32_t nwords = s.nwords;
+#pragma unroll 1
+			for (uint32_t i = (uint32_t)tid; i < nwords; i += kThreads) {
+				const uint32_t e = smem_wl(s)[i];
+				const uint32_t widx = e & 1023u;
+				emit_word_descs(s, widx, reinterpret_cast<const uint32_t *>(s.S)[widx], di + (e >> 10));
+			}
+			if (tid == 0) p.cnt_i[c] = s.nq;
+		} else if (tid == 0) {
+			p.cnt_i[c] = 0;
 		}
 		if (amb & kFlagCrossed) {
-			__syncwarp();  // wl is dead: Cz takes its place
+			__syncthreads();  // wl is dead: Cz takes its place
 			uint16_t *Cz = smem_Cz(s);
-#pragma unroll 1
-			for (int j = 0; j < 8; j++) {
+#pragma unroll
+			for (int j = 0; j < 256 / kThreads; j++) {
+				const int col = kThreads * j + tid;
 				uint32_t cz = 0;
-				if ((crossed_cols >> j) & 1u) cz = col_crossed(flags, lds_col(raw + (32 * j + lane) * 16));
-				Cz[32 * j + lane] = (uint16_t)cz;
+				if ((crossed_cols >> j) & 1u) cz = col_crossed(flags, lds_col(raw + col * 16));
+				Cz[col] = (uint16_t)cz;
 			}
-			__syncwarp();
-			const uint32_t mine = count_plants8(s, lane);
-			const uint32_t inc = warp_incl_scan(mine, lane);
-			npl = __shfl_sync(full, inc, 31);
-			if (mine) emit_plant_descs(s, lane, p.desc_t + (size_t)c * kDescStrideT + (inc - mine));
-		}
-		if (lane == 0) {
-			p.cnt_i[c] = nq;
-			p.cnt_t[c] = npl * (uint32_t)kPlantQuads;
+			__syncthreads();
+			if (warp == 0) {
+				const uint32_t mine = count_plants8(s, lane);
+				const uint32_t inc = warp_incl_scan(mine, lane);
+				if (mine) emit_plant_descs(s, lane, p.desc_t + (size_t)c * kDescStrideT + (inc - mine));
+				if (lane == 31) p.cnt_t[c] = inc * (uint32_t)kPlantQuads;
+			}
+		} else if (tid == 0) {
+			p.cnt_t[c] = 0;
 		}
 	}
 }
 
 // ---- kernel 2: expansion -------------------------------------------------------------------
-// Exclusive prefix of cnt[0..n) into pre[0..n], pre[n] = total; pre[k > n] = 0xffffffff so that a
-// fixed-depth binary search never steps past n.  All kExpandThreads threads take part.
-__device__ __forceinline__ void block_scan_counts(const uint32_t *cnt, uint32_t n, uint32_t *pre, uint32_t *warp_tot,
-                                                  int tid) {
+// Exclusive prefixes of cnt_i / cnt_t [0..n) into pre_i / pre_t [0..lim), lim = the span the binary
+// search can touch; entries at and beyond n hold 0xffffffff so that a fixed-depth search never
+// steps past n.  Warp w scans the contiguous span [w * rounds * 128, (w+1) * rounds * 128), four
+// entries per lane and round (16-byte loads and stores, no bank conflicts); the warp totals are
+// combined through shared memory.  Returns the two totals.  All kExpandThreads threads take part.
+constexpr int kMaxScanRounds = (kMaxLaunchChunks + kExpandWarps * 128 - 1) / (kExpandWarps * 128);
+__device__ __forceinline__ void block_scan_counts(const uint32_t *cnt_i, const uint32_t *cnt_t, uint32_t n, uint32_t lim,
+                                                  uint32_t *pre_i, uint32_t *pre_t, uint32_t *warp_tot, int tid,
+                                                  uint32_t &tot_i, uint32_t &tot_t) {
 	const int lane = tid & 31, warp = tid >> 5;
-	uint32_t v[kScanPerThread];
-	const uint32_t first = (uint32_t)tid * kScanPerThread;
-	uint32_t sum = 0;
+	const uint32_t rounds = (lim + kExpandWarps * 128 - 1) / (kExpandWarps * 128);
+	const uint32_t first = (uint32_t)warp * rounds * 128u + (uint32_t)lane * 4u;
+	uint4 vi[kMaxScanRounds], vt[kMaxScanRounds];
+	uint32_t ei[kMaxScanRounds], et[kMaxScanRounds];  // exclusive prefix of this lane's four, relative to the warp's span
+	uint32_t run_i = 0, run_t = 0;
 #pragma unroll
-	for (int k = 0; k < kScanPerThread; k += 4) {
-		uint4 q = make_uint4(0, 0, 0, 0);
-		if (first + k < n) q = *reinterpret_cast<const uint4 *>(cnt + first + k);  // the arrays are padded to kMaxLaunchChunks
-		v[k] = first + k < n ? q.x : 0u;
-		v[k + 1] = first + k + 1 < n ? q.y : 0u;
-		v[k + 2] = first + k + 2 < n ? q.z : 0u;
-		v[k + 3] = first + k + 3 < n ? q.w : 0u;
-		sum += v[k] + v[k + 1] + v[k + 2] + v[k + 3];
+	for (int r = 0; r < kMaxScanRounds; r++) {
+		vi[r] = make_uint4(0, 0, 0, 0);
+		vt[r] = make_uint4(0, 0, 0, 0);
+		const uint32_t i = first + (uint32_t)r * 128u;
+		if ((uint32_t)r < rounds && i < n) {  // the count arrays are padded to kMaxLaunchChunks
+			vi[r] = *reinterpret_cast<const uint4 *>(cnt_i + i);
+			vt[r] = *reinterpret_cast<const uint4 *>(cnt_t + i);
+			if (i + 1 >= n) vi[r].y = vt[r].y = 0;
+			if (i + 2 >= n) vi[r].z = vt[r].z = 0;
+			if (i + 3 >= n) vi[r].w = vt[r].w = 0;
+		}
 	}
-	const uint32_t inc = warp_incl_scan(sum, lane);
-	if (lane == 31) warp_tot[warp] = inc;
+#pragma unroll
+	for (int r = 0; r < kMaxScanRounds; r++) {
+		if ((uint32_t)r < rounds) {
+			const uint32_t si = vi[r].x + vi[r].y + vi[r].z + vi[r].w, st = vt[r].x + vt[r].y + vt[r].z + vt[r].w;
+			const uint32_t ii = warp_incl_scan(si, lane), it = warp_incl_scan(st, lane);
+			ei[r] = run_i + ii - si;
+			et[r] = run_t + it - st;
+			run_i += __shfl_sync(0xffffffffu, ii, 31);
+			run_t += __shfl_sync(0xffffffffu, it, 31);
+		}
+	}
+	if (lane == 0) {
+		warp_tot[warp] = run_i;
+		warp_tot[kExpandWarps + warp] = run_t;
+	}
 	__syncthreads();
-	uint32_t wt = lane < kExpandWarps ? warp_tot[lane] : 0u;
-	const uint32_t winc = warp_incl_scan(wt, lane);
-	const uint32_t wbase = __shfl_sync(0xffffffffu, winc - wt, warp);
-	const uint32_t total = __shfl_sync(0xffffffffu, winc, kExpandWarps - 1);
-	uint32_t run = wbase + inc - sum;
+	static_assert(kExpandWarps <= 16, "one lane per warp total, two streams in one warp scan");
+	{
+		const uint32_t wt = lane < 2 * kExpandWarps ? warp_tot[lane] : 0u;
+		// lanes 0..15: stream i, lanes 16..31: stream t (segmented by construction: kExpandWarps == 16 or zero padding)
+		uint32_t inc = wt;
 #pragma unroll
-	for (int k = 0; k < kScanPerThread; k++) {
-		const uint32_t i = first + k;
-		pre[i] = i <= n ? run : 0xffffffffu;
-		run += v[k];
+		for (int d = 1; d < kExpandWarps; d <<= 1) {
+			const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
+			if ((lane & (kExpandWarps - 1)) >= d) inc += o;
+		}
+		const uint32_t ex = inc - wt;
+		run_i = __shfl_sync(0xffffffffu, ex, warp);
+		run_t = __shfl_sync(0xffffffffu, ex, kExpandWarps + warp);
+		tot_i = __shfl_sync(0xffffffffu, inc, kExpandWarps - 1);
+		tot_t = __shfl_sync(0xffffffffu, inc, 2 * kExpandWarps - 1);
 	}
-	if (tid < 4) pre[kMaxLaunchChunks + tid] = (kMaxLaunchChunks + tid) <= n ? total : 0xffffffffu;
+#pragma unroll
+	for (int r = 0; r < kMaxScanRounds; r++) {
+		const uint32_t i = first + (uint32_t)r * 128u;
+		if ((uint32_t)r < rounds && i < lim) {
+			uint4 a, b;
+			a.x = run_i + ei[r]; a.y = a.x + vi[r].x; a.z = a.y + vi[r].y; a.w = a.z + vi[r].z;
+			b.x = run_t + et[r]; b.y = b.x + vt[r].x; b.z = b.y + vt[r].y; b.w = b.z + vt[r].z;
+			if (i >= n) a.x = b.x = 0xffffffffu;
+			if (i + 1 >= n) a.y = b.y = 0xffffffffu;
+			if (i + 2 >= n) a.z = b.z = 0xffffffffu;
+			if (i + 3 >= n) a.w = b.w = 0xffffffffu;
+			*reinterpret_cast<uint4 *>(pre_i + i) = a;
+			*reinterpret_cast<uint4 *>(pre_t + i) = b;
+		}
+	}
 	__syncthreads();
 }
 
@@ -310,10 +351,13 @@ __global__ void __launch_bounds__(kExpandThreads, 1) expand_kernel(const ExpandP
 	unsigned char *stage = smem_raw_bytes + 2048 + 2 * 4 * kExpandPrefixWords + 256 + (size_t)warp * (kStageBytes + 16);
 
 	if (tid < 128) reinterpret_cast<uint4 *>(tab)[tid] = __ldg(reinterpret_cast<const uint4 *>(p.table) + tid);
+	uint32_t top = 1;
+	while (top * 2u <= p.n) top *= 2u;
+	if (top == p.n) top >>= 1;  // the steps top, top/2, .., 1 then reach exactly [0, 2*top) >= [0, n)
+	const uint32_t lim = ((max(p.n, 2u * top) + 3u) & ~3u);
 	pdl_wait();  // everything the analysis wrote is visible from here on
-	block_scan_counts(p.cnt_i, p.n, pre_i, warp_tot, tid);
-	block_scan_counts(p.cnt_t, p.n, pre_t, warp_tot, tid);
-	const uint32_t tot_i = pre_i[p.n], tot_t = pre_t[p.n];
+	uint32_t tot_i, tot_t;
+	block_scan_counts(p.cnt_i, p.cnt_t, p.n, lim, pre_i, pre_t, warp_tot, tid, tot_i, tot_t);
 	u64 carry_i = 0, carry_t = 0;
 	if (p.carry_in) {
 		carry_i = p.carry_in[0];
@@ -321,9 +365,10 @@ __global__ void __launch_bounds__(kExpandThreads, 1) expand_kernel(const ExpandP
 	}
 	// per-chunk ranges and the totals: spread over the grid
 	for (uint32_t c = blockIdx.x * kExpandThreads + tid; c < p.n; c += gridDim.x * kExpandThreads) {
+		const uint32_t ni = (c + 1 < p.n ? pre_i[c + 1] : tot_i) - pre_i[c], nt = (c + 1 < p.n ? pre_t[c + 1] : tot_t) - pre_t[c];
 		Range ri, rt;
-		ri.first_vertex = (carry_i + pre_i[c]) * 6ull; ri.vertex_count = (pre_i[c + 1] - pre_i[c]) * 6u; ri.reserved = 0;
-		rt.first_vertex = (carry_t + pre_t[c]) * 6ull; rt.vertex_count = (pre_t[c + 1] - pre_t[c]) * 6u; rt.reserved = 0;
+		ri.first_vertex = (carry_i + pre_i[c]) * 6ull; ri.vertex_count = ni * 6u; ri.reserved = 0;
+		rt.first_vertex = (carry_t + pre_t[c]) * 6ull; rt.vertex_count = nt * 6u; rt.reserved = 0;
 		p.ranges_i[c] = ri;
 		p.ranges_t[c] = rt;
 	}
@@ -331,9 +376,6 @@ __global__ void __launch_bounds__(kExpandThreads, 1) expand_kernel(const ExpandP
 		p.totals[0] = carry_i + tot_i;
 		p.totals[1] = carry_t + tot_t;
 	}
-	uint32_t top = 1;
-	while (top * 2u <= p.n) top *= 2u;
-	if (top == p.n) top >>= 1;  // the steps top, top/2, .., 1 then reach exactly [0, 2*top) >= [0, n)
 
 	const bool fits_i = carry_i + tot_i <= p.cap_i, fits_t = carry_t + tot_t <= p.cap_t;
 	const uint32_t tiles_i = fits_i ? (tot_i + kTileQuads - 1) / kTileQuads : 0u;

@@ -22,7 +22,6 @@
 static_assert(sizeof(mm_vertex) == 36, "Vertex must be 36 bytes (SURVEY.md 8b)");
 static_assert(sizeof(mm_range) == 16 && sizeof(mm::Range) == 16, "range layout");
 static_assert(sizeof(mm_block_entry) == 12, "block entry layout");
-static_assert(mm::kAnalyseSmemBytes <= 113 * 1024, "2 analysing CTAs per SM need <= 113 KiB each");
 static_assert(mm::kExpandSmemBytes <= 227 * 1024, "the expand CTA must fit the 227 KiB of an SM");
 
 namespace {
@@ -128,11 +127,10 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, ui
 		a.cnt_t = c->d_cnt + mm::kMaxLaunchChunks;
 		a.ticket = c->d_ticket;
 		a.ticket_base = c->ticket_base;
-		const uint32_t ctas = (m + mm::kWarpsPerCta - 1) / mm::kWarpsPerCta;
-		const uint32_t grid = std::min<uint32_t>(ctas, (uint32_t)(c->sm_count * c->ctas_per_sm));
-		mm::analyse_kernel<<<grid, mm::kThreads, mm::kAnalyseSmemBytes, c->stream>>>(a);
+		const uint32_t grid = std::min<uint32_t>(m, (uint32_t)(c->sm_count * c->ctas_per_sm));
+		mm::analyse_kernel<<<grid, mm::kThreads, 0, c->stream>>>(a);
 		MM_CUDA(c, cudaGetLastError());
-		c->ticket_base += (mm::u64)m + (mm::u64)grid * mm::kWarpsPerCta;  // every warp draws exactly one ticket >= m
+		c->ticket_base += (mm::u64)m + (mm::u64)grid;  // every CTA draws exactly one ticket >= m
 
 		mm::ExpandParams e;
 		e.offs = d_offs + (size_t)first * 3u;
@@ -199,12 +197,11 @@ int mm_ctx_create(int device, mm_ctx **out) {
 		MM_CUDA(c, cudaGetDeviceProperties(&prop, device));
 		if (prop.major < 10) return fail(c, MM_ERR_NO_DEVICE, "device %d is sm_%d%d; this library is built for sm_100a", device, prop.major, prop.minor);
 		c->sm_count = prop.multiProcessorCount;
-		MM_CUDA(c, cudaFuncSetAttribute(mm::analyse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mm::kAnalyseSmemBytes));
 		MM_CUDA(c, cudaFuncSetAttribute(mm::analyse_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
 		MM_CUDA(c, cudaFuncSetAttribute(mm::expand_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mm::kExpandSmemBytes));
 		MM_CUDA(c, cudaFuncSetAttribute(mm::expand_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
 		int occ = 0;
-		MM_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mm::analyse_kernel, mm::kThreads, mm::kAnalyseSmemBytes));
+		MM_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mm::analyse_kernel, mm::kThreads, 0));
 		if (occ < 1) return fail(c, MM_ERR_CUDA, "analyse kernel does not fit on an SM");
 		c->ctas_per_sm = occ;
 		int occ2 = 0;

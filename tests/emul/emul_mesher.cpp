@@ -51,8 +51,8 @@ extern "C" uint32_t emul_eq_mask16(const uint8_t a[16], const uint8_t b[16]) {
 extern "C" int emul_mesh_batch(const uint8_t *chunks, const int64_t *offs, uint32_t n, const TabEntry *tab,
                                unsigned char *out_i, uint64_t cap_i, unsigned char *out_t, uint64_t cap_t,
                                Range *ranges_i, Range *ranges_t, uint64_t *totals) {
-	WarpSmem *sp = new WarpSmem();
-	WarpSmem &s = *sp;
+	ChunkSmem *sp = new ChunkSmem();
+	ChunkSmem &s = *sp;
 	memset(&s, 0xA5, sizeof(s));  // nothing may depend on stale shared memory
 	uint8_t flags[256];
 	build_flags(tab, flags);
@@ -90,22 +90,21 @@ extern "C" int emul_mesh_batch(const uint8_t *chunks, const int64_t *offs, uint3
 				for (int lane = 0; lane < kLanes; lane++) col_starts(s, tab, raw, 2 * j + (lane >> 4), lane & 15, amb);
 			// C
 			for (int lane = 0; lane < kLanes; lane++) transpose_blocky(s, lane);
-			uint32_t tc[kGroups], wofs[kGroups], nwords = 0;
-			for (int m = 0; m < kGroups; m++) tc[m] = transpose_group(s, m);
-			for (int m = 0; m < kGroups; m++) {
-				wofs[m] = nwords;
-				nq += tc[m] & 0xffffu;
-				nwords += tc[m] >> 16;
+			uint32_t run = 0;
+			for (int m = 0; m < kGroups; m++) s.gcnt[m] = transpose_group(s, m);
+			for (int m = 0; m < kGroups; m++) {  // exclusive scan, quads (low half) and words (high half) at once
+				const uint32_t v = s.gcnt[m];
+				s.gcnt[m] = run;
+				run += v;
 			}
-			for (int m = 0; m < kGroups; m++)
-				if (tc[m]) list_group_words(s, m, wofs[m]);
+			nq = run & 0xffffu;
+			const uint32_t nwords = run >> 16;
+			for (int m = 0; m < kGroups; m++) list_group_words(s, m, s.gcnt[m]);
 			// D
-			uint32_t qbase = 0;
 			for (uint32_t i = 0; i < nwords; i++) {
-				const uint32_t widx = smem_wl(s)[i];
-				const uint32_t word = reinterpret_cast<const uint32_t *>(s.S)[widx];
-				emit_word_descs(s, widx, word, di + qbase);
-				qbase += (uint32_t)popc32(word);
+				const uint32_t e = smem_wl(s)[i];
+				const uint32_t widx = e & 1023u;
+				emit_word_descs(s, widx, reinterpret_cast<const uint32_t *>(s.S)[widx], di + (e >> 10));
 			}
 		}
 		if (amb & kFlagCrossed) {

@@ -155,6 +155,21 @@ def test_full_size_terrain_batch_4096(mesher, ocache):
     assert_batch_equal(mesher.mesh_batch(offs, chunks), oracle.mesh_batch(chunks, offs, ocache, threads=8))
 
 
+def test_batch_larger_than_one_launch(mesher, ocache):
+    """More chunks than one analyse/expand launch pair takes (4096): the second pair continues the packed
+    streams where the first ended (carry), across runs of empty chunks and a partial last tile."""
+    import mimas_b200
+    chunks, offs = mimas_b200.gen_terrain_host(78, (-16, -16, -2), (32, 32, 4))
+    rng = np.random.RandomState(21)
+    extra = np.zeros((1500, 4096), np.uint8)
+    extra[::7] = np.array([0, 0, 0, 5, 3, 42, 11, 200], np.uint8)[rng.randint(0, 8, size=(len(extra[::7]), 4096))]
+    chunks = np.concatenate([chunks[1024:], extra, chunks[:1024]])
+    eo = (rng.randint(-500, 500, size=(1500, 3)) * 16).astype(np.int64)
+    offs = np.concatenate([offs[1024:], eo, offs[:1024]])
+    assert len(chunks) == 5596
+    assert_batch_equal(mesher.mesh_batch(offs, chunks), oracle.mesh_batch(chunks, offs, ocache, threads=8))
+
+
 def test_push_block_matches_oracle(mesher):
     """push_block (lib.rs:183-219) for every blocked-face combination."""
     from mimas_b200.meshgen import BlockTextureIds
