@@ -86,7 +86,7 @@ typedef struct mm_batch_out {
 	uint64_t n_transparent;           /* total vertices in d_transparent   */
 	uint32_t n_chunks;
 	uint32_t launches;                /* kernels launched for this batch (incl. re-runs after growth) */
-	float kernel_ms;                  /* CUDA-event time of the last mesher kernel of this batch */
+	float kernel_ms;                  /* CUDA-event time of this batch's kernels (mm_mesh_batch); 0 for mm_mesh_batch_async batches */
 	uint32_t reserved;
 } mm_batch_out;
 

@@ -27,7 +27,7 @@ constexpr int kWarpsPerCta = 4;                  // analyse_kernel: one CTA per 
 constexpr int kThreads = kWarpsPerCta * 32;
 constexpr int kAnalyseCtasPerSm = 8;
 static_assert(kThreads == 128, "phase C hands one of 32 + 96 jobs to every thread");
-constexpr int kExpandWarps = 16;                 // expand_kernel
+constexpr int kExpandWarps = 12;                 // expand_kernel
 constexpr int kExpandThreads = kExpandWarps * 32;
 constexpr uint32_t kMaxLaunchChunks = 4096;      // the prefix of one launch lives in shared memory
 // expand: table | prefix_i[4096+4] | prefix_t[4096+4] | warp totals | stage tiles
@@ -58,6 +58,7 @@ struct ExpandParams {
 	Range *ranges_i, *ranges_t;   // n entries each
 	const u64 *carry_in;          // quads already in the streams (earlier launches of the batch) or NULL
 	u64 *totals;                  // [0] quads in out_i, [1] quad slots in out_t after this launch
+	u64 *host_totals;             // the same two words in mapped pinned host memory
 };
 
 __device__ __forceinline__ Col lds_col(const unsigned char *p) {
@@ -252,6 +253,9 @@ __global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(co
 			p.cnt_t[c] = 0;
 		}
 	}
+	// Programmatic dependent launch: this grid runs beside the expansion of the previous batch; it must
+	// not complete (and so release the expansion of this batch onto the arenas) before that one has.
+	pdl_wait();
 }
 
 // ---- kernel 2: expansion -------------------------------------------------------------------
@@ -296,24 +300,24 @@ __device__ __forceinline__ void block_scan_counts(const uint32_t *cnt_i, const u
 	}
 	if (lane == 0) {
 		warp_tot[warp] = run_i;
-		warp_tot[kExpandWarps + warp] = run_t;
+		warp_tot[16 + warp] = run_t;
 	}
 	__syncthreads();
 	static_assert(kExpandWarps <= 16, "one lane per warp total, two streams in one warp scan");
 	{
-		const uint32_t wt = lane < 2 * kExpandWarps ? warp_tot[lane] : 0u;
-		// lanes 0..15: stream i, lanes 16..31: stream t (segmented by construction: kExpandWarps == 16 or zero padding)
+		// lanes 0..15: stream i, lanes 16..31: stream t; warps that do not exist count zero
+		const uint32_t wt = (lane & 15) < kExpandWarps ? warp_tot[lane] : 0u;
 		uint32_t inc = wt;
 #pragma unroll
-		for (int d = 1; d < kExpandWarps; d <<= 1) {
+		for (int d = 1; d < 16; d <<= 1) {
 			const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
-			if ((lane & (kExpandWarps - 1)) >= d) inc += o;
+			if ((lane & 15) >= d) inc += o;
 		}
 		const uint32_t ex = inc - wt;
 		run_i = __shfl_sync(0xffffffffu, ex, warp);
-		run_t = __shfl_sync(0xffffffffu, ex, kExpandWarps + warp);
-		tot_i = __shfl_sync(0xffffffffu, inc, kExpandWarps - 1);
-		tot_t = __shfl_sync(0xffffffffu, inc, 2 * kExpandWarps - 1);
+		run_t = __shfl_sync(0xffffffffu, ex, 16 + warp);
+		tot_i = __shfl_sync(0xffffffffu, inc, 15);
+		tot_t = __shfl_sync(0xffffffffu, inc, 31);
 	}
 #pragma unroll
 	for (int r = 0; r < kMaxScanRounds; r++) {
@@ -355,7 +359,12 @@ __global__ void __launch_bounds__(kExpandThreads, 1) expand_kernel(const ExpandP
 	while (top * 2u <= p.n) top *= 2u;
 	if (top == p.n) top >>= 1;  // the steps top, top/2, .., 1 then reach exactly [0, 2*top) >= [0, n)
 	const uint32_t lim = ((max(p.n, 2u * top) + 3u) & ~3u);
-	pdl_wait();  // everything the analysis wrote is visible from here on
+	// Programmatic dependent launch.  The analysis of this batch has completed once the wait returns,
+	// and with it (its CTAs end in a wait of their own) the expansion of the previous batch: the
+	// arenas and the other half of the hand-over buffers are free.  Only then may the next analysis
+	// start: it overlaps the tile loop below.
+	pdl_wait();
+	pdl_launch_dependents();
 	uint32_t tot_i, tot_t;
 	block_scan_counts(p.cnt_i, p.cnt_t, p.n, lim, pre_i, pre_t, warp_tot, tid, tot_i, tot_t);
 	u64 carry_i = 0, carry_t = 0;
@@ -375,6 +384,9 @@ __global__ void __launch_bounds__(kExpandThreads, 1) expand_kernel(const ExpandP
 	if (blockIdx.x == 0 && tid == 0) {
 		p.totals[0] = carry_i + tot_i;
 		p.totals[1] = carry_t + tot_t;
+		p.host_totals[0] = carry_i + tot_i;
+		p.host_totals[1] = carry_t + tot_t;
+		__threadfence_system();
 	}
 
 	const bool fits_i = carry_i + tot_i <= p.cap_i, fits_t = carry_t + tot_t <= p.cap_t;

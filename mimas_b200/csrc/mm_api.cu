@@ -99,8 +99,8 @@ int ensure_desc_capacity(mm_ctx *c, uint32_t n) {
 	cudaFree(c->d_desc_i); cudaFree(c->d_desc_t);
 	c->d_desc_i = c->d_desc_t = nullptr;
 	c->cap_desc_chunks = 0;
-	MM_CUDA(c, cudaMalloc(&c->d_desc_i, sizeof(uint32_t) * (size_t)nc * mm::kDescStrideI));
-	MM_CUDA(c, cudaMalloc(&c->d_desc_t, sizeof(uint32_t) * (size_t)nc * mm::kDescStrideT));
+	MM_CUDA(c, cudaMalloc(&c->d_desc_i, 2 * sizeof(uint32_t) * (size_t)nc * mm::kDescStrideI));
+	MM_CUDA(c, cudaMalloc(&c->d_desc_t, 2 * sizeof(uint32_t) * (size_t)nc * mm::kDescStrideT));
 	c->cap_desc_chunks = nc;
 	return MM_OK;
 }
@@ -108,10 +108,13 @@ int ensure_desc_capacity(mm_ctx *c, uint32_t n) {
 // Enqueue the mesher for (d_chunks, d_offs, n) on the context's stream: per kMaxLaunchChunks
 // chunks one analyse + one expand launch, each pair continuing the packed streams where the
 // previous one ended.
-int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, uint32_t n) {
+// Nothing but kernels is enqueued for an untimed batch (the totals reach the host through mapped
+// pinned memory), so that back-to-back batches chain by programmatic dependent launch.
+int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, uint32_t n, bool timed) {
 	int rc;
 	if ((rc = ensure_desc_capacity(c, n))) return rc;
-	MM_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+	c->last_timed = timed;
+	if (timed) MM_CUDA(c, cudaEventRecord(c->ev0, c->stream));
 	const mm::u64 *carry = nullptr;
 	for (uint32_t first = 0; first < n; first += mm::kMaxLaunchChunks) {
 		const uint32_t m = std::min<uint32_t>(n - first, mm::kMaxLaunchChunks);
@@ -121,23 +124,36 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, ui
 		a.n = m;
 		a.table = c->d_table;
 		a.flags = c->d_flags;
-		a.desc_i = c->d_desc_i;
-		a.desc_t = c->d_desc_t;
-		a.cnt_i = c->d_cnt;
-		a.cnt_t = c->d_cnt + mm::kMaxLaunchChunks;
+		c->pair_parity ^= 1;
+		const size_t par = (size_t)c->pair_parity;
+		a.desc_i = c->d_desc_i + par * c->cap_desc_chunks * mm::kDescStrideI;
+		a.desc_t = c->d_desc_t + par * c->cap_desc_chunks * mm::kDescStrideT;
+		a.cnt_i = c->d_cnt + par * 2 * mm::kMaxLaunchChunks;
+		a.cnt_t = a.cnt_i + mm::kMaxLaunchChunks;
 		a.ticket = c->d_ticket;
 		a.ticket_base = c->ticket_base;
 		const uint32_t grid = std::min<uint32_t>(m, (uint32_t)(c->sm_count * c->ctas_per_sm));
-		mm::analyse_kernel<<<grid, mm::kThreads, 0, c->stream>>>(a);
-		MM_CUDA(c, cudaGetLastError());
+		cudaLaunchAttribute attr[1];
+		attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+		attr[0].val.programmaticStreamSerializationAllowed = c->use_pdl ? 1 : 0;
+		{
+			cudaLaunchConfig_t cfg = {};
+			cfg.gridDim = dim3(grid);
+			cfg.blockDim = dim3(mm::kThreads);
+			cfg.dynamicSmemBytes = 0;
+			cfg.stream = c->stream;
+			cfg.attrs = attr;
+			cfg.numAttrs = 1;
+			MM_CUDA(c, cudaLaunchKernelEx(&cfg, mm::analyse_kernel, a));
+		}
 		c->ticket_base += (mm::u64)m + (mm::u64)grid;  // every CTA draws exactly one ticket >= m
 
 		mm::ExpandParams e;
 		e.offs = d_offs + (size_t)first * 3u;
 		e.n = m;
 		e.table = c->d_table;
-		e.desc_i = c->d_desc_i;
-		e.desc_t = c->d_desc_t;
+		e.desc_i = a.desc_i;
+		e.desc_t = a.desc_t;
 		e.cnt_i = a.cnt_i;
 		e.cnt_t = a.cnt_t;
 		e.out_i = c->d_out_i;
@@ -148,16 +164,13 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, ui
 		e.ranges_t = c->d_ranges_t + first;
 		e.carry_in = carry;
 		e.totals = c->d_ticket + 2 + 2 * c->totals_slot;
-		// programmatic dependent launch: the expand CTAs start (table load) while the analysis
-		// drains and wait in griddepcontrol.wait for its results
+		e.host_totals = c->d_h_totals;
+		// programmatic dependent launch (see the kernels): analysis of batch k+1 beside expansion of batch k
 		cudaLaunchConfig_t cfg = {};
 		cfg.gridDim = dim3((unsigned)c->expand_grid);
 		cfg.blockDim = dim3(mm::kExpandThreads);
 		cfg.dynamicSmemBytes = mm::kExpandSmemBytes;
 		cfg.stream = c->stream;
-		cudaLaunchAttribute attr[1];
-		attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-		attr[0].val.programmaticStreamSerializationAllowed = c->use_pdl ? 1 : 0;
 		cfg.attrs = attr;
 		cfg.numAttrs = 1;
 		MM_CUDA(c, cudaLaunchKernelEx(&cfg, mm::expand_kernel, e));
@@ -165,8 +178,7 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, ui
 		c->last_launches += 2;
 		c->total_launches += 2;
 	}
-	MM_CUDA(c, cudaEventRecord(c->ev1, c->stream));
-	MM_CUDA(c, cudaMemcpyAsync(c->h_totals, carry, 2 * sizeof(mm::u64), cudaMemcpyDeviceToHost, c->stream));
+	if (timed) MM_CUDA(c, cudaEventRecord(c->ev1, c->stream));
 	return MM_OK;
 }
 
@@ -217,9 +229,10 @@ int mm_ctx_create(int device, mm_ctx **out) {
 		MM_CUDA(c, cudaMalloc(&c->d_ticket, sizeof(mm::u64) * 8));
 		MM_CUDA(c, cudaMemset(c->d_ticket, 0, sizeof(mm::u64) * 8));
 		MM_CUDA(c, cudaMalloc(&c->d_flags, 256));
-		MM_CUDA(c, cudaMalloc(&c->d_cnt, sizeof(uint32_t) * 2 * mm::kMaxLaunchChunks));
-		MM_CUDA(c, cudaMemset(c->d_cnt, 0, sizeof(uint32_t) * 2 * mm::kMaxLaunchChunks));
-		MM_CUDA(c, cudaHostAlloc(&c->h_totals, sizeof(mm::u64) * 2, cudaHostAllocDefault));
+		MM_CUDA(c, cudaMalloc(&c->d_cnt, sizeof(uint32_t) * 4 * mm::kMaxLaunchChunks));
+		MM_CUDA(c, cudaMemset(c->d_cnt, 0, sizeof(uint32_t) * 4 * mm::kMaxLaunchChunks));
+		MM_CUDA(c, cudaHostAlloc(&c->h_totals, sizeof(mm::u64) * 2, cudaHostAllocMapped));
+		MM_CUDA(c, cudaHostGetDevicePointer((void **)&c->d_h_totals, c->h_totals, 0));
 		return MM_OK;
 	};
 	rc = body();
@@ -356,7 +369,8 @@ int mm_mesh_batch_async(mm_ctx *c, const uint8_t *d_chunks, const int64_t *d_off
 	if (n == 0) { c->pending = true; return MM_OK; }
 	int rc;
 	if ((rc = ensure_chunk_capacity(c, n))) return rc;
-	if ((rc = launch(c, d_chunks, c->last_offs, n))) return rc;
+	if ((rc = launch(c, d_chunks, c->last_offs, n, c->time_next))) return rc;
+	c->time_next = false;
 	c->pending = true;
 	return MM_OK;
 }
@@ -375,9 +389,10 @@ int mm_batch_finish(mm_ctx *c, mm_batch_out *out) {
 			int rc;  // grow to fit (+1/8 head room) and run again: the inputs are still resident
 			if ((rc = ensure_arena(c, &c->d_out_i, &c->cap_i, c->tot_i + c->tot_i / 8))) return rc;
 			if ((rc = ensure_arena(c, &c->d_out_t, &c->cap_t, c->tot_t + c->tot_t / 8))) return rc;
-			if ((rc = launch(c, c->last_chunks, c->last_offs, c->last_n))) return rc;
+			if ((rc = launch(c, c->last_chunks, c->last_offs, c->last_n, c->last_timed))) return rc;
 		}
-		MM_CUDA(c, cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1));
+		c->last_ms = 0.f;  // an untimed (mm_mesh_batch_async) batch enqueues kernels only
+		if (c->last_timed) MM_CUDA(c, cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1));
 	} else {
 		c->last_ms = 0.f;
 	}
@@ -425,6 +440,7 @@ int mm_mesh_batch(mm_ctx *c, const uint8_t *chunks, const int64_t *offs, const u
 		}
 	}
 	int rc;
+	c->time_next = true;  // the synchronous call brackets its kernels with events: mm_batch_out.kernel_ms
 	if ((rc = mm_mesh_batch_async(c, dc, dof, n))) return rc;
 	return mm_batch_finish(c, out);
 }

@@ -25,16 +25,21 @@ struct mm_ctx {
 	uint32_t cap_chunks = 0;
 	mm::Range *d_ranges_i = nullptr, *d_ranges_t = nullptr;
 	// analysis -> expansion hand-over (mesh_kernel.cuh): per-chunk descriptor slots and counts
-	uint32_t *d_desc_i = nullptr, *d_desc_t = nullptr;  // cap_desc_chunks * kDescStrideI / kDescStrideT words
+	// -- two of each: consecutive launch pairs alternate, so that the analysis of one batch can run
+	// beside the expansion of the previous one (programmatic dependent launch)
+	uint32_t *d_desc_i = nullptr, *d_desc_t = nullptr;  // 2 x cap_desc_chunks * kDescStrideI / kDescStrideT words
 	uint32_t cap_desc_chunks = 0;
-	uint32_t *d_cnt = nullptr;        // cnt_i[kMaxLaunchChunks] then cnt_t[kMaxLaunchChunks]
+	uint32_t *d_cnt = nullptr;        // 2 x { cnt_i[kMaxLaunchChunks], cnt_t[kMaxLaunchChunks] }
+	int pair_parity = 0;
 	int expand_grid = 0;
 	bool use_pdl = true;
 	mm::u64 *d_ticket = nullptr;      // [0] ticket counter, [2..3] and [4..5] alternating totals slots
 	int totals_slot = 0;              // slot the last launch wrote
 	mm::u64 ticket_base = 0;
 	unsigned char *d_flags = nullptr; // 256 flag bytes derived from the block table
-	mm::u64 *h_totals = nullptr;    // pinned, 2 words
+	mm::u64 *h_totals = nullptr;    // pinned + mapped, 2 words: the expand kernel writes the totals straight to the host
+	mm::u64 *d_h_totals = nullptr;  // the same words as the device sees them
+	bool time_next = false, last_timed = false;
 
 	// staged inputs for host callers
 	unsigned char *d_in_chunks = nullptr;

@@ -141,7 +141,7 @@ def test_device_resident_path_and_device_terrain_generator(mesher, ocache):
         for _ in range(3):  # back-to-back async launches, last one read back
             mesher.mesh_batch_async(d_c, d_o, n)
         out = mesher.batch_finish()
-        assert out.n_chunks == n and out.kernel_ms > 0
+        assert out.n_chunks == n and out.kernel_ms == 0  # async batches enqueue kernels only, no timing events
         assert_batch_equal(mesher.copy_out(out), want)
     finally:
         mesher.dev_free(d_c)
