@@ -62,8 +62,17 @@ def main():
             d["dram_bytes_total"] = rd + wr
             traffic.append(rd + wr)
     json.dump({"report": os.path.basename(rep), "launches": launches}, open(out + "_ncu_summary.json", "w"), indent=1)
+    # one step of the mesher = an analyse + an expand launch: DRAM bytes of the first complete pair
+    # (a pair whose expand kernel wrote nothing is the capacity probe of a fresh arena, not a step)
+    pairs = []
+    for a, b in zip(launches, launches[1:]):
+        if "analyse" in a["kernel"] and "expand" in b["kernel"] and "dram_bytes_total" in a:
+            if b["dram__bytes_write.sum"] * TO_BYTES.get(b["dram__bytes_write.sum.unit"], 1) > 1e6:
+                pairs.append(a["dram_bytes_total"] + b["dram_bytes_total"])
+    if pairs:
+        traffic = pairs
     if traffic:
-        json.dump({"source": os.path.basename(out) + "_ncu_summary.json", "kernel": launches[0]["kernel"],
+        json.dump({"source": os.path.basename(out) + "_ncu_summary.json", "kernel": "analyse_kernel + expand_kernel" if pairs else launches[0]["kernel"],
                    "dram_bytes_per_launch": sum(traffic) / len(traffic), "per_launch": traffic},
                   open(os.path.join(os.path.dirname(out) or ".", "roofline_traffic.json"), "w"), indent=1)
 

@@ -148,6 +148,39 @@ def test_device_resident_path_and_device_terrain_generator(mesher, ocache):
         mesher.dev_free(d_o)
 
 
+def test_overlapping_batches_do_not_disturb_each_other(ocache):
+    """Back-to-back mm_mesh_batch_async batches chain by programmatic dependent launch: the analysis of
+    batch k+1 runs beside the expansion of batch k, on the other half of the hand-over buffers, and the
+    expansion of k+1 may only touch the arenas once k has finished.  Alternate between batches of very
+    different content and size; whichever comes last must be exact."""
+    import mimas_b200
+    from tests.util import checkerboard_chunks
+    rng = np.random.RandomState(33)
+    a_c, a_o = mimas_b200.gen_terrain_host(78, (-8, -8, -2), (16, 16, 4))          # 1024 terrain chunks
+    b_c = rng.randint(0, 256, size=(700, 4096)).astype(np.uint8)                      # dense random ids, many plants
+    b_o = (rng.randint(-1000, 1000, size=(700, 3)) * 16).astype(np.int64)
+    c_c, c_o = checkerboard_chunks(40)                                                # few huge chunks
+    e_c, e_o = np.zeros((3000, 4096), np.uint8), np.zeros((3000, 3), np.int64)        # nothing at all
+    sets = [(a_c, a_o), (b_c, b_o), (c_c, c_o), (e_c, e_o)]
+    want = [oracle.mesh_batch(c, o, ocache, threads=8) for c, o in sets]
+    with mimas_b200.Mesher(0, product_cache(G)) as m:
+        dev = []
+        for c, o in sets:
+            dc, do = m.dev_alloc(c.size), m.dev_alloc(o.size * 8)
+            m.upload(dc, c)
+            m.upload(do, o)
+            dev.append((dc, do, len(c)))
+        m.reserve(4096, 700 * 73728, 700 * 400 * 24)
+        order = rng.randint(0, 4, size=60)
+        for last in range(4):
+            for k in list(order) + [last]:
+                m.mesh_batch_async(*dev[k])
+            assert_batch_equal(m.copy_out(m.batch_finish()), want[last])
+        for dc, do, _ in dev:
+            m.dev_free(dc)
+            m.dev_free(do)
+
+
 def test_full_size_terrain_batch_4096(mesher, ocache):
     """BASELINE.json configs[1] at full size: 4096 terrain chunks, every byte compared."""
     import mimas_b200
