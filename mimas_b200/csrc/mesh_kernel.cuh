@@ -1,21 +1,25 @@
 // mesh_kernel.cuh -- the sm_100a batch mesher, v3: two kernels per batch (device only).
 //
-// analyse_kernel: persistent CTAs of 8 warps; every WARP is an independent chunk worker that
-// draws chunk tickets and runs phases A-D of mesh_core.cuh with its 32 lanes:
-//   A. one bulk async copy (TMA) brings the 4 KiB chunk into shared memory; blocky masks and
-//      id-equality masks per column
+// analyse_kernel: persistent CTAs of 128 threads, 8 per SM; every CTA has one chunk in flight, draws
+// chunk tickets and runs phases A-D of mesh_core.cuh:
+//   A. one bulk async copy (TMA) brings the 4 KiB chunk into shared memory; thread <-> two columns:
+//      blocky masks and id-equality masks
 //   B. visibility / run starts of the six passes as bit operations on 16-bit z-masks
-//   C. popc -> quads per (pass, c1) group, warp shuffle scan -> offsets inside the chunk
-//   D. in-register 16x16 bit transposes -> rows in emission order; one 32-bit descriptor per
-//      quad / per plant into the chunk's descriptor slot, the two counts into the count arrays
+//   C. 32 + 96 jobs, one per thread: 16x16 bit transposes in registers -> rows in emission order;
+//      popc + one warp scan -> quads and non-empty words per (pass, c1) group
+//   D. the non-empty words (two rows each) are listed; thread <-> word writes one 32-bit descriptor
+//      per quad into the chunk's descriptor slot; plants likewise; the two counts into the count arrays
 // The analysis never waits for another chunk: no look-back, no spinning.
 //
-// expand_kernel: one persistent CTA of 16 warps per SM.  Every CTA scans the per-chunk counts
+// expand_kernel: one persistent CTA of 12 warps per SM.  Every CTA scans the per-chunk counts
 // into shared memory (exclusive prefix = where each chunk starts in the packed streams, chunk
 // order, tightly packed); then each warp takes tiles of 32 consecutive quads of the packed
 // stream: quad -> chunk by binary search in shared memory, descriptor -> 216 B per lane into the
 // warp's staging tile, one cp.async.bulk (TMA) shared -> global store per tile.  Tiles are
 // uniform, so the write-bound part of the job is balanced to one tile per warp.
+//
+// Consecutive batches chain by programmatic dependent launch: the analysis of batch k+1 runs beside
+// the expansion of batch k (see the griddepcontrol calls and DESIGN.md section 3).
 // No tensor cores: the path is a scan/compaction bound by the vertex-stream writes.
 #pragma once
 #include <cuda_runtime.h>
