@@ -187,6 +187,7 @@ def main():
     ap.add_argument("--workload", default="terrain", choices=["terrain", "checkerboard"])
     ap.add_argument("--e2e-steps", type=int, default=0, help="host-in/host-out steps (default: min(steps, 20))")
     ap.add_argument("--no-verify", action="store_true", help="skip the pre-timing parity check")
+    ap.add_argument("--quick", action="store_true", help="tuning runs: device-resident timing only (no e2e, no CPU baseline)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
 
@@ -302,7 +303,7 @@ def main():
     vert_bytes = float(np.mean([36 * verts[i % rot] for i in range(args.steps)]))
 
     # ---- end to end through the C ABI with host buffers (H2D + kernel + D2H every step) -----------
-    e2e_steps = args.e2e_steps or min(args.steps, 20)
+    e2e_steps = 1 if args.quick else (args.e2e_steps or min(args.steps, 20))
     hc, ho = make_host_batch(args.workload, rank, 0)
     pin_c, pin_o = mesher.host_alloc(n * 4096), mesher.host_alloc(n * 24)
     pin_c[:] = hc.reshape(-1)
@@ -325,7 +326,7 @@ def main():
 
     # ---- CPU baseline on this box's host cores (rank 0, N = 1 only) ---------------------------------
     cpu = None
-    if rank == 0 and world == 1:
+    if rank == 0 and world == 1 and not args.quick:
         cores = os.cpu_count() or 1
         rate_all, reps = cpu_mesher_rate(hc, ho, cores)
         rate_1, _ = cpu_mesher_rate(hc[:1024], ho[:1024], 1, min_seconds=1.0)

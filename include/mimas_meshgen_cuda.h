@@ -202,6 +202,12 @@ int mm_host_free(mm_ctx *ctx, void *h_ptr);
 int mm_device_info(mm_ctx *ctx, int *sm_count, int *ctas_per_sm, int *threads_per_cta);
 /* Number of mesher kernels this context has launched since creation. */
 int mm_launch_count(mm_ctx *ctx, uint64_t *launches);
+/* Development aid, no reference counterpart: device timeline (%globaltimer, ns) of the launch pairs since
+ * the previous call, as a ring of `pairs` records of 8 words: analyse {first CTA start, -, last CTA out of
+ * work, last CTA end}, expand {first CTA start, first CTA past its dependency wait, -, last CTA end}.
+ * Copies the ring recorded so far (as many records as the previous call armed) into `out` (may be NULL),
+ * then re-arms with `pairs` records (0 = off). */
+int mm_debug_trace(mm_ctx *ctx, uint32_t pairs, uint64_t *out, uint64_t *n_launched);
 
 #ifdef __cplusplus
 }

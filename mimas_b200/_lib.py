@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libmimas_meshgen_cuda.so")
+# MM_LIB_PATH: a differently tuned build of the same library (scripts/variants.sh); never a different implementation
+LIB_PATH = os.environ.get("MM_LIB_PATH") or os.path.join(HERE, "libmimas_meshgen_cuda.so")
 
 STATUS_NAMES = {0: "MM_OK", 1: "MM_ERR_INVALID", 2: "MM_ERR_NO_DEVICE", 3: "MM_ERR_CUDA", 4: "MM_ERR_OOM",
                 5: "MM_ERR_NO_TABLE", 6: "MM_ERR_NO_BATCH", 7: "MM_ERR_UNSUPPORTED"}
@@ -20,6 +21,7 @@ SYMBOLS = (
     "mm_batch_finish", "mm_copy_out", "mm_mesh_batch_host", "mm_mesh_for_chunk", "mm_push_blocks",
     "mm_gen_terrain_host", "mm_gen_terrain_device", "mm_dev_alloc", "mm_dev_free", "mm_dev_upload",
     "mm_dev_download", "mm_ctx_sync", "mm_device_info", "mm_host_alloc", "mm_host_free", "mm_launch_count",
+    "mm_debug_trace",
 )
 
 

@@ -29,9 +29,21 @@ namespace mm {
 
 constexpr int kWarpsPerCta = 4;                  // analyse_kernel: one CTA per chunk in flight
 constexpr int kThreads = kWarpsPerCta * 32;
-constexpr int kAnalyseCtasPerSm = 8;
+#ifndef MM_ANALYSE_CTAS
+#define MM_ANALYSE_CTAS 10
+#endif
+#ifndef MM_EXPAND_WARPS
+#define MM_EXPAND_WARPS 12
+#endif
+#ifndef MM_EXPAND_MINBLOCKS
+#define MM_EXPAND_MINBLOCKS 1
+#endif
+#ifndef MM_EXPAND_PREFETCH
+#define MM_EXPAND_PREFETCH 0
+#endif
+constexpr int kAnalyseCtasPerSm = MM_ANALYSE_CTAS;   // register budget of the analysis: 65536 / (128 * this)
 static_assert(kThreads == 128, "phase C hands one of 32 + 96 jobs to every thread");
-constexpr int kExpandWarps = 12;                 // expand_kernel
+constexpr int kExpandWarps = MM_EXPAND_WARPS;    // expand_kernel
 constexpr int kExpandThreads = kExpandWarps * 32;
 constexpr uint32_t kMaxLaunchChunks = 4096;      // the prefix of one launch lives in shared memory
 // expand: table | prefix_i[4096+4] | prefix_t[4096+4] | warp totals | stage tiles
@@ -49,6 +61,7 @@ struct AnalyseParams {
 	uint32_t *cnt_t;              // transparent quad slots per chunk (4 per plant)
 	u64 *ticket;                  // monotonically increasing across launches
 	u64 ticket_base;              // its value at launch
+	u64 *trace;                   // NULL, or 4 words of this launch: first CTA start, -, last CTA work done, last CTA end (ns)
 };
 
 struct ExpandParams {
@@ -63,6 +76,7 @@ struct ExpandParams {
 	const u64 *carry_in;          // quads already in the streams (earlier launches of the batch) or NULL
 	u64 *totals;                  // [0] quads in out_i, [1] quad slots in out_t after this launch
 	u64 *host_totals;             // the same two words in mapped pinned host memory
+	u64 *trace;                   // NULL, or 4 words of this launch: first CTA start, first CTA past the wait, -, last CTA end (ns)
 };
 
 __device__ __forceinline__ Col lds_col(const unsigned char *p) {
@@ -124,6 +138,14 @@ __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wa
 // prologue early / wait until everything the previous kernel wrote is visible
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+// timeline of a launch for mm_debug_trace (one thread per CTA; words 0,1 keep the minimum, 2,3 the maximum)
+__device__ __forceinline__ void trace_mark(u64 *trace, int word) {
+	if (trace == nullptr) return;
+	u64 t;
+	asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+	if (word < 2) atomicMin(trace + word, t);
+	else atomicMax(trace + word, t);
+}
 
 // Called by ONE lane after the tile is complete and fenced.  `g` is the byte address
 // of the tile in the stream (8-byte aligned); `sp` is the tile in shared memory with
@@ -151,6 +173,7 @@ __global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(co
 	const unsigned full = 0xffffffffu;
 
 	pdl_launch_dependents();  // the expand kernel may set itself up while this one works
+	if (tid == 0) trace_mark(p.trace, 0);
 	if (tid < 16) reinterpret_cast<uint4 *>(flags)[tid] = __ldg(reinterpret_cast<const uint4 *>(p.flags) + tid);
 	if (warp == 1) init_warp_smem(s, lane);
 	if (tid == 0) {
@@ -259,7 +282,9 @@ __global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(co
 	}
 	// Programmatic dependent launch: this grid runs beside the expansion of the previous batch; it must
 	// not complete (and so release the expansion of this batch onto the arenas) before that one has.
+	if (tid == 0) trace_mark(p.trace, 2);
 	pdl_wait();
+	if (tid == 0) trace_mark(p.trace, 3);
 }
 
 // ---- kernel 2: expansion -------------------------------------------------------------------
@@ -349,7 +374,7 @@ __device__ __forceinline__ uint32_t find_chunk(const uint32_t *pre, uint32_t q, 
 	return lo;
 }
 
-__global__ void __launch_bounds__(kExpandThreads, 1) expand_kernel(const ExpandParams p) {
+__global__ void __launch_bounds__(kExpandThreads, MM_EXPAND_MINBLOCKS) expand_kernel(const ExpandParams p) {
 	extern __shared__ __align__(128) unsigned char smem_raw_bytes[];
 	TabEntry *tab = reinterpret_cast<TabEntry *>(smem_raw_bytes);
 	uint32_t *pre_i = reinterpret_cast<uint32_t *>(smem_raw_bytes + 2048);
@@ -367,8 +392,10 @@ __global__ void __launch_bounds__(kExpandThreads, 1) expand_kernel(const ExpandP
 	// and with it (its CTAs end in a wait of their own) the expansion of the previous batch: the
 	// arenas and the other half of the hand-over buffers are free.  Only then may the next analysis
 	// start: it overlaps the tile loop below.
+	if (tid == 0) trace_mark(p.trace, 0);
 	pdl_wait();
 	pdl_launch_dependents();
+	if (tid == 0) trace_mark(p.trace, 1);
 	uint32_t tot_i, tot_t;
 	block_scan_counts(p.cnt_i, p.cnt_t, p.n, lim, pre_i, pre_t, warp_tot, tid, tot_i, tot_t);
 	u64 carry_i = 0, carry_t = 0;
@@ -397,38 +424,52 @@ __global__ void __launch_bounds__(kExpandThreads, 1) expand_kernel(const ExpandP
 	const uint32_t tiles_i = fits_i ? (tot_i + kTileQuads - 1) / kTileQuads : 0u;
 	const uint32_t tiles_t = fits_t ? (tot_t + kTileQuads - 1) / kTileQuads : 0u;
 	const uint32_t gw = blockIdx.x * kExpandWarps + warp, nw = gridDim.x * kExpandWarps;
+	const uint32_t tiles = tiles_i + tiles_t;
+	// what a lane needs for its quad of a tile; fetched one tile ahead so that the shared-memory search
+	// and the L2 round trip of tile k+1 hide behind the expansion of tile k
+	struct Fetched {
+		uint32_t d;
+		long long ox, oy, oz;
+	};
+	auto fetch = [&](uint32_t t, Fetched &f) {
+		const bool face = t < tiles_i;
+		const uint32_t q = (face ? t : t - tiles_i) * kTileQuads + (uint32_t)lane;
+		f.d = 0; f.ox = 0; f.oy = 0; f.oz = 0;
+		if (q < (face ? tot_i : tot_t)) {
+			const uint32_t *pre = face ? pre_i : pre_t;
+			const uint32_t c = find_chunk(pre, q, top);
+			const uint32_t r = q - pre[c];
+			f.d = face ? __ldg(p.desc_i + (size_t)c * kDescStrideI + r) : __ldg(p.desc_t + (size_t)c * kDescStrideT + (r >> 2));
+			f.ox = __ldg(p.offs + 3 * (size_t)c);
+			f.oy = __ldg(p.offs + 3 * (size_t)c + 1);
+			f.oz = __ldg(p.offs + 3 * (size_t)c + 2);
+		}
+	};
+	Fetched cur, nxt;
+	if (MM_EXPAND_PREFETCH && gw < tiles) fetch(gw, cur);
 #pragma unroll 1
-	for (uint32_t t = gw; t < tiles_i + tiles_t; t += nw) {
+	for (uint32_t t = gw; t < tiles; t += nw) {
+		if (!MM_EXPAND_PREFETCH) fetch(t, cur);
+		else if (t + nw < tiles) fetch(t + nw, nxt);
 		const bool face = t < tiles_i;
 		const uint32_t q0 = (face ? t : t - tiles_i) * kTileQuads;
-		const uint32_t tot = face ? tot_i : tot_t;
-		const uint32_t tn = min((uint32_t)kTileQuads, tot - q0);
-		const uint32_t q = q0 + (uint32_t)lane;
+		const uint32_t tn = min((uint32_t)kTileQuads, (face ? tot_i : tot_t) - q0);
 		const bool act = (uint32_t)lane < tn;
-		uint32_t d = 0, c = 0;
-		long long ox = 0, oy = 0, oz = 0;
-		if (act) {
-			const uint32_t *pre = face ? pre_i : pre_t;
-			c = find_chunk(pre, q, top);
-			const uint32_t r = q - pre[c];
-			d = face ? __ldg(p.desc_i + (size_t)c * kDescStrideI + r) : __ldg(p.desc_t + (size_t)c * kDescStrideT + (r >> 2));
-			ox = __ldg(p.offs + 3 * (size_t)c);
-			oy = __ldg(p.offs + 3 * (size_t)c + 1);
-			oz = __ldg(p.offs + 3 * (size_t)c + 2);
-		}
 		unsigned char *g = (face ? p.out_i + (carry_i + q0) * (u64)kQuadBytes : p.out_t + (carry_t + q0) * (u64)kQuadBytes);
 		unsigned char *sp = stage + ((uintptr_t)g & 8u);
 		if (lane == 0) bulk_wait_read_all();  // the staging tile is free once the last bulk store has read it
 		__syncwarp();
 		if (act) {
-			if (face) expand_face_desc(tab, ox, oy, oz, d, sp + lane * kQuadBytes);
-			else expand_plant_desc(tab, ox, oy, oz, d, (int)(q & 3u), sp + lane * kQuadBytes);
+			if (face) expand_face_desc(tab, cur.ox, cur.oy, cur.oz, cur.d, sp + lane * kQuadBytes);
+			else expand_plant_desc(tab, cur.ox, cur.oy, cur.oz, cur.d, lane & 3, sp + lane * kQuadBytes);
 		}
 		fence_proxy_async_smem();
 		__syncwarp();
 		if (lane == 0) store_tile(g, sp, tn * kQuadBytes);
+		if (MM_EXPAND_PREFETCH) cur = nxt;
 	}
 	if (lane == 0) bulk_wait_all();  // all bulk stores of this warp have landed before it exits
+	if (tid == 0) trace_mark(p.trace, 3);
 }
 
 }  // namespace mm

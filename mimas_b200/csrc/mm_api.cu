@@ -132,6 +132,8 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, ui
 		a.cnt_t = a.cnt_i + mm::kMaxLaunchChunks;
 		a.ticket = c->d_ticket;
 		a.ticket_base = c->ticket_base;
+		mm::u64 *tr = c->d_trace ? c->d_trace + 8 * (c->trace_next++ % c->trace_pairs) : nullptr;
+		a.trace = tr;
 		const uint32_t grid = std::min<uint32_t>(m, (uint32_t)(c->sm_count * c->ctas_per_sm));
 		cudaLaunchAttribute attr[1];
 		attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -165,6 +167,7 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, ui
 		e.carry_in = carry;
 		e.totals = c->d_ticket + 2 + 2 * c->totals_slot;
 		e.host_totals = c->d_h_totals;
+		e.trace = tr ? tr + 4 : nullptr;
 		// programmatic dependent launch (see the kernels): analysis of batch k+1 beside expansion of batch k
 		cudaLaunchConfig_t cfg = {};
 		cfg.gridDim = dim3((unsigned)c->expand_grid);
@@ -251,7 +254,7 @@ int mm_ctx_destroy(mm_ctx *c) {
 	if (c->own_stream) cudaStreamSynchronize(c->own_stream);
 	cudaFree(c->d_table); cudaFree(c->d_out_i); cudaFree(c->d_out_t); cudaFree(c->d_ranges_i);
 	cudaFree(c->d_ranges_t); cudaFree(c->d_cnt); cudaFree(c->d_desc_i); cudaFree(c->d_desc_t); cudaFree(c->d_flags); cudaFree(c->d_ticket);
-	cudaFree(c->d_in_chunks); cudaFree(c->d_in_offs);
+	cudaFree(c->d_in_chunks); cudaFree(c->d_in_offs); cudaFree(c->d_trace);
 	if (c->h_totals) cudaFreeHost(c->h_totals);
 	if (c->h_in) cudaFreeHost(c->h_in);
 	if (c->h_out) cudaFreeHost(c->h_out);
@@ -500,6 +503,28 @@ int mm_mesh_for_chunk(mm_ctx *c, const int64_t offs[3], const uint8_t chunk[MM_C
 	if (rc) return rc;
 	*vi = hm.intransparent; *ni = hm.n_intransparent;
 	*vt = hm.transparent; *nt = hm.n_transparent;
+	return MM_OK;
+}
+
+int mm_debug_trace(mm_ctx *c, uint32_t pairs, uint64_t *out, uint64_t *n_launched) {
+	if (!c) return MM_ERR_INVALID;
+	if (use_device(c)) return MM_ERR_CUDA;
+	MM_CUDA(c, cudaStreamSynchronize(c->stream));
+	if (out && c->d_trace) MM_CUDA(c, cudaMemcpy(out, c->d_trace, sizeof(mm::u64) * 8 * c->trace_pairs, cudaMemcpyDeviceToHost));
+	if (n_launched) *n_launched = c->trace_next;
+	if (pairs != c->trace_pairs) {
+		cudaFree(c->d_trace);
+		c->d_trace = nullptr;
+		c->trace_pairs = 0;
+		if (pairs) MM_CUDA(c, cudaMalloc(&c->d_trace, sizeof(mm::u64) * 8 * pairs));
+		c->trace_pairs = pairs;
+	}
+	if (c->d_trace) {  // minima start at all-ones, maxima at zero
+		std::vector<mm::u64> init((size_t)8 * pairs);
+		for (size_t i = 0; i < init.size(); i++) init[i] = (i & 2) ? 0ull : ~0ull;
+		MM_CUDA(c, cudaMemcpy(c->d_trace, init.data(), sizeof(mm::u64) * init.size(), cudaMemcpyHostToDevice));
+	}
+	c->trace_next = 0;
 	return MM_OK;
 }
 

@@ -40,6 +40,10 @@ struct mm_ctx {
 	mm::u64 *h_totals = nullptr;    // pinned + mapped, 2 words: the expand kernel writes the totals straight to the host
 	mm::u64 *d_h_totals = nullptr;  // the same words as the device sees them
 	bool time_next = false, last_timed = false;
+	// mm_debug_trace: device timeline of the last trace_pairs launch pairs (8 words per pair, ring)
+	mm::u64 *d_trace = nullptr;
+	uint32_t trace_pairs = 0;
+	uint64_t trace_next = 0;
 
 	// staged inputs for host callers
 	unsigned char *d_in_chunks = nullptr;

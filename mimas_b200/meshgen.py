@@ -364,6 +364,16 @@ class Mesher:
         self._ck(self._lib.mm_mesh_batch_host(self._ctx, C.c_void_p(chunks_ptr), C.c_void_p(offs_ptr), n, C.byref(hm)))
         return hm
 
+    def debug_trace(self, pairs: int) -> np.ndarray:
+        """Device timeline (ns) of the launch pairs since the previous call, shape (k, 2, 4): see
+        mm_debug_trace in the header.  Re-arms the ring with `pairs` records (0 = off)."""
+        armed = getattr(self, "_trace_pairs", 0)
+        have = np.zeros((max(armed, 1), 8), dtype=np.uint64)
+        n = C.c_uint64()
+        self._ck(self._lib.mm_debug_trace(self._ctx, pairs, have.ctypes.data, C.byref(n)))
+        self._trace_pairs = pairs
+        return have[:min(int(n.value), armed)].reshape(-1, 2, 4)
+
     def launch_count(self) -> int:
         v = C.c_uint64()
         self._ck(self._lib.mm_launch_count(self._ctx, C.byref(v)))
