@@ -110,7 +110,14 @@ int ensure_desc_capacity(mm_ctx *c, uint32_t n) {
 // previous one ended.
 // Nothing but kernels is enqueued for an untimed batch (the totals reach the host through mapped
 // pinned memory), so that back-to-back batches chain by programmatic dependent launch.
-int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, uint32_t n, bool timed) {
+struct Targets {  // where a batch's vertices and range records go
+	unsigned char *out_i, *out_t;
+	uint64_t cap_i, cap_t;
+	mm::Range *ranges_i, *ranges_t;
+};
+Targets device_targets(const mm_ctx *c) { return Targets{c->d_out_i, c->d_out_t, c->cap_i, c->cap_t, c->d_ranges_i, c->d_ranges_t}; }
+
+int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, uint32_t n, bool timed, const Targets &tg) {
 	int rc;
 	if ((rc = ensure_desc_capacity(c, n))) return rc;
 	c->last_timed = timed;
@@ -158,12 +165,12 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, ui
 		e.desc_t = a.desc_t;
 		e.cnt_i = a.cnt_i;
 		e.cnt_t = a.cnt_t;
-		e.out_i = c->d_out_i;
-		e.out_t = c->d_out_t;
-		e.cap_i = c->cap_i;
-		e.cap_t = c->cap_t;
-		e.ranges_i = c->d_ranges_i + first;
-		e.ranges_t = c->d_ranges_t + first;
+		e.out_i = tg.out_i;
+		e.out_t = tg.out_t;
+		e.cap_i = tg.cap_i;
+		e.cap_t = tg.cap_t;
+		e.ranges_i = tg.ranges_i + first;
+		e.ranges_t = tg.ranges_t + first;
 		e.carry_in = carry;
 		e.totals = c->d_ticket + 2 + 2 * c->totals_slot;
 		e.host_totals = c->d_h_totals;
@@ -224,6 +231,7 @@ int mm_ctx_create(int device, mm_ctx **out) {
 		if (occ2 < 1) return fail(c, MM_ERR_CUDA, "expand kernel does not fit on an SM");
 		c->expand_grid = c->sm_count * occ2;
 		c->use_pdl = getenv("MM_NO_PDL") == nullptr;
+		c->no_small = getenv("MM_NO_SMALL_PATH") != nullptr;
 		MM_CUDA(c, cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
 		c->stream = c->own_stream;
 		MM_CUDA(c, cudaEventCreate(&c->ev0));
@@ -257,6 +265,7 @@ int mm_ctx_destroy(mm_ctx *c) {
 	cudaFree(c->d_in_chunks); cudaFree(c->d_in_offs); cudaFree(c->d_trace);
 	if (c->h_totals) cudaFreeHost(c->h_totals);
 	if (c->h_in) cudaFreeHost(c->h_in);
+	if (c->h_small) cudaFreeHost(c->h_small);
 	if (c->h_out) cudaFreeHost(c->h_out);
 	if (c->ev0) cudaEventDestroy(c->ev0);
 	if (c->ev1) cudaEventDestroy(c->ev1);
@@ -372,7 +381,7 @@ int mm_mesh_batch_async(mm_ctx *c, const uint8_t *d_chunks, const int64_t *d_off
 	if (n == 0) { c->pending = true; return MM_OK; }
 	int rc;
 	if ((rc = ensure_chunk_capacity(c, n))) return rc;
-	if ((rc = launch(c, d_chunks, c->last_offs, n, c->time_next))) return rc;
+	if ((rc = launch(c, d_chunks, c->last_offs, n, c->time_next, device_targets(c)))) return rc;
 	c->time_next = false;
 	c->pending = true;
 	return MM_OK;
@@ -392,7 +401,7 @@ int mm_batch_finish(mm_ctx *c, mm_batch_out *out) {
 			int rc;  // grow to fit (+1/8 head room) and run again: the inputs are still resident
 			if ((rc = ensure_arena(c, &c->d_out_i, &c->cap_i, c->tot_i + c->tot_i / 8))) return rc;
 			if ((rc = ensure_arena(c, &c->d_out_t, &c->cap_t, c->tot_t + c->tot_t / 8))) return rc;
-			if ((rc = launch(c, c->last_chunks, c->last_offs, c->last_n, c->last_timed))) return rc;
+			if ((rc = launch(c, c->last_chunks, c->last_offs, c->last_n, c->last_timed, device_targets(c)))) return rc;
 		}
 		c->last_ms = 0.f;  // an untimed (mm_mesh_batch_async) batch enqueues kernels only
 		if (c->last_timed) MM_CUDA(c, cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1));
@@ -460,10 +469,59 @@ int mm_copy_out(mm_ctx *c, mm_vertex *vi, mm_vertex *vt, mm_range *ri, mm_range 
 	return MM_OK;
 }
 
+// Small batches (the reference's own call pattern is one chunk per call, client.rs:259-267) skip every
+// cudaMemcpy: the kernels read the chunks from, and write vertices and range records to, mapped pinned
+// host memory.  One memcpy in, two launches, one stream synchronise.  Returns MM_OK with *done = false
+// when the result does not fit the mapped arenas (the caller then takes the ordinary path).
+constexpr uint32_t kSmallChunks = 32;
+constexpr uint64_t kSmallQuadsI = 49152, kSmallQuadsT = 16384;  // 10.1 MiB + 3.4 MiB
+struct SmallLayout {
+	size_t chunks = 0, offs = chunks + (size_t)kSmallChunks * 4096, ranges_i = offs + (size_t)kSmallChunks * 24,
+	       ranges_t = ranges_i + (size_t)kSmallChunks * 16, out_i = (ranges_t + (size_t)kSmallChunks * 16 + 255) & ~(size_t)255,
+	       out_t = (out_i + kSmallQuadsI * mm::kQuadBytes + 16 + 255) & ~(size_t)255,
+	       total = out_t + kSmallQuadsT * mm::kQuadBytes + 16;
+};
+static int small_batch_host(mm_ctx *c, const uint8_t *chunks, const int64_t *offs, uint32_t n, mm_host_mesh *out, bool *done) {
+	*done = false;
+	if (!c->have_table) return fail(c, MM_ERR_NO_TABLE, "mm_set_block_table has not been called");
+	const SmallLayout L;
+	if (!c->h_small) {
+		MM_CUDA(c, cudaStreamSynchronize(c->stream));
+		MM_CUDA(c, cudaHostAlloc(&c->h_small, L.total, cudaHostAllocMapped));
+		MM_CUDA(c, cudaHostGetDevicePointer((void **)&c->d_small, c->h_small, 0));
+	}
+	memcpy(c->h_small + L.chunks, chunks, (size_t)n * 4096);
+	memcpy(c->h_small + L.offs, offs, (size_t)n * 24);
+	Targets tg{c->d_small + L.out_i, c->d_small + L.out_t, kSmallQuadsI, kSmallQuadsT,
+	           (mm::Range *)(c->d_small + L.ranges_i), (mm::Range *)(c->d_small + L.ranges_t)};
+	c->pending = c->finished = false;  // the device arenas hold no batch of this call
+	c->last_launches = 0;
+	int rc;
+	if ((rc = launch(c, c->d_small + L.chunks, (const long long *)(c->d_small + L.offs), n, false, tg))) return rc;
+	MM_CUDA(c, cudaStreamSynchronize(c->stream));
+	const uint64_t ti = c->h_totals[0], tt = c->h_totals[1];
+	if (ti > kSmallQuadsI || tt > kSmallQuadsT) return MM_OK;  // nothing was written: ordinary path
+	out->intransparent = (const mm_vertex *)(c->h_small + L.out_i);
+	out->transparent = (const mm_vertex *)(c->h_small + L.out_t);
+	out->ranges_i = (const mm_range *)(c->h_small + L.ranges_i);
+	out->ranges_t = (const mm_range *)(c->h_small + L.ranges_t);
+	out->n_intransparent = ti * 6;
+	out->n_transparent = tt * 6;
+	out->n_chunks = n;
+	out->reserved = 0;
+	*done = true;
+	return MM_OK;
+}
+
 int mm_mesh_batch_host(mm_ctx *c, const uint8_t *chunks, const int64_t *offs, uint32_t n, mm_host_mesh *out) {
 	if (!c || !out || (n && (!chunks || !offs))) return MM_ERR_INVALID;
 	if (use_device(c)) return MM_ERR_CUDA;
 	int rc;
+	if (n && n <= kSmallChunks && !c->no_small) {
+		bool done = false;
+		if ((rc = small_batch_host(c, chunks, offs, n, out, &done))) return rc;
+		if (done) return MM_OK;
+	}
 	// pageable inputs are staged through pinned memory so that the H2D copy is one DMA;
 	// inputs already in page-locked memory (mm_host_alloc) go out directly
 	const uint8_t *hc = chunks;

@@ -52,6 +52,10 @@ struct mm_ctx {
 	unsigned char *h_in = nullptr;  // pinned staging: chunks then offs
 	size_t h_in_bytes = 0;
 
+	// small-batch path: one mapped pinned block holding inputs, range records and both vertex streams
+	unsigned char *h_small = nullptr, *d_small = nullptr;
+	bool no_small = false;
+
 	// host results (pinned)
 	unsigned char *h_out = nullptr;
 	size_t h_out_bytes = 0;
