@@ -27,6 +27,7 @@
 //      copy (TMA) stores to the packed vertex stream.
 #pragma once
 #include <stdint.h>
+#include <string.h>
 
 #if defined(__CUDACC__)
 #define MM_HD __host__ __device__ __forceinline__
@@ -84,7 +85,6 @@ struct Col {
 struct alignas(128) ChunkSmem {
 	// the chunk itself, filled by one bulk async copy (TMA)
 	alignas(128) unsigned char raw[4096];
-	// phases A-B: id-equality masks Ey (vs column (x, y-1)) and Ex (vs (x-1, y)), [x*16 + y], 2 x 512 B;
 	// phase D: wl, the list of non-empty 32-bit words of S (two rows each) with their quad offsets;
 	// plants: Cz, the crossed mask over z per column
 	alignas(16) uint32_t u[768];
@@ -102,8 +102,6 @@ struct alignas(128) ChunkSmem {
 	alignas(8) unsigned long long mbar;        // mbarrier of the chunk load (device only)
 };
 
-MM_HD uint16_t *smem_Ey(ChunkSmem &s) { return reinterpret_cast<uint16_t *>(s.u); }
-MM_HD uint16_t *smem_Ex(ChunkSmem &s) { return reinterpret_cast<uint16_t *>(s.u) + 256; }
 MM_HD unsigned char *smem_raw(ChunkSmem &s) { return s.raw; }
 MM_HD uint16_t *smem_Bzp(ChunkSmem &s) { return s.Bzp; }
 MM_HD const uint16_t *smem_Bzp(const ChunkSmem &s) { return s.Bzp; }
@@ -210,6 +208,18 @@ MM_HD void init_warp_smem(ChunkSmem &s, int lane) {
 	}
 }
 
+// 16 block ids of one column from the chunk in shared memory (16-byte aligned)
+MM_HD Col load_col(const uint8_t *p) {
+	Col c;
+#if defined(__CUDA_ARCH__)
+	const uint4 v = *reinterpret_cast<const uint4 *>(p);
+	c.w[0] = v.x; c.w[1] = v.y; c.w[2] = v.z; c.w[3] = v.w;
+#else
+	memcpy(c.w, p, 16);
+#endif
+	return c;
+}
+
 // ---- phase A: one column (x, y) ------------------------------------------------------
 // Blocky mask over z (bit z <=> cell (x, y, z) is drawn as a cube, i.e. get_bl_tex_ids is
 // Some, lib.rs:105-109) in the return value; `orf` receives the OR of the column's flag bytes.
@@ -298,7 +308,6 @@ MM_HD void col_starts(ChunkSmem &s, const TabEntry *tab, const uint8_t *chunk, i
 	const uint32_t bym = B[-1], byp = B[1], bxm = B[-kBzStride], bxp = B[kBzStride];
 	const uint32_t bmm = B[-kBzStride - 1], bpm = B[kBzStride - 1], bmp = B[-kBzStride + 1];
 	const int col = x * 16 + y;
-	const uint32_t ey = smem_Ey(s)[col], ex = smem_Ex(s)[col];
 	// own faces
 	const uint32_t V1 = b & ~(b << 1), V4 = b & ~(b >> 1);   // [0,0,-1] lib.rs:317, [0,0,1] lib.rs:365
 	const uint32_t V3 = b & ~bxm, V6 = b & ~bxp;             // [-1,0,0] lib.rs:349, [1,0,0] lib.rs:397
@@ -308,6 +317,15 @@ MM_HD void col_starts(ChunkSmem &s, const TabEntry *tab, const uint8_t *chunk, i
 	const uint32_t Q1 = V1 & bym & ~(bym << 1), Q4 = V4 & bym & ~(bym >> 1);
 	const uint32_t Q3 = V3 & bym & ~bmm, Q6 = V6 & bym & ~bpm;
 	const uint32_t Q2 = V2 & bxm & ~bmm, Q5 = V5 & bxm & ~bmp;
+	// Runs merge on equal textures; equal block ids are equal textures, and the id-equality masks
+	// against the previous column are only worked out where two visible faces meet at all.
+	const uint32_t qy = Q1 | Q3 | Q4 | Q6, qx = Q2 | Q5;
+	uint32_t ey = 0, ex = 0;
+	if (qy | qx) {
+		const Col own = load_col(chunk + col * 16);
+		if (qy) ey = eq_mask16(own, load_col(chunk + (col - 1) * 16));    // (x, y-1): exists, its blocky mask is not empty
+		if (qx) ex = eq_mask16(own, load_col(chunk + (col - 16) * 16));   // (x-1, y)
+	}
 	uint32_t e1 = ey, e3 = ey, e4 = ey, e6 = ey, e2 = ex, e5 = ex;
 	// rare: visible neighbours with different ids in a chunk where different ids may share a texture
 	if ((amb & kFlagAmbAny) && (((Q1 | Q3 | Q4 | Q6) & ~ey) | ((Q2 | Q5) & ~ex))) {

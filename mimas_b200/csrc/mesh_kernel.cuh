@@ -36,7 +36,7 @@ constexpr int kThreads = kWarpsPerCta * 32;
 #define MM_EXPAND_WARPS 12
 #endif
 #ifndef MM_EXPAND_MINBLOCKS
-#define MM_EXPAND_MINBLOCKS 1
+#define MM_EXPAND_MINBLOCKS 3
 #endif
 #ifndef MM_EXPAND_PREFETCH
 #define MM_EXPAND_PREFETCH 0
@@ -197,19 +197,31 @@ __global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(co
 		}
 		mbar_wait(&s.mbar, par);
 
-		// A. thread <-> columns col = tid, tid + 128 (col = x*16 + y): blocky masks and id-equality masks
+		// A. thread <-> columns col = tid, tid + 128 (col = x*16 + y): blocky mask over z per column
 		uint32_t crossed_cols = 0, amb = 0;
+		Col own[256 / kThreads];
+		bool uniform = true;
+#pragma unroll
+		for (int j = 0; j < 256 / kThreads; j++) {
+			own[j] = load_col(raw + (kThreads * j + tid) * 16);
+			const uint32_t w0 = own[j].w[0];
+			uniform = uniform && w0 == own[j].w[1] && w0 == own[j].w[2] && w0 == own[j].w[3] &&
+			          w0 == __byte_perm(w0, 0, 0) && w0 == *reinterpret_cast<const uint32_t *>(raw);
+		}
+		// a chunk of one undrawn id (all air: a quarter of a terrain region) is done here
+		if (__syncthreads_and(uniform) && (flags[raw[0]] & (kFlagBlocky | kFlagCrossed)) == 0) {
+			if (tid == 0) {
+				p.cnt_i[c] = 0;
+				p.cnt_t[c] = 0;
+			}
+			continue;
+		}
 #pragma unroll
 		for (int j = 0; j < 256 / kThreads; j++) {
 			const int col = kThreads * j + tid;
-			const Col own = lds_col(raw + col * 16);
-			const Col ny = lds_col(raw + ((col - 1) & 255) * 16);   // (x, y-1); unused garbage for y = 0
-			const Col nx = lds_col(raw + ((col - 16) & 255) * 16);  // (x-1, y); unused garbage for x = 0
 			uint32_t orf;
-			const uint32_t bz = col_flags(flags, own, orf);
+			const uint32_t bz = col_flags(flags, own[j], orf);
 			smem_Bzp(s)[((col >> 4) + 1) * kBzStride + (col & 15) + 1] = (uint16_t)bz;
-			smem_Ey(s)[col] = (uint16_t)eq_mask16(own, ny);
-			smem_Ex(s)[col] = (uint16_t)eq_mask16(own, nx);
 			crossed_cols |= ((orf >> 1) & 1u) << j;
 			amb |= orf;
 		}
@@ -244,7 +256,7 @@ __global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(co
 					s.nwords = run >> 16;
 				}
 			}
-			__syncthreads();  // also: Ey / Ex are dead, wl takes their place
+			__syncthreads();
 			if (tid >= 32) list_group_words(s, tid - 32, s.gcnt[tid - 32]);
 			__syncthreads();
 			// D. descriptors: thread <-> non-empty word (two rows)
@@ -366,10 +378,13 @@ __device__ __forceinline__ void block_scan_counts(const uint32_t *cnt_i, const u
 	__syncthreads();
 }
 
-// largest c in [0, n) with pre[c] <= q  (q < pre[n]); `top` = highest power of two <= n
-__device__ __forceinline__ uint32_t find_chunk(const uint32_t *pre, uint32_t q, uint32_t top) {
+// largest c in [0, n) with pre[c] <= q  (q < pre[n]).  pre[] is filled up to kMaxLaunchChunks with
+// 0xffffffff beyond n, so a search of fixed depth needs no bounds: 12 steps of load, compare, add.
+__device__ __forceinline__ uint32_t find_chunk(const uint32_t *pre, uint32_t q) {
+	static_assert(kMaxLaunchChunks == 4096, "12 fixed steps");
 	uint32_t lo = 0;
-	for (uint32_t step = top; step >= 1; step >>= 1)
+#pragma unroll
+	for (uint32_t step = kMaxLaunchChunks / 2; step >= 1; step >>= 1)
 		if (pre[lo + step] <= q) lo += step;
 	return lo;
 }
@@ -384,10 +399,7 @@ __global__ void __launch_bounds__(kExpandThreads, MM_EXPAND_MINBLOCKS) expand_ke
 	unsigned char *stage = smem_raw_bytes + 2048 + 2 * 4 * kExpandPrefixWords + 256 + (size_t)warp * (kStageBytes + 16);
 
 	if (tid < 128) reinterpret_cast<uint4 *>(tab)[tid] = __ldg(reinterpret_cast<const uint4 *>(p.table) + tid);
-	uint32_t top = 1;
-	while (top * 2u <= p.n) top *= 2u;
-	if (top == p.n) top >>= 1;  // the steps top, top/2, .., 1 then reach exactly [0, 2*top) >= [0, n)
-	const uint32_t lim = ((max(p.n, 2u * top) + 3u) & ~3u);
+	const uint32_t lim = kMaxLaunchChunks;  // find_chunk() may touch every entry below that
 	// Programmatic dependent launch.  The analysis of this batch has completed once the wait returns,
 	// and with it (its CTAs end in a wait of their own) the expansion of the previous batch: the
 	// arenas and the other half of the hand-over buffers are free.  Only then may the next analysis
@@ -437,7 +449,7 @@ __global__ void __launch_bounds__(kExpandThreads, MM_EXPAND_MINBLOCKS) expand_ke
 		f.d = 0; f.ox = 0; f.oy = 0; f.oz = 0;
 		if (q < (face ? tot_i : tot_t)) {
 			const uint32_t *pre = face ? pre_i : pre_t;
-			const uint32_t c = find_chunk(pre, q, top);
+			const uint32_t c = find_chunk(pre, q);
 			const uint32_t r = q - pre[c];
 			f.d = face ? __ldg(p.desc_i + (size_t)c * kDescStrideI + r) : __ldg(p.desc_t + (size_t)c * kDescStrideT + (r >> 2));
 			f.ox = __ldg(p.offs + 3 * (size_t)c);

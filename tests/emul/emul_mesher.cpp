@@ -25,12 +25,6 @@ static void store_tile(unsigned char *g, const unsigned char *sp, uint32_t bytes
 	if (bytes - head - body) memcpy(g + head + body, sp + head + body, 8);
 }
 
-static Col load_col(const uint8_t *chunk, int x, int y) {
-	Col c;
-	memcpy(c.w, chunk + (x * 16 + y) * 16, 16);
-	return c;
-}
-
 extern "C" void emul_transpose16(uint16_t rows[16]) {
 	uint32_t w[8];
 	for (int k = 0; k < 8; k++) w[k] = rows[2 * k] | ((uint32_t)rows[2 * k + 1] << 16);
@@ -66,28 +60,28 @@ extern "C" int emul_mesh_batch(const uint8_t *chunks, const int64_t *offs, uint3
 		const uint8_t *raw = smem_raw(s);
 		// A
 		uint32_t amb = 0;
-		uint32_t crossed_cols[kLanes] = {0};
-		for (int j = 0; j < 8; j++)
-			for (int lane = 0; lane < kLanes; lane++) {
-				const int col = 32 * j + lane, h = lane >> 4, y = lane & 15, x = 2 * j + h;
-				const Col own = load_col(raw, x, y);
-				Col ny, nx;  // what the kernel loads: wrapped-around garbage at y = 0 / x = 0
-				memcpy(ny.w, raw + ((col - 1) & 255) * 16, 16);
-				memcpy(nx.w, raw + ((col - 16) & 255) * 16, 16);
+		uint32_t crossed_cols[kLanes * 4] = {0};
+		bool uniform = true;
+		for (int i = 1; i < 4096; i++) uniform = uniform && raw[i] == raw[0];
+		if (uniform && (flags[raw[0]] & (kFlagBlocky | kFlagCrossed)) == 0) {  // the kernel's all-air exit
+			cnt_i[c] = 0;
+			cnt_t[c] = 0;
+			continue;
+		}
+		for (int j = 0; j < 2; j++)
+			for (int tid = 0; tid < 128; tid++) {
+				const int col = 128 * j + tid;
 				uint32_t orf;
-				const uint32_t bz = col_flags(flags, own, orf);
-				smem_Bzp(s)[(x + 1) * kBzStride + y + 1] = (uint16_t)bz;
-				smem_Ey(s)[col] = (uint16_t)eq_mask16(own, ny);
-				smem_Ex(s)[col] = (uint16_t)eq_mask16(own, nx);
-				crossed_cols[lane] |= ((orf >> 1) & 1u) << j;
+				const uint32_t bz = col_flags(flags, load_col(raw + col * 16), orf);
+				smem_Bzp(s)[((col >> 4) + 1) * kBzStride + (col & 15) + 1] = (uint16_t)bz;
+				crossed_cols[tid] |= ((orf >> 1) & 1u) << j;
 				amb |= orf;
 			}
 		uint32_t nq = 0, npl = 0;
 		uint32_t *di = desc_i.data() + (size_t)c * kDescStrideI;
 		if (amb & kFlagBlocky) {
 			// B
-			for (int j = 0; j < 8; j++)
-				for (int lane = 0; lane < kLanes; lane++) col_starts(s, tab, raw, 2 * j + (lane >> 4), lane & 15, amb);
+			for (int col = 0; col < 256; col++) col_starts(s, tab, raw, col >> 4, col & 15, amb);
 			// C
 			for (int lane = 0; lane < kLanes; lane++) transpose_blocky(s, lane);
 			uint32_t run = 0;
@@ -109,11 +103,10 @@ extern "C" int emul_mesh_batch(const uint8_t *chunks, const int64_t *offs, uint3
 		}
 		if (amb & kFlagCrossed) {
 			uint16_t *Cz = smem_Cz(s);
-			for (int j = 0; j < 8; j++)
-				for (int lane = 0; lane < kLanes; lane++) {
-					const int h = lane >> 4, y = lane & 15, x = 2 * j + h;
-					Cz[32 * j + lane] =
-					    (uint16_t)(((crossed_cols[lane] >> j) & 1u) ? col_crossed(flags, load_col(raw, x, y)) : 0u);
+			for (int j = 0; j < 2; j++)
+				for (int tid = 0; tid < 128; tid++) {
+					const int col = 128 * j + tid;
+					Cz[col] = (uint16_t)(((crossed_cols[tid] >> j) & 1u) ? col_crossed(flags, load_col(raw + col * 16)) : 0u);
 				}
 			for (int lane = 0; lane < kLanes; lane++) {
 				const uint32_t mine = count_plants8(s, lane);
