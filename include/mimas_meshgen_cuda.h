@@ -202,6 +202,41 @@ int mm_host_free(mm_ctx *ctx, void *h_ptr);
 int mm_device_info(mm_ctx *ctx, int *sm_count, int *ctas_per_sm, int *threads_per_cta);
 /* Number of mesher kernels this context has launched since creation. */
 int mm_launch_count(mm_ctx *ctx, uint64_t *launches);
+
+/* ---- headless consumer of the vertex stream (GL itself is unavailable on this box) ----
+ * What the reference does with the meshes every frame, up to the rasteriser: chunk culling
+ * (mimas-client/client.rs:679-696: viewing range on the chunk origin, then frustum_query's sphere test on
+ * the chunk centre with r = 16*sqrt(3)) and the vertex shader (mimas-client/vertex-shader.glsl:18-27).
+ * Matrices are the `[[f32; 4]; 4]` uniforms of client.rs:599-600: column-major, m[4*col + row]. */
+typedef struct mm_camera {
+	float vmatrix[16];       /* Camera::get_matrix, client.rs:1388-1393 */
+	float pmatrix[16];       /* Camera::get_perspective, client.rs:1395-1400 */
+	float pos[3];            /* camera.pos, client.rs:677 */
+	float viewing_range;     /* config.viewing_range, client.rs:682 */
+} mm_camera;
+typedef struct mm_shaded_vertex {   /* the outputs of vertex-shader.glsl */
+	float clip[4];           /* gl_Position */
+	float vposition[4];
+	float vlamb;
+	float vtex_pos[2];
+	uint32_t vtex_ind;
+} mm_shaded_vertex;
+typedef struct mm_draw_out {
+	const mm_shaded_vertex *d_shaded;  /* visible chunks in chunk order: all intransparent meshes, then all transparent (client.rs:699-701) */
+	const uint32_t *d_draw_list;       /* indices of the drawn chunks, ascending */
+	uint64_t n_shaded_i, n_shaded_t;   /* vertices */
+	uint32_t n_drawn, n_chunks;
+	float kernel_ms;
+	uint32_t reserved;
+} mm_draw_out;
+/* vertex shader over n device-resident vertices */
+int mm_vertex_stage(mm_ctx *ctx, const mm_vertex *d_in, uint64_t n, const mm_camera *cam, mm_shaded_vertex *d_out);
+/* client.rs:679-696 over n chunk origins (host or device pointer); h_draw (n entries, host) receives the drawn indices */
+int mm_cull_chunks(mm_ctx *ctx, const int64_t *offs, uint32_t n, const mm_camera *cam, uint32_t *h_draw, uint32_t *n_drawn);
+/* one frame over the last finished device batch (mm_mesh_batch / mm_batch_finish): cull its chunks, shade the
+ * visible ones.  Results stay in library-owned device memory until the next call. */
+int mm_draw_batch(mm_ctx *ctx, const mm_camera *cam, mm_draw_out *out);
+
 /* Development aid, no reference counterpart: device timeline (%globaltimer, ns) of the launch pairs since
  * the previous call, as a ring of `pairs` records of 8 words: analyse {first CTA start, -, last CTA out of
  * work, last CTA end}, expand {first CTA start, first CTA past its dependency wait, -, last CTA end}.

@@ -21,7 +21,7 @@ SYMBOLS = (
     "mm_batch_finish", "mm_copy_out", "mm_mesh_batch_host", "mm_mesh_for_chunk", "mm_push_blocks",
     "mm_gen_terrain_host", "mm_gen_terrain_device", "mm_dev_alloc", "mm_dev_free", "mm_dev_upload",
     "mm_dev_download", "mm_ctx_sync", "mm_device_info", "mm_host_alloc", "mm_host_free", "mm_launch_count",
-    "mm_debug_trace",
+    "mm_debug_trace", "mm_vertex_stage", "mm_cull_chunks", "mm_draw_batch",
 )
 
 

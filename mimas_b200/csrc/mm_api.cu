@@ -266,6 +266,10 @@ int mm_ctx_destroy(mm_ctx *c) {
 	if (c->h_totals) cudaFreeHost(c->h_totals);
 	if (c->h_in) cudaFreeHost(c->h_in);
 	if (c->h_small) cudaFreeHost(c->h_small);
+	if (c->h_draw_totals) cudaFreeHost(c->h_draw_totals);
+	cudaFree(c->d_cull); cudaFree(c->d_shaded);
+	if (c->ev2) cudaEventDestroy(c->ev2);
+	if (c->ev3) cudaEventDestroy(c->ev3);
 	if (c->h_out) cudaFreeHost(c->h_out);
 	if (c->ev0) cudaEventDestroy(c->ev0);
 	if (c->ev1) cudaEventDestroy(c->ev1);

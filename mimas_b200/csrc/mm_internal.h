@@ -70,6 +70,14 @@ struct mm_ctx {
 	uint64_t tot_i = 0, tot_t = 0;  // quads
 	float last_ms = 0.f;
 
+	// headless draw (mm_render.cu): scratch of mm_cull_chunks / mm_draw_batch
+	unsigned char *d_cull = nullptr;   // flags, draw list, per-visible-chunk output offsets, block sums
+	size_t cull_bytes = 0;
+	unsigned char *d_shaded = nullptr;
+	size_t shaded_bytes = 0;
+	cudaEvent_t ev2 = nullptr, ev3 = nullptr;
+	unsigned long long *h_draw_totals = nullptr, *d_h_draw_totals = nullptr;  // mapped pinned: drawn chunks, vertices i, t
+
 	char err[512] = {0};
 };
 

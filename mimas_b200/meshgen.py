@@ -364,6 +364,28 @@ class Mesher:
         self._ck(self._lib.mm_mesh_batch_host(self._ctx, C.c_void_p(chunks_ptr), C.c_void_p(offs_ptr), n, C.byref(hm)))
         return hm
 
+    # -- headless draw: culling + vertex shader on the device (render.py, csrc/mm_render.cu) ---------
+    def cull_chunks(self, offs, cam) -> np.ndarray:
+        """client.rs:679-696: indices (ascending) of the chunks a frame would draw."""
+        offs = np.ascontiguousarray(offs, dtype=np.int64).reshape(-1, 3)
+        draw = np.zeros(max(len(offs), 1), dtype=np.uint32)
+        n = C.c_uint32()
+        cc = cam.to_c()
+        self._ck(self._lib.mm_cull_chunks(self._ctx, offs.ctypes.data, len(offs), C.byref(cc), draw.ctypes.data, C.byref(n)))
+        return draw[:n.value].copy()
+
+    def vertex_stage(self, d_in: int, n: int, cam, d_out: int):
+        cc = cam.to_c()
+        self._ck(self._lib.mm_vertex_stage(self._ctx, C.c_void_p(d_in), C.c_uint64(n), C.byref(cc), C.c_void_p(d_out)))
+
+    def draw_batch(self, cam):
+        """One frame over the last finished device batch: returns render.DrawOut (device pointers)."""
+        from .render import DrawOut
+        out = DrawOut()
+        cc = cam.to_c()
+        self._ck(self._lib.mm_draw_batch(self._ctx, C.byref(cc), C.byref(out)))
+        return out
+
     def debug_trace(self, pairs: int) -> np.ndarray:
         """Device timeline (ns) of the launch pairs since the previous call, shape (k, 2, 4): see
         mm_debug_trace in the header.  Re-arms the ring with `pairs` records (0 = off)."""

@@ -161,3 +161,56 @@ def mesh_batch(chunks, offs, cache: Cache, threads: int = 1, discard: bool = Fal
                       threads, C.byref(secs))
     return dict(intransparent=vi, transparent=vt, count_i=ci, count_t=ct,
                 first_i=fi, first_t=ft, seconds=secs.value)
+
+
+# ---- render oracle (oracle/render_oracle.c): culling + vertex shader restatement ----------------------
+class RoCamera(C.Structure):
+    _fields_ = [("vmatrix", C.c_float * 16), ("pmatrix", C.c_float * 16), ("pos", C.c_float * 3),
+                ("viewing_range", C.c_float)]
+
+
+SHADED_DTYPE = np.dtype([("clip", "<f4", (4,)), ("vposition", "<f4", (4,)), ("vlamb", "<f4"),
+                         ("vtex_pos", "<f4", (2,)), ("vtex_ind", "<u4")])
+_rlib = None
+
+
+def _render():
+    global _rlib
+    if _rlib is None:
+        subprocess.run(["make", "-C", HERE, "-s"], check=True)
+        _rlib = C.CDLL(os.path.join(HERE, "librender_oracle.so"))
+        _rlib.ro_cull_chunks.restype = C.c_uint32
+    return _rlib
+
+
+def _ro_camera(vmatrix, pmatrix, pos, viewing_range) -> RoCamera:
+    cam = RoCamera()
+    cam.vmatrix[:] = [float(v) for v in np.asarray(vmatrix, dtype=np.float32).reshape(-1)]
+    cam.pmatrix[:] = [float(v) for v in np.asarray(pmatrix, dtype=np.float32).reshape(-1)]
+    cam.pos[:] = [float(v) for v in pos]
+    cam.viewing_range = float(viewing_range)
+    return cam
+
+
+def cull_chunks(offs, vmatrix, pmatrix, pos, viewing_range) -> np.ndarray:
+    offs = np.ascontiguousarray(offs, dtype=np.int64).reshape(-1, 3)
+    draw = np.zeros(max(len(offs), 1), dtype=np.uint32)
+    cam = _ro_camera(vmatrix, pmatrix, pos, viewing_range)
+    n = _render().ro_cull_chunks(offs.ctypes.data_as(C.c_void_p), C.c_uint32(len(offs)), C.byref(cam), draw.ctypes.data_as(C.c_void_p))
+    return draw[:n].copy()
+
+
+def vertex_stage(verts, vmatrix, pmatrix) -> np.ndarray:
+    verts = np.ascontiguousarray(verts, dtype=VERTEX_DTYPE)
+    out = np.zeros(len(verts), dtype=SHADED_DTYPE)
+    cam = _ro_camera(vmatrix, pmatrix, (0, 0, 0), 0)
+    _render().ro_vertex_stage(verts.ctypes.data_as(C.c_void_p), C.c_uint64(len(verts)), C.byref(cam), out.ctypes.data_as(C.c_void_p))
+    return out
+
+
+def frustum_planes(vmatrix, pmatrix) -> np.ndarray:
+    pl = np.zeros((6, 4), dtype=np.float32)
+    v = np.ascontiguousarray(vmatrix, dtype=np.float32).reshape(-1)
+    p = np.ascontiguousarray(pmatrix, dtype=np.float32).reshape(-1)
+    _render().ro_frustum(v.ctypes.data_as(C.c_void_p), p.ctypes.data_as(C.c_void_p), pl.ctypes.data_as(C.c_void_p))
+    return pl
