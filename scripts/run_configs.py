@@ -216,11 +216,58 @@ def cfg5(m, stream):
                        "65536_sampled_counts_equal": counts_ok, "2048_sampled_chunks_bit_exact": bool(sample_ok)}}
 
 
+def cfg_draw(m, stream):
+    """one frame over the view-radius-32 region (21125 chunks): culling (client.rs:679-696)
+    + vertex shader (vertex-shader.glsl:18-27) on the device; then the vertex shader over the whole stream."""
+    from mimas_b200.render import SHADED_DTYPE, Camera
+    r = 32
+    dims = (2 * r + 1, 2 * r + 1, 5)
+    n = dims[0] * dims[1] * dims[2]
+    dc, do = m.dev_alloc(n * 4096), m.dev_alloc(n * 24)
+    m.gen_terrain_device(78, (-r, -r, -2), dims, dc, do)
+    out = m.mesh_batch_device(dc, do, n)
+    offs = m.download(do, n * 24).view(np.int64).reshape(n, 3)
+    frames = []
+    for cam in (Camera(pos=(8.0, 8.0, 24.0), pitch=-10.0, yaw=30.0, viewing_range=128.0),
+                Camera(pos=(8.0, 8.0, 24.0), pitch=-25.0, yaw=-100.0, viewing_range=512.0),
+                Camera(pos=(-200.0, 150.0, 40.0), pitch=-30.0, yaw=20.0, viewing_range=1e6)):
+        m.draw_batch(cam)
+        ms = [m.draw_batch(cam).kernel_ms for _ in range(7)]
+        d = m.draw_batch(cam)
+        want = oracle.cull_chunks(offs, cam.get_matrix(), cam.get_perspective(), cam.pos, cam.viewing_range)
+        ok = m.download(d.d_draw_list, 4 * d.n_drawn).view(np.uint32).tolist() == want.tolist()
+        nv = int(d.n_shaded_i + d.n_shaded_t)
+        t = float(np.median(ms)) * 1e-3
+        alg = n * (24 + 32) + nv * (36 + 48)  # chunk origins + both range records read; per drawn vertex 36 B in, 48 B out
+        frames.append({"viewing_range": cam.viewing_range, "drawn_chunks": int(d.n_drawn), "of": n, "shaded_vertices": nv,
+                       "frame_ms": t * 1e3, "algorithmic_gbs": alg / t / 1e9, "draw_list_equals_restatement": bool(ok)})
+    # vertex shader alone over every vertex of the region
+    nv = int(out.n_intransparent)
+    d_out = m.dev_alloc(48 * nv)
+    cam = Camera(pos=(1, 2, 3), pitch=5, yaw=6)
+    m.set_stream(stream.cuda_stream)
+    m.vertex_stage(out.d_intransparent, nv, cam, d_out)
+    t = timed(stream, lambda: m.vertex_stage(out.d_intransparent, nv, cam, d_out), reps=20) * 1e-3
+    m.set_stream(0)
+    idx = np.random.RandomState(2).choice(nv, 4096, replace=False)
+    vin = m.download(out.d_intransparent, 36 * nv).view(mimas_b200.meshgen.VERTEX_DTYPE)
+    got = m.download(d_out, 48 * nv).view(SHADED_DTYPE)
+    want = oracle.vertex_stage(vin, cam.get_matrix(), cam.get_perspective())
+    res = {"config": "headless frame over the radius-32 region (21125 terrain chunks): device culling + vertex shader",
+           "frames": frames,
+           "vertex_stage_all": {"vertices": nv, "ms": t * 1e3, "algorithmic_gbs": nv * 84 / t / 1e9,
+                                "frac_of_measured_peak": nv * 84 / t / 1e9 / PEAK, "bit_exact_vs_restatement": bool(got.tobytes() == want.tobytes())}}
+    m.dev_free(d_out)
+    m.dev_free(dc)
+    m.dev_free(do)
+    return res
+
+
 def main():
-    which = [a for a in sys.argv[1:] if a.startswith("cfg")] or ["cfg1", "cfg3", "cfg4", "cfg5"]
+    which = [a for a in sys.argv[1:] if a.startswith("cfg")] or ["cfg1", "cfg3", "cfg4", "cfg5", "cfg_draw"]
     m = mimas_b200.Mesher(0, mimas_b200.default_cache())
     stream = torch.cuda.Stream()
-    fns = {"cfg1": cfg1, "cfg3": cfg3, "cfg4": cfg4, "cfg5": cfg5}
+    fns = {"cfg1": cfg1, "cfg3": cfg3, "cfg4": cfg4, "cfg5": cfg5, "cfg_draw": cfg_draw}
     for w in which:
         t0 = time.time()
         r = fns[w](m, stream)
