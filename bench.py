@@ -38,6 +38,26 @@ def region_origin(rank: int, r: int):
     return (-16 + 32 * r, -16 + 32 * rank, -2)
 
 
+def make_reducers(world: int, device: str):
+    """barrier / max-over-ranks / sum-over-ranks: the only uses of torch.distributed in the bench (the data
+    path has no collective: chunks are independent, every rank meshes its own shard)."""
+    import torch
+    import torch.distributed as dist
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    def reduce(x: float, op) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=device)
+        dist.all_reduce(t, op=op)
+        return float(t.item())
+
+    return barrier, (lambda x: reduce(x, dist.ReduceOp.MAX)), (lambda x: reduce(x, dist.ReduceOp.SUM))
+
+
 def checkerboard(n, parity0=0):
     idx = np.arange(4096)
     base = ((idx >> 8) + ((idx >> 4) & 15) + (idx & 15)) & 1
@@ -211,23 +231,7 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-
-    def max_over_ranks(x: float) -> float:
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    def sum_over_ranks(x: float) -> float:
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
+    barrier, max_over_ranks, sum_over_ranks = make_reducers(world, "cuda")
 
     mesher = mimas_b200.Mesher(local_rank, mimas_b200.default_cache())
     stream = torch.cuda.Stream()
