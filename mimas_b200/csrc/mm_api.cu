@@ -232,6 +232,7 @@ int mm_ctx_create(int device, mm_ctx **out) {
 		c->expand_grid = c->sm_count * occ2;
 		c->use_pdl = getenv("MM_NO_PDL") == nullptr;
 		c->no_small = getenv("MM_NO_SMALL_PATH") != nullptr;
+		if (const char *e = getenv("MM_MAPPED_MAX_CHUNKS")) c->mapped_max_chunks = (uint32_t)strtoul(e, nullptr, 10);
 		MM_CUDA(c, cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
 		c->stream = c->own_stream;
 		MM_CUDA(c, cudaEventCreate(&c->ev0));
@@ -473,55 +474,93 @@ int mm_copy_out(mm_ctx *c, mm_vertex *vi, mm_vertex *vt, mm_range *ri, mm_range 
 	return MM_OK;
 }
 
-// Small batches (the reference's own call pattern is one chunk per call, client.rs:259-267) skip every
-// cudaMemcpy: the kernels read the chunks from, and write vertices and range records to, mapped pinned
-// host memory.  One memcpy in, two launches, one stream synchronise.  Returns MM_OK with *done = false
-// when the result does not fit the mapped arenas (the caller then takes the ordinary path).
-constexpr uint32_t kSmallChunks = 32;
-constexpr uint64_t kSmallQuadsI = 49152, kSmallQuadsT = 16384;  // 10.1 MiB + 3.4 MiB
-struct SmallLayout {
-	size_t chunks = 0, offs = chunks + (size_t)kSmallChunks * 4096, ranges_i = offs + (size_t)kSmallChunks * 24,
-	       ranges_t = ranges_i + (size_t)kSmallChunks * 16, out_i = (ranges_t + (size_t)kSmallChunks * 16 + 255) & ~(size_t)255,
-	       out_t = (out_i + kSmallQuadsI * mm::kQuadBytes + 16 + 255) & ~(size_t)255,
-	       total = out_t + kSmallQuadsT * mm::kQuadBytes + 16;
+// The mapped path.  Small batches (the reference's own call pattern is one chunk per call,
+// client.rs:259-267) skip every cudaMemcpy: the kernels read the chunks from, and write vertices and
+// range records to, mapped pinned host memory.  One memcpy in, two launches, one stream synchronise.
+// The mapped block grows on demand (arenas that turn out too small: grow and run again, like the device
+// arenas) up to kMappedMaxBytes; beyond that, or above c->mapped_max_chunks chunks, *done = false and the
+// caller takes the copy path.
+constexpr size_t kMappedMaxBytes = (size_t)1 << 30;
+struct MappedLayout {
+	size_t chunks, offs, ranges_i, ranges_t, out_i, out_t, total;
+	MappedLayout(uint32_t nc, uint64_t qi, uint64_t qt) {
+		const auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+		chunks = 0;
+		offs = up(chunks + (size_t)nc * 4096);
+		ranges_i = up(offs + (size_t)nc * 24);
+		ranges_t = up(ranges_i + (size_t)nc * 16);
+		out_i = up(ranges_t + (size_t)nc * 16);
+		out_t = up(out_i + qi * mm::kQuadBytes + 16);
+		total = out_t + qt * mm::kQuadBytes + 16;
+	}
 };
 static int small_batch_host(mm_ctx *c, const uint8_t *chunks, const int64_t *offs, uint32_t n, mm_host_mesh *out, bool *done) {
 	*done = false;
 	if (!c->have_table) return fail(c, MM_ERR_NO_TABLE, "mm_set_block_table has not been called");
-	const SmallLayout L;
-	if (!c->h_small) {
-		MM_CUDA(c, cudaStreamSynchronize(c->stream));
-		MM_CUDA(c, cudaHostAlloc(&c->h_small, L.total, cudaHostAllocMapped));
-		MM_CUDA(c, cudaHostGetDevicePointer((void **)&c->d_small, c->h_small, 0));
-	}
-	memcpy(c->h_small + L.chunks, chunks, (size_t)n * 4096);
-	memcpy(c->h_small + L.offs, offs, (size_t)n * 24);
-	Targets tg{c->d_small + L.out_i, c->d_small + L.out_t, kSmallQuadsI, kSmallQuadsT,
-	           (mm::Range *)(c->d_small + L.ranges_i), (mm::Range *)(c->d_small + L.ranges_t)};
-	c->pending = c->finished = false;  // the device arenas hold no batch of this call
-	c->last_launches = 0;
 	int rc;
-	if ((rc = launch(c, c->d_small + L.chunks, (const long long *)(c->d_small + L.offs), n, false, tg))) return rc;
-	MM_CUDA(c, cudaStreamSynchronize(c->stream));
-	const uint64_t ti = c->h_totals[0], tt = c->h_totals[1];
-	if (ti > kSmallQuadsI || tt > kSmallQuadsT) return MM_OK;  // nothing was written: ordinary path
-	out->intransparent = (const mm_vertex *)(c->h_small + L.out_i);
-	out->transparent = (const mm_vertex *)(c->h_small + L.out_t);
-	out->ranges_i = (const mm_range *)(c->h_small + L.ranges_i);
-	out->ranges_t = (const mm_range *)(c->h_small + L.ranges_t);
-	out->n_intransparent = ti * 6;
-	out->n_transparent = tt * 6;
-	out->n_chunks = n;
-	out->reserved = 0;
-	*done = true;
-	return MM_OK;
+	bool regrow = false;
+	for (int attempt = 0;; attempt++) {
+		if (!c->h_small || n > c->mapped_chunks || regrow) {  // first use, more chunks than ever before, or bigger arenas
+			const uint32_t nc = std::max<uint32_t>(std::max<uint32_t>(n, 32u), c->mapped_chunks);
+			const uint64_t qi = std::max<uint64_t>(c->mapped_qi, 49152), qt = std::max<uint64_t>(c->mapped_qt, 16384);  // 10.1 + 3.4 MiB
+			const MappedLayout L(nc, qi, qt);
+			if (L.total > kMappedMaxBytes) return MM_OK;
+			MM_CUDA(c, cudaStreamSynchronize(c->stream));
+			if (c->h_small) cudaFreeHost(c->h_small);
+			c->h_small = c->d_small = nullptr;
+			MM_CUDA(c, cudaHostAlloc(&c->h_small, L.total, cudaHostAllocMapped));
+			MM_CUDA(c, cudaHostGetDevicePointer((void **)&c->d_small, c->h_small, 0));
+			c->mapped_chunks = nc; c->mapped_qi = qi; c->mapped_qt = qt;
+			regrow = false;
+		}
+		const MappedLayout L(c->mapped_chunks, c->mapped_qi, c->mapped_qt);
+		// inputs in page-locked memory (mm_host_alloc) are read in place; pageable ones are copied into the block
+		const unsigned char *d_chunks = nullptr;
+		const long long *d_offs = nullptr;
+		if (is_pinned_ptr(chunks) && is_pinned_ptr(offs) &&
+		    cudaHostGetDevicePointer((void **)&d_chunks, (void *)chunks, 0) == cudaSuccess &&
+		    cudaHostGetDevicePointer((void **)&d_offs, (void *)offs, 0) == cudaSuccess) {
+		} else {
+			cudaGetLastError();
+			memcpy(c->h_small + L.chunks, chunks, (size_t)n * 4096);
+			memcpy(c->h_small + L.offs, offs, (size_t)n * 24);
+			d_chunks = c->d_small + L.chunks;
+			d_offs = (const long long *)(c->d_small + L.offs);
+		}
+		Targets tg{c->d_small + L.out_i, c->d_small + L.out_t, c->mapped_qi, c->mapped_qt,
+		           (mm::Range *)(c->d_small + L.ranges_i), (mm::Range *)(c->d_small + L.ranges_t)};
+		c->pending = c->finished = false;  // the device arenas hold no batch of this call
+		c->last_launches = 0;
+		if ((rc = launch(c, d_chunks, d_offs, n, false, tg))) return rc;
+		MM_CUDA(c, cudaStreamSynchronize(c->stream));
+		const uint64_t ti = c->h_totals[0], tt = c->h_totals[1];
+		if (ti > c->mapped_qi || tt > c->mapped_qt) {  // nothing was written: grow the mapped arenas and run again
+			if (attempt >= 1) return MM_OK;
+			const MappedLayout G(c->mapped_chunks, std::max(c->mapped_qi, ti + ti / 8), std::max(c->mapped_qt, tt + tt / 8));
+			if (G.total > kMappedMaxBytes) return MM_OK;
+			c->mapped_qi = std::max(c->mapped_qi, ti + ti / 8);
+			c->mapped_qt = std::max(c->mapped_qt, tt + tt / 8);
+			regrow = true;
+			continue;
+		}
+		out->intransparent = (const mm_vertex *)(c->h_small + L.out_i);
+		out->transparent = (const mm_vertex *)(c->h_small + L.out_t);
+		out->ranges_i = (const mm_range *)(c->h_small + L.ranges_i);
+		out->ranges_t = (const mm_range *)(c->h_small + L.ranges_t);
+		out->n_intransparent = ti * 6;
+		out->n_transparent = tt * 6;
+		out->n_chunks = n;
+		out->reserved = 0;
+		*done = true;
+		return MM_OK;
+	}
 }
 
 int mm_mesh_batch_host(mm_ctx *c, const uint8_t *chunks, const int64_t *offs, uint32_t n, mm_host_mesh *out) {
 	if (!c || !out || (n && (!chunks || !offs))) return MM_ERR_INVALID;
 	if (use_device(c)) return MM_ERR_CUDA;
 	int rc;
-	if (n && n <= kSmallChunks && !c->no_small) {
+	if (n && n <= c->mapped_max_chunks && !c->no_small) {
 		bool done = false;
 		if ((rc = small_batch_host(c, chunks, offs, n, out, &done))) return rc;
 		if (done) return MM_OK;

@@ -55,6 +55,8 @@ struct mm_ctx {
 	// small-batch path: one mapped pinned block holding inputs, range records and both vertex streams
 	unsigned char *h_small = nullptr, *d_small = nullptr;
 	bool no_small = false;
+	uint32_t mapped_max_chunks = 256, mapped_chunks = 0;  // batches up to this size take the mapped path; capacity of the block
+	uint64_t mapped_qi = 0, mapped_qt = 0;               // capacities of the mapped arenas (quads)
 
 	// host results (pinned)
 	unsigned char *h_out = nullptr;
