@@ -12,7 +12,7 @@
 //   * six run-merging face passes (lib.rs:316-410) -> `intransparent`
 //   * crossed-plant pass (lib.rs:412-440)          -> `transparent`
 // re-formulated as two kernels.
-// ANALYSE (one warp per chunk):
+// ANALYSE (one 128-thread CTA per chunk; "lane" below = the thread's job index in a phase):
 //   A. lane <-> column (x, y): 16 block ids along z (one 16-byte load) -> 16-bit "blocky"
 //      mask over z, plus SWAR id-equality masks against the (x, y-1) and (x-1, y) columns
 //   B. visibility and run-start masks of all six passes as bit operations on z-masks

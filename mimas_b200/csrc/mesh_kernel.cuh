@@ -108,7 +108,6 @@ __device__ __forceinline__ void mbar_wait(unsigned long long *mbar, uint32_t par
 		             : "memory");
 	} while (!done);
 }
-__device__ __forceinline__ uint32_t warp_sum(uint32_t v) { return __reduce_add_sync(0xffffffffu, v); }
 __device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, int lane) {
 #pragma unroll
 	for (int d = 1; d < 32; d <<= 1) {

@@ -1,7 +1,7 @@
 // mm_api.cu -- C ABI of libmimas_meshgen_cuda.so (see include/mimas_meshgen_cuda.h).
 //
 // Host side of the B200 mesher: context, device block table, arenas for the packed
-// vertex streams, launch of the persistent mesher kernel, grow-and-rerun when a batch
+// vertex streams, launch of the analyse + expand kernel pairs, grow-and-rerun when a batch
 // does not fit, host<->device staging for the `chunk in, Vec<Vertex> out` crate API.
 // There is no CPU implementation of the mesher in this library.
 #include <cuda_runtime.h>

@@ -1,7 +1,7 @@
 // TEST INFRASTRUCTURE -- host emulation of the mesher kernel's control flow.
 //
 // Compiles mimas_b200/csrc/mesh_core.cuh (the per-lane phase functions the CUDA kernel
-// is built from) with g++ and runs the 32 logical lanes of one warp in a loop per phase,
+// is built from) with g++ and runs the threads of one analysing CTA / the lanes of one expanding warp in a loop per phase,
 // with the warp shuffles, the warp scans, the batch-wide prefix and the tile stores
 // replaced by their serial meaning.  Lets the bit-level logic be checked against the
 // oracle on a machine without a GPU.  Never linked into libmimas_meshgen_cuda.so.
@@ -51,7 +51,7 @@ extern "C" int emul_mesh_batch(const uint8_t *chunks, const int64_t *offs, uint3
 	uint8_t flags[256];
 	build_flags(tab, flags);
 	for (int lane = 0; lane < kLanes; lane++) init_warp_smem(s, lane);
-	// ---- analyse kernel: one warp per chunk -> counts + descriptors ----------------------
+	// ---- analyse kernel: one CTA per chunk -> counts + descriptors ----------------------
 	std::vector<uint32_t> desc_i((size_t)n * kDescStrideI, 0xDEADBEEFu), desc_t((size_t)n * kDescStrideT, 0xDEADBEEFu);
 	std::vector<uint32_t> cnt_i(n), cnt_t(n);
 	for (uint32_t c = 0; c < n; c++) {

@@ -1,7 +1,7 @@
 """CPU check of the kernel's per-thread phase functions (mimas_b200/csrc/mesh_core.cuh), compiled
 with g++ by tests/emul/ and run as a serial emulation of one CTA, against the oracle.  This pins the
 bit-level logic the CUDA kernel is built from without needing a GPU; the GPU tests then cover the
-real kernel (scan, look-back, bulk stores)."""
+real kernels (tickets, barriers, the shared-memory prefix of the expand kernel, bulk loads and stores)."""
 import ctypes as C
 import os
 import subprocess

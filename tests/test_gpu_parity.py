@@ -118,7 +118,7 @@ def test_shared_textures_merge_across_block_ids(ocache):
 
 
 def test_repeated_launches_with_changing_batch_sizes(mesher, ocache):
-    """Exercises arena growth + re-run and the double-buffered look-back status words."""
+    """Exercises arena growth + re-run and the alternating hand-over buffers across launches of changing size."""
     import mimas_b200
     with mimas_b200.Mesher(0, product_cache(G)) as m:
         for dims in [(2, 2, 1), (6, 6, 2), (1, 1, 1), (7, 5, 3), (3, 3, 3), (7, 5, 3), (2, 1, 1)]:
