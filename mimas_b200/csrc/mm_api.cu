@@ -141,7 +141,7 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, ui
 		a.ticket_base = c->ticket_base;
 		mm::u64 *tr = c->d_trace ? c->d_trace + 8 * (c->trace_next++ % c->trace_pairs) : nullptr;
 		a.trace = tr;
-		const uint32_t grid = std::min<uint32_t>(m, (uint32_t)(c->sm_count * c->ctas_per_sm));
+		const uint32_t grid = std::min<uint32_t>(m, (uint32_t)(c->sm_count * c->analyse_ctas_per_sm));
 		cudaLaunchAttribute attr[1];
 		attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
 		attr[0].val.programmaticStreamSerializationAllowed = c->use_pdl ? 1 : 0;
@@ -226,6 +226,8 @@ int mm_ctx_create(int device, mm_ctx **out) {
 		MM_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mm::analyse_kernel, mm::kThreads, 0));
 		if (occ < 1) return fail(c, MM_ERR_CUDA, "analyse kernel does not fit on an SM");
 		c->ctas_per_sm = occ;
+		c->analyse_ctas_per_sm = occ;
+		if (const char *e = getenv("MM_ANALYSE_GRID_PER_SM")) c->analyse_ctas_per_sm = std::max(1, std::min(occ, atoi(e)));
 		int occ2 = 0;
 		MM_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, mm::expand_kernel, mm::kExpandThreads, mm::kExpandSmemBytes));
 		if (occ2 < 1) return fail(c, MM_ERR_CUDA, "expand kernel does not fit on an SM");

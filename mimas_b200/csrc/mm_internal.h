@@ -12,6 +12,7 @@ struct mm_ctx {
 	int device = 0;
 	int sm_count = 0;
 	int ctas_per_sm = 0;
+	int analyse_ctas_per_sm = 0;  // CTAs per SM the analyse grid is sized for
 	cudaStream_t own_stream = nullptr;
 	cudaStream_t stream = nullptr;
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
