@@ -123,19 +123,28 @@ def push_block(pos, ids, siz: float, blocked_mask: int):
     return _take(p, n.value)
 
 
-def count_batch(chunks, offs, cache: Cache):
+def _halo_ptr(halo, n):
+    """halo: None (reference semantics) or [n, 6, 256] block ids (optional extension, see blocked() in the C file)."""
+    if halo is None:
+        return None, None
+    halo = np.ascontiguousarray(halo, dtype=np.uint8).reshape(n, 1536)
+    return halo, C.c_void_p(halo.ctypes.data)
+
+
+def count_batch(chunks, offs, cache: Cache, halo=None):
     lib = load()
     chunks = np.ascontiguousarray(chunks, dtype=np.uint8).reshape(-1, 4096)
     n = chunks.shape[0]
     offs = np.ascontiguousarray(offs, dtype=np.int64).reshape(n, 3)
     ci = np.zeros(n, dtype=np.uint32)
     ct = np.zeros(n, dtype=np.uint32)
-    lib.mo_count_batch(chunks.ctypes.data, offs.ctypes.data, n, C.byref(cache),
-                       ci.ctypes.data, ct.ctypes.data)
+    keep, hp = _halo_ptr(halo, n)
+    lib.mo_count_batch_halo(C.c_void_p(chunks.ctypes.data), C.c_void_p(offs.ctypes.data), C.c_uint64(n), C.byref(cache),
+                            C.c_void_p(ci.ctypes.data), C.c_void_p(ct.ctypes.data), hp)
     return ci, ct
 
 
-def mesh_batch(chunks, offs, cache: Cache, threads: int = 1, discard: bool = False):
+def mesh_batch(chunks, offs, cache: Cache, threads: int = 1, discard: bool = False, halo=None):
     """Packed batch result in chunk order: dict(intransparent, transparent, count_i, count_t,
     first_i, first_t, seconds).  discard=True builds every mesh but keeps nothing (the CPU
     baseline's timing mode)."""
@@ -144,11 +153,13 @@ def mesh_batch(chunks, offs, cache: Cache, threads: int = 1, discard: bool = Fal
     n = chunks.shape[0]
     offs = np.ascontiguousarray(offs, dtype=np.int64).reshape(n, 3)
     secs = C.c_double()
+    keep, hp = _halo_ptr(halo, n)
+    lib.mo_mesh_batch_halo.restype = C.c_uint64
     if discard:
-        verts = lib.mo_mesh_batch(chunks.ctypes.data, offs.ctypes.data, n, C.byref(cache),
-                                  None, None, None, None, threads, C.byref(secs))
+        verts = lib.mo_mesh_batch_halo(C.c_void_p(chunks.ctypes.data), C.c_void_p(offs.ctypes.data), C.c_uint64(n), C.byref(cache),
+                                       None, None, None, None, C.c_uint32(threads), C.byref(secs), hp)
         return dict(vertices=int(verts), seconds=secs.value)
-    ci, ct = count_batch(chunks, offs, cache)
+    ci, ct = count_batch(chunks, offs, cache, halo)
     fi = np.zeros(n, dtype=np.uint64)
     ft = np.zeros(n, dtype=np.uint64)
     if n:
@@ -156,9 +167,9 @@ def mesh_batch(chunks, offs, cache: Cache, threads: int = 1, discard: bool = Fal
         ft[1:] = np.cumsum(ct[:-1], dtype=np.uint64)
     vi = np.zeros(int(ci.sum(dtype=np.uint64)), dtype=VERTEX_DTYPE)
     vt = np.zeros(int(ct.sum(dtype=np.uint64)), dtype=VERTEX_DTYPE)
-    lib.mo_mesh_batch(chunks.ctypes.data, offs.ctypes.data, n, C.byref(cache),
-                      vi.ctypes.data, fi.ctypes.data, vt.ctypes.data, ft.ctypes.data,
-                      threads, C.byref(secs))
+    lib.mo_mesh_batch_halo(C.c_void_p(chunks.ctypes.data), C.c_void_p(offs.ctypes.data), C.c_uint64(n), C.byref(cache),
+                           C.c_void_p(vi.ctypes.data), C.c_void_p(fi.ctypes.data), C.c_void_p(vt.ctypes.data),
+                           C.c_void_p(ft.ctypes.data), C.c_uint32(threads), C.byref(secs), hp)
     return dict(intransparent=vi, transparent=vt, count_i=ci, count_t=ct,
                 first_i=fi, first_t=ft, seconds=secs.value)
 

@@ -156,22 +156,31 @@ static int get_bl_tex_ids(const mo_cache *c, uint8_t id, mo_bti *out) {
 	return 1;
 }
 
-/* mimas-meshgen/lib.rs:273-283 `blocked` */
-static int blocked(const uint8_t *chunk, const int64_t o[3], const int64_t pos[3],
+/* mimas-meshgen/lib.rs:273-283 `blocked`.
+ * `halo` == NULL is the reference: a neighbour outside the chunk never blocks (lib.rs:277-280).
+ * A non-NULL halo is the OPTIONAL extension of this repo (no reference counterpart):
+ * 6 slabs of 256 block ids, the layer of each face-neighbour chunk that touches this chunk, in the
+ * order x-, x+, y-, y+, z-, z+; x slabs indexed y*16+z, y slabs x*16+z, z slabs x*16+y.  A blocky
+ * cell there blocks the face exactly as a cell inside the chunk would; nothing else changes. */
+static int blocked(const uint8_t *chunk, const uint8_t *halo, const int64_t o[3], const int64_t pos[3],
 		const mo_cache *cache) {
 	int64_t p[3] = { pos[0] + o[0], pos[1] + o[1], pos[2] + o[2] };
-	for (int i = 0; i < 3; i++)
-		if (p[i] < 0 || p[i] >= CHUNKSIZE) return 0; /* outside => not blocked */
 	mo_bti t;
+	for (int i = 0; i < 3; i++)
+		if (p[i] < 0 || p[i] >= CHUNKSIZE) {
+			if (!halo) return 0; /* outside => not blocked */
+			const int64_t u = i == 0 ? p[1] : p[0], v = i == 2 ? p[1] : p[2];  /* the two in-range coordinates */
+			return get_bl_tex_ids(cache, halo[(2 * i + (p[i] < 0 ? 0 : 1)) * 256 + u * CHUNKSIZE + v], &t);
+		}
 	return get_bl_tex_ids(cache, get_blk(chunk, p), &t);
 }
 
 /* mimas-meshgen/lib.rs:284-293 `get_tex_ind` */
-static int get_tex_ind(const uint8_t *chunk, const int64_t pos[3], const int64_t offsets[3],
+static int get_tex_ind(const uint8_t *chunk, const uint8_t *halo, const int64_t pos[3], const int64_t offsets[3],
 		const mo_cache *cache, mo_bti *out) {
 	mo_bti t;
 	int some = get_bl_tex_ids(cache, get_blk(chunk, pos), &t);
-	if (some && blocked(chunk, offsets, pos, cache)) return 0;
+	if (some && blocked(chunk, halo, offsets, pos, cache)) return 0;
 	if (some) *out = t;
 	return some;
 }
@@ -245,7 +254,7 @@ static void walker_next(walker *w, float v, int has_item, uint16_t item,
 /* mimas-meshgen/lib.rs:294-313 `walk_for_all_blocks` + the `g` closures
  * (lib.rs:322-328 etc.: pos = offs + rel_pos; walker.next(pos.<inner> as f32, ...)). */
 static void walk_for_all_blocks(const pass_desc *p, const int64_t offs[3],
-		const uint8_t *chunk, const mo_cache *cache, mo_vec *r) {
+		const uint8_t *chunk, const uint8_t *halo, const mo_cache *cache, mo_vec *r) {
 	for (int64_t c1 = 0; c1 < CHUNKSIZE; c1++) {
 		for (int64_t c2 = 0; c2 < CHUNKSIZE; c2++) {
 			walker w = { 0, 0.0f, 0 };
@@ -258,7 +267,7 @@ static void walk_for_all_blocks(const pass_desc *p, const int64_t offs[3],
 				uint16_t tex_ind = 0;
 				if (cinner < CHUNKSIZE) {
 					mo_bti t;
-					has = get_tex_ind(chunk, rel, p->offsets, cache, &t);
+					has = get_tex_ind(chunk, halo, rel, p->offsets, cache, &t);
 					if (has) tex_ind = p->face == 0 ? t.id_sides : p->face == 1 ? t.id_top : t.id_bottom;
 				} /* else: the sentinel g(&mut walker, None, f(c1,c2,CHUNKSIZE)), lib.rs:309-310 */
 				int64_t pos[3] = { offs[0] + rel[0], offs[1] + rel[1], offs[2] + rel[2] };
@@ -270,10 +279,10 @@ static void walk_for_all_blocks(const pass_desc *p, const int64_t offs[3],
 }
 
 /* mimas-meshgen/lib.rs:231-446 `mesh_for_chunk` */
-static void mesh_for_chunk(const int64_t offs[3], const uint8_t *chunk, const mo_cache *cache,
+static void mesh_for_chunk_h(const int64_t offs[3], const uint8_t *chunk, const uint8_t *halo, const mo_cache *cache,
 		mo_vec *r, mo_vec *rt) {
 	for (int i = 0; i < 6; i++)
-		walk_for_all_blocks(&PASSES[i], offs, chunk, cache, r);
+		walk_for_all_blocks(&PASSES[i], offs, chunk, halo, cache, r);
 
 	/* Crossed nodes, lib.rs:414-440 */
 	const float siz = 1.0f;
@@ -317,6 +326,11 @@ static void push_block(mo_vec *r, float x, float y, float z, mo_bti ids, float s
 	if (!(blocked_mask & 32)) rpush_face_rev(r, x + siz, y, z, 0.0f, siz, 0.0f, siz, ids.id_sides);
 }
 
+static void mesh_for_chunk(const int64_t offs[3], const uint8_t *chunk, const mo_cache *cache,
+		mo_vec *r, mo_vec *rt) {
+	mesh_for_chunk_h(offs, chunk, 0, cache, r, rt);
+}
+
 /* ------------------------------------------------------------------------------------
  * C entry points (ctypes-facing).  All "mo_" = meshgen oracle.
  * ---------------------------------------------------------------------------------- */
@@ -341,11 +355,17 @@ void mo_push_block(float x, float y, float z, const mo_bti *ids, float siz,
 }
 
 /* Count pass over a batch: per chunk vertex counts only (cheap way to size buffers). */
+void mo_count_batch_halo(const uint8_t *chunks, const int64_t *offs, uint64_t n, const mo_cache *cache,
+		uint32_t *n_intransparent, uint32_t *n_transparent, const uint8_t *halo);
 void mo_count_batch(const uint8_t *chunks, const int64_t *offs, uint64_t n, const mo_cache *cache,
 		uint32_t *n_intransparent, uint32_t *n_transparent) {
+	mo_count_batch_halo(chunks, offs, n, cache, n_intransparent, n_transparent, 0);
+}
+void mo_count_batch_halo(const uint8_t *chunks, const int64_t *offs, uint64_t n, const mo_cache *cache,
+		uint32_t *n_intransparent, uint32_t *n_transparent, const uint8_t *halo) {
 	for (uint64_t i = 0; i < n; i++) {
 		mo_vec r = { 0, 0, 0 }, rt = { 0, 0, 0 };
-		mesh_for_chunk(offs + 3 * i, chunks + 4096 * i, cache, &r, &rt);
+		mesh_for_chunk_h(offs + 3 * i, chunks + 4096 * i, halo ? halo + 1536 * i : 0, cache, &r, &rt);
 		n_intransparent[i] = (uint32_t)r.len; n_transparent[i] = (uint32_t)rt.len;
 		free(r.data); free(rt.data);
 	}
@@ -356,7 +376,7 @@ void mo_count_batch(const uint8_t *chunks, const int64_t *offs, uint64_t n, cons
  * chunks' vertices back to back in chunk order -- the same packing the CUDA library
  * produces, so a whole batch can be compared with one memcmp. */
 typedef struct {
-	const uint8_t *chunks; const int64_t *offs; const mo_cache *cache;
+	const uint8_t *chunks; const int64_t *offs; const mo_cache *cache; const uint8_t *halo;
 	uint64_t begin, end;
 	mo_vertex *intr; mo_vertex *trans;
 	const uint64_t *first_intr; const uint64_t *first_trans;
@@ -369,7 +389,7 @@ static void *batch_worker(void *arg) {
 	for (uint64_t i = j->begin; i < j->end; i++) {
 		/* fresh, empty vectors per chunk, as in the reference (lib.rs:233,412) */
 		mo_vec r = { 0, 0, 0 }, rt = { 0, 0, 0 };
-		mesh_for_chunk(j->offs + 3 * i, j->chunks + 4096 * i, j->cache, &r, &rt);
+		mesh_for_chunk_h(j->offs + 3 * i, j->chunks + 4096 * i, j->halo ? j->halo + 1536 * i : 0, j->cache, &r, &rt);
 		if (j->intr && r.len) memcpy(j->intr + j->first_intr[i], r.data, r.len * sizeof(mo_vertex));
 		if (j->trans && rt.len) memcpy(j->trans + j->first_trans[i], rt.data, rt.len * sizeof(mo_vertex));
 		verts += r.len + rt.len;
@@ -384,10 +404,21 @@ static void *batch_worker(void *arg) {
  * baseline's timing mode -- the meshes are still fully built in per-chunk vectors).
  * Returns total vertices produced; *seconds receives the wall time of the parallel
  * region (CLOCK_MONOTONIC). */
+uint64_t mo_mesh_batch_halo(const uint8_t *chunks, const int64_t *offs, uint64_t n, const mo_cache *cache,
+		mo_vertex *intr, const uint64_t *first_intr,
+		mo_vertex *trans, const uint64_t *first_trans,
+		uint32_t threads, double *seconds, const uint8_t *halo);
 uint64_t mo_mesh_batch(const uint8_t *chunks, const int64_t *offs, uint64_t n, const mo_cache *cache,
 		mo_vertex *intr, const uint64_t *first_intr,
 		mo_vertex *trans, const uint64_t *first_trans,
 		uint32_t threads, double *seconds) {
+	return mo_mesh_batch_halo(chunks, offs, n, cache, intr, first_intr, trans, first_trans, threads, seconds, 0);
+}
+/* the same with the optional halo (n * 1536 bytes) */
+uint64_t mo_mesh_batch_halo(const uint8_t *chunks, const int64_t *offs, uint64_t n, const mo_cache *cache,
+		mo_vertex *intr, const uint64_t *first_intr,
+		mo_vertex *trans, const uint64_t *first_trans,
+		uint32_t threads, double *seconds, const uint8_t *halo) {
 	if (threads < 1) threads = 1;
 	if (threads > 1024) threads = 1024;
 	if ((uint64_t)threads > n && n > 0) threads = (uint32_t)n;
@@ -397,7 +428,7 @@ uint64_t mo_mesh_batch(const uint8_t *chunks, const int64_t *offs, uint64_t n, c
 	clock_gettime(CLOCK_MONOTONIC, &t0);
 	for (uint32_t t = 0; t < threads; t++) {
 		batch_job *j = &jobs[t];
-		j->chunks = chunks; j->offs = offs; j->cache = cache;
+		j->chunks = chunks; j->offs = offs; j->cache = cache; j->halo = halo;
 		j->begin = n * t / threads; j->end = n * (t + 1) / threads;
 		j->intr = intr; j->trans = trans; j->first_intr = first_intr; j->first_trans = first_trans;
 		if (threads == 1) batch_worker(j);

@@ -91,3 +91,27 @@ def assert_batch_equal(got, want):
     assert d is None, "intransparent: " + d
     d = first_diff(got.transparent.tobytes(), want["transparent"].tobytes())
     assert d is None, "transparent: " + d
+
+
+# ---- halo extension (no reference counterpart; see oracle/meshgen_oracle.c blocked()) ------------
+
+def region_to_chunks_and_halos(vol, outside=0):
+    """vol: uint8 [16*X, 16*Y, 16*Z] block ids.  Returns (chunks [n,4096], offs [n,3], halo [n,6,256]) with
+    chunk order cx-major, each halo slab the touching layer of the face neighbour (order x-,x+,y-,y+,z-,z+;
+    x slabs [y,z], y slabs [x,z], z slabs [x,y]); `outside` fills what lies beyond the region."""
+    X, Y, Z = (s // 16 for s in vol.shape)
+    pad = np.full(tuple(s + 2 for s in vol.shape), outside, dtype=np.uint8)
+    pad[1:-1, 1:-1, 1:-1] = vol
+    chunks, offs, halos = [], [], []
+    for cx in range(X):
+        for cy in range(Y):
+            for cz in range(Z):
+                x0, y0, z0 = 16 * cx + 1, 16 * cy + 1, 16 * cz + 1
+                chunks.append(pad[x0:x0 + 16, y0:y0 + 16, z0:z0 + 16].reshape(4096))
+                offs.append((16 * cx, 16 * cy, 16 * cz))
+                halos.append(np.stack([
+                    pad[x0 - 1, y0:y0 + 16, z0:z0 + 16], pad[x0 + 16, y0:y0 + 16, z0:z0 + 16],
+                    pad[x0:x0 + 16, y0 - 1, z0:z0 + 16], pad[x0:x0 + 16, y0 + 16, z0:z0 + 16],
+                    pad[x0:x0 + 16, y0:y0 + 16, z0 - 1], pad[x0:x0 + 16, y0:y0 + 16, z0 + 16]]).reshape(6, 256))
+    return (np.ascontiguousarray(np.stack(chunks)), np.array(offs, dtype=np.int64),
+            np.ascontiguousarray(np.stack(halos)))
