@@ -26,6 +26,7 @@ extern "C" {
 #define MM_ABI_VERSION 1u
 #define MM_CHUNKSIZE 16u           /* mimas-common/map.rs:11  CHUNKSIZE            */
 #define MM_CHUNK_BYTES 4096u       /* mimas-common/map.rs:56-61 [MapBlock; 16^3]   */
+#define MM_HALO_BYTES 1536u        /* optional halo of one chunk: 6 slabs of 256 block ids (extension) */
 #define MM_TABLE_ENTRIES 256u      /* MapBlock is a u8 id, mimas-common/map.rs:14  */
 
 typedef enum mm_status {
@@ -36,7 +37,7 @@ typedef enum mm_status {
 	MM_ERR_OOM = 4,         /* device or pinned host allocation failed               */
 	MM_ERR_NO_TABLE = 5,    /* mm_set_block_table has not been called                */
 	MM_ERR_NO_BATCH = 6,    /* no finished batch to read back                        */
-	MM_ERR_UNSUPPORTED = 7  /* e.g. a non-NULL halo (extension, not in the reference) */
+	MM_ERR_UNSUPPORTED = 7
 } mm_status;
 
 /* mimas-meshgen/lib.rs:18-24 `Vertex`, fixed as #[repr(C)] in declared order:
@@ -126,8 +127,15 @@ int mm_reserve(mm_ctx *ctx, uint32_t max_chunks, uint64_t intransparent_vertices
  *            host or device memory (detected)
  *   offs   : n * 3 int64 chunk origins in blocks (`offs :Vector3<isize>`, lib.rs:231)
  *            host or device memory (detected)
- *   halo   : must be NULL.  The reference treats out-of-chunk neighbours as not
- *            blocking (lib.rs:277-280); a non-NULL halo returns MM_ERR_UNSUPPORTED.
+ *   halo   : NULL = the reference's semantics: out-of-chunk neighbours never block
+ *            (lib.rs:277-280).  Non-NULL = an EXTENSION with no counterpart in the reference
+ *            (parity: oracle/meshgen_oracle.c `blocked` with halo slabs): n * MM_HALO_BYTES
+ *            block ids, per chunk the six layers of the face-neighbour chunks that touch it, in
+ *            the order x-, x+, y-, y+, z-, z+, 256 ids each; the x slabs indexed y*16 + z, the
+ *            y slabs x*16 + z, the z slabs x*16 + y.  A face against a blocky cell of a slab is
+ *            culled like one against a blocky cell of the chunk; runs, textures and the crossed
+ *            pass are untouched.  Host or device memory (detected); device memory must be
+ *            16-byte aligned.  mm_gather_halos builds the slabs for a resident region.
  * Synchronous: returns after the kernel finished and totals are known. */
 int mm_mesh_batch(mm_ctx *ctx, const uint8_t *chunks, const int64_t *offs,
                   const uint8_t *halo, uint32_t n, mm_batch_out *out);
@@ -137,6 +145,15 @@ int mm_mesh_batch(mm_ctx *ctx, const uint8_t *chunks, const int64_t *offs,
  * arenas were too small, and reports totals.  Several _async calls may be queued
  * back to back; only the last one's result is retrievable. */
 int mm_mesh_batch_async(mm_ctx *ctx, const uint8_t *d_chunks, const int64_t *d_offs, uint32_t n);
+/* The same with halo slabs (device memory, 16-byte aligned; NULL = mm_mesh_batch_async). */
+int mm_mesh_batch_halo_async(mm_ctx *ctx, const uint8_t *d_chunks, const int64_t *d_offs, const uint8_t *d_halo,
+                             uint32_t n);
+/* Halo slabs of a device-resident box of nx * ny * nz chunks laid out like mm_gen_terrain_* lays
+ * them out (chunk i at (i % nx, (i / nx) % ny, i / (nx*ny))): every chunk's six slabs from its
+ * neighbours in the box, `outside_id` beyond the box.  d_halo: nx*ny*nz * MM_HALO_BYTES,
+ * 16-byte aligned.  Stream-ordered. */
+int mm_gather_halos(mm_ctx *ctx, const uint8_t *d_chunks, uint32_t nx, uint32_t ny, uint32_t nz, uint8_t outside_id,
+                    uint8_t *d_halo);
 int mm_batch_finish(mm_ctx *ctx, mm_batch_out *out);
 
 /* Host-`Vec` path: copy the last finished batch to caller memory sized from

@@ -21,7 +21,8 @@ SYMBOLS = (
     "mm_batch_finish", "mm_copy_out", "mm_mesh_batch_host", "mm_mesh_for_chunk", "mm_push_blocks",
     "mm_gen_terrain_host", "mm_gen_terrain_device", "mm_dev_alloc", "mm_dev_free", "mm_dev_upload",
     "mm_dev_download", "mm_ctx_sync", "mm_device_info", "mm_host_alloc", "mm_host_free", "mm_launch_count",
-    "mm_debug_trace", "mm_vertex_stage", "mm_cull_chunks", "mm_draw_batch",
+    "mm_debug_trace", "mm_vertex_stage", "mm_cull_chunks", "mm_draw_batch", "mm_mesh_batch_halo_async",
+    "mm_gather_halos",
 )
 
 
@@ -54,6 +55,8 @@ def lib() -> C.CDLL:
     l.mm_reserve.argtypes = [vp, u32, u64, u64]
     l.mm_mesh_batch.argtypes = [vp, vp, vp, vp, u32, vp]
     l.mm_mesh_batch_async.argtypes = [vp, vp, vp, u32]
+    l.mm_mesh_batch_halo_async.argtypes = [vp, vp, vp, vp, u32]
+    l.mm_gather_halos.argtypes = [vp, vp, u32, u32, u32, C.c_uint8, vp]
     l.mm_batch_finish.argtypes = [vp, vp]
     l.mm_copy_out.argtypes = [vp, vp, vp, vp, vp]
     l.mm_mesh_batch_host.argtypes = [vp, vp, vp, u32, vp]

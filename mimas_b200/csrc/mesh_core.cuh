@@ -96,6 +96,11 @@ struct alignas(128) ChunkSmem {
 	alignas(16) uint16_t Bx[256];              // blocky mask over x for row (y, z): [y*16 + z]
 	alignas(16) uint16_t Bzp[kBzStride * kBzStride + 4];  // blocky mask over z per column, zero border
 	alignas(16) uint32_t gcnt[kGroups];        // per group: quads | non-empty words << 16; then the exclusive prefix of that
+	// halo mode only (an extension, see halo_row): blocky masks of the touching layers of the z-, z+ neighbour
+	// chunks over y per x (Hz[x], Hz[16 + x]) and of the x-, x+, y-, y+ neighbours over the merge axis per z
+	// (Hm[0..15] x- over y, Hm[16..31] x+ over y, Hm[32..47] y- over x, Hm[48..63] y+ over x)
+	alignas(16) uint16_t Hz[32];
+	alignas(16) uint16_t Hm[64];
 	uint32_t nq, nwords, npl;                  // totals of the chunk
 	uint32_t amb[2];                           // OR of the flag bytes of the chunk's cells (double buffered)
 	uint32_t ticket[2];                        // chunk index of this / the next round (double buffered)
@@ -302,21 +307,35 @@ MM_HD uint32_t fix_equal(const TabEntry *tab, const uint8_t *chunk, uint32_t d, 
 }
 
 // `amb` = OR of the flag bytes of every cell of the chunk.
+// HALO: the border of Bzp and Hz hold the neighbour chunks' touching layers (halo_row); they occlude
+// faces like cells of the chunk do, but a run never continues from them (a row starts at 0, lib.rs:294-313).
+template <bool HALO>
 MM_HD void col_starts(ChunkSmem &s, const TabEntry *tab, const uint8_t *chunk, int x, int y, uint32_t amb) {
 	const uint16_t *B = smem_Bzp(s) + (x + 1) * kBzStride + (y + 1);
 	const uint32_t b = B[0];
 	const uint32_t bym = B[-1], byp = B[1], bxm = B[-kBzStride], bxp = B[kBzStride];
 	const uint32_t bmm = B[-kBzStride - 1], bpm = B[kBzStride - 1], bmp = B[-kBzStride + 1];
 	const int col = x * 16 + y;
+	// previous cell along the merge axis; cells below z = 0 / above z = 15 of this and of the previous column
+	uint32_t py = bym, px = bxm, zlo = 0, zhi = 0, pzlo = 0, pzhi = 0;
+	if (HALO) {
+		const uint32_t hm = s.Hz[x], hp = s.Hz[16 + x];
+		py = y > 0 ? bym : 0u;
+		px = x > 0 ? bxm : 0u;
+		zlo = (hm >> y) & 1u;
+		zhi = ((hp >> y) & 1u) << 15;
+		pzlo = ((hm << 1) >> y) & 1u;
+		pzhi = (((hp << 1) >> y) & 1u) << 15;
+	}
 	// own faces
-	const uint32_t V1 = b & ~(b << 1), V4 = b & ~(b >> 1);   // [0,0,-1] lib.rs:317, [0,0,1] lib.rs:365
+	const uint32_t V1 = b & ~((b << 1) | zlo), V4 = b & ~((b >> 1) | zhi);   // [0,0,-1] lib.rs:317, [0,0,1] lib.rs:365
 	const uint32_t V3 = b & ~bxm, V6 = b & ~bxp;             // [-1,0,0] lib.rs:349, [1,0,0] lib.rs:397
 	const uint32_t V2 = b & ~bym, V5 = b & ~byp;             // [0,-1,0] lib.rs:333, [0,1,0] lib.rs:381
 	// the same faces of the previous cell along the merge axis: (x, y-1) for the y-inner
 	// passes 1,3,4,6 and (x-1, y) for the x-inner passes 2,5 (zero border: no previous cell)
-	const uint32_t Q1 = V1 & bym & ~(bym << 1), Q4 = V4 & bym & ~(bym >> 1);
-	const uint32_t Q3 = V3 & bym & ~bmm, Q6 = V6 & bym & ~bpm;
-	const uint32_t Q2 = V2 & bxm & ~bmm, Q5 = V5 & bxm & ~bmp;
+	const uint32_t Q1 = V1 & py & ~((py << 1) | pzlo), Q4 = V4 & py & ~((py >> 1) | pzhi);
+	const uint32_t Q3 = V3 & py & ~bmm, Q6 = V6 & py & ~bpm;
+	const uint32_t Q2 = V2 & px & ~bmm, Q5 = V5 & px & ~bmp;
 	// Runs merge on equal textures; equal block ids are equal textures, and the id-equality masks
 	// against the previous column are only worked out where two visible faces meet at all.
 	const uint32_t qy = Q1 | Q3 | Q4 | Q6, qx = Q2 | Q5;
@@ -401,6 +420,48 @@ MM_HD void transpose_blocky(ChunkSmem &s, int job) {
 	for (int k = 0; k < 8; k++) p[k] = w[k];
 }
 
+// ---- halo mode (extension; the reference has no halo: lib.rs:277-280) -----------------------------
+// Per chunk 6 slabs of 256 block ids, the layers of the face-neighbour chunks that touch this chunk, in the
+// order x-, x+, y-, y+, z-, z+; x slabs indexed y*16 + z, y slabs x*16 + z, z slabs x*16 + y (the same
+// layout as oracle/meshgen_oracle.c blocked()).  Job t = 0..95 takes the 16 ids of row t & 15 of slab
+// t >> 4 (`c`) to a blocky mask: the x / y slabs give masks over z for the border columns of Bzp, the
+// z slabs masks over y per x.
+MM_HD void halo_row(ChunkSmem &s, const uint8_t *flags, const Col &c, int t) {
+	uint32_t orf;
+	const uint16_t m = (uint16_t)col_flags(flags, c, orf);
+	const int slab = t >> 4, r = t & 15;
+	uint16_t *B = smem_Bzp(s);
+	if (slab == 0) B[r + 1] = m;
+	else if (slab == 1) B[(kBzStride - 1) * kBzStride + r + 1] = m;
+	else if (slab == 2) B[(r + 1) * kBzStride] = m;
+	else if (slab == 3) B[(r + 1) * kBzStride + kBzStride - 1] = m;
+	else s.Hz[(slab - 4) * 16 + r] = m;
+}
+// Job 0..3: the border masks of the x-, x+, y-, y+ layer (over z per y resp. x) transposed to masks over
+// the merge axis per z, as phase D needs them.
+MM_HD void transpose_halo(ChunkSmem &s, int job) {
+	uint32_t w[8];
+	const uint16_t *B = smem_Bzp(s);
+#pragma unroll
+	for (int k = 0; k < 8; k++) {
+		uint32_t lo, hi;
+		if (job < 2) {
+			const int x = job == 0 ? 0 : kBzStride - 1;
+			lo = B[x * kBzStride + 2 * k + 1];
+			hi = B[x * kBzStride + 2 * k + 2];
+		} else {
+			const int y = job == 2 ? 0 : kBzStride - 1;
+			lo = B[(2 * k + 1) * kBzStride + y];
+			hi = B[(2 * k + 2) * kBzStride + y];
+		}
+		w[k] = lo | (hi << 16);
+	}
+	transpose16(w);
+	uint32_t *p = reinterpret_cast<uint32_t *>(s.Hm + job * 16);
+#pragma unroll
+	for (int k = 0; k < 8; k++) p[k] = w[k];
+}
+
 // Transposes the 16-entry block at S[m*16 ..] in place: from masks over z per column to masks
 // over the merge axis per row c2, i.e. word k of the block = rows 2k (low half) and 2k+1 (high
 // half) of group m = pass*16 + c1 in emission order.  Returns quads | non-empty words << 16.
@@ -447,6 +508,7 @@ MM_HD void list_group_words(ChunkSmem &s, int m, uint32_t pre) {
 // group m, widx = m*8 + k; `word` = that word, non-zero) in emission order (rows ascending,
 // runs ascending, lib.rs:294-313) to dst[0..popc(word)).  A run (lib.rs:244-271) ends where
 // the next one starts, where the face stops being visible, or at the end of the row.
+template <bool HALO>
 MM_HD void emit_word_descs(const ChunkSmem &s, uint32_t widx, uint32_t word, uint32_t *dst) {
 	const int m = (int)(widx >> 3), c2lo = (int)(widx & 7u) * 2;
 	const int p = m >> 4, c1 = m & 15;
@@ -456,10 +518,17 @@ MM_HD void emit_word_descs(const ChunkSmem &s, uint32_t widx, uint32_t word, uin
 	const uint16_t *Bm = (xin ? s.Bx : s.By) + c1 * 16 + c2lo;
 	const uint32_t b = *reinterpret_cast<const uint32_t *>(Bm);
 	uint32_t nb;
-	if (p == 0) nb = (b << 16) | (c2lo > 0 ? (uint32_t)Bm[-1] : 0u);                   // [0,0,-1]: row c2-1
-	else if (p == 3) nb = (b >> 16) | (c2lo < 14 ? (uint32_t)Bm[2] << 16 : 0u);        // [0,0,1]:  row c2+1
-	else if (p == 1 || p == 2) nb = c1 > 0 ? *reinterpret_cast<const uint32_t *>(Bm - 16) : 0u;   // [0,-1,0] / [-1,0,0]
-	else nb = c1 < 15 ? *reinterpret_cast<const uint32_t *>(Bm + 16) : 0u;             // [0,1,0] / [1,0,0]
+	// beyond the chunk: nothing (lib.rs:277-280), or the neighbour chunk's layer in halo mode
+	uint32_t out = 0;
+	if (HALO) {
+		if (p == 0) out = s.Hz[c1];
+		else if (p == 3) out = (uint32_t)s.Hz[16 + c1] << 16;
+		else out = *reinterpret_cast<const uint32_t *>(s.Hm + (p == 2 ? 0 : p == 5 ? 16 : p == 1 ? 32 : 48) + c2lo);
+	}
+	if (p == 0) nb = (b << 16) | (c2lo > 0 ? (uint32_t)Bm[-1] : out);                  // [0,0,-1]: row c2-1
+	else if (p == 3) nb = (b >> 16) | (c2lo < 14 ? (uint32_t)Bm[2] << 16 : out);       // [0,0,1]:  row c2+1
+	else if (p == 1 || p == 2) nb = c1 > 0 ? *reinterpret_cast<const uint32_t *>(Bm - 16) : out;  // [0,-1,0] / [-1,0,0]
+	else nb = c1 < 15 ? *reinterpret_cast<const uint32_t *>(Bm + 16) : out;            // [0,1,0] / [1,0,0]
 	const uint32_t T = (word | ~(b & ~nb) | 0x10000u) >> 1;  // run boundaries: start | not visible | end of the low row
 	const uint32_t base = ((uint32_t)m << 16) | ((uint32_t)c2lo << 12);
 	const int cell0 = (xin ? c1 * 16 : c1 * 256) + c2lo;   // + st*256 (x-inner) or st*16 (y-inner) + (c2 & 1)

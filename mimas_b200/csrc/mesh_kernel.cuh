@@ -52,6 +52,7 @@ constexpr size_t kExpandSmemBytes = 2048 + 2 * 4 * kExpandPrefixWords + 256 + kE
 
 struct AnalyseParams {
 	const unsigned char *chunks;  // n * 4096
+	const unsigned char *halo;    // halo mode: n * 1536 (see halo_row in mesh_core.cuh), 16-byte aligned; else unused
 	uint32_t n;                   // <= kMaxLaunchChunks
 	const TabEntry *table;        // 256 entries
 	const unsigned char *flags;   // 256 flag bytes (kFlagBlocky / kFlagCrossed)
@@ -165,6 +166,10 @@ __device__ __forceinline__ void store_tile(unsigned char *g, const unsigned char
 
 // ---- kernel 1: analysis ------------------------------------------------------------------
 // One CTA of kThreads threads per chunk in flight; CTAs are persistent and draw chunk tickets.
+// HALO = the optional mode in which the touching layers of the six neighbour chunks occlude faces (an
+// extension; false = the reference's semantics, lib.rs:277-280, and the instantiation every number in
+// DESIGN.md is measured on).
+template <bool HALO>
 __global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(const AnalyseParams p) {
 	__shared__ ChunkSmem s;
 	__shared__ __align__(16) unsigned char flags[256];
@@ -194,6 +199,11 @@ __global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(co
 			s.ticket[par ^ 1u] = (uint32_t)min(atomicAdd(p.ticket, 1ull) - p.ticket_base, (u64)0xffffffffu);
 			s.amb[par ^ 1u] = 0;
 		}
+		Col hrow;
+		if (HALO && tid < 96) {  // one 16-byte row of the halo slabs per thread, in flight beside the chunk
+			const uint4 v = __ldg(reinterpret_cast<const uint4 *>(p.halo + (size_t)c * 1536u) + tid);
+			hrow.w[0] = v.x; hrow.w[1] = v.y; hrow.w[2] = v.z; hrow.w[3] = v.w;
+		}
 		mbar_wait(&s.mbar, par);
 
 		// A. thread <-> columns col = tid, tid + 128 (col = x*16 + y): blocky mask over z per column
@@ -215,6 +225,7 @@ __global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(co
 			}
 			continue;
 		}
+		if (HALO && tid < 96) halo_row(s, flags, hrow, tid);
 #pragma unroll
 		for (int j = 0; j < 256 / kThreads; j++) {
 			const int col = kThreads * j + tid;
@@ -234,12 +245,13 @@ __global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(co
 #pragma unroll 1
 			for (int j = 0; j < 256 / kThreads; j++) {
 				const int col = kThreads * j + tid;
-				col_starts(s, tab, raw, col >> 4, col & 15, amb);
+				col_starts<HALO>(s, tab, raw, col >> 4, col & 15, amb);
 			}
 			__syncthreads();
 			// C. masks over the merge axes: 32 blocky jobs + 96 groups = one job per thread
 			if (tid < 32) transpose_blocky(s, tid);
 			else s.gcnt[tid - 32] = transpose_group(s, tid - 32);
+			if (HALO && tid >= 124) transpose_halo(s, tid - 124);  // Bzp's border is read-only here
 			__syncthreads();
 			if (warp == 0) {  // exclusive scan of quads (low half) and non-empty words (high half) over the groups
 				uint32_t run = 0;
@@ -264,7 +276,7 @@ __global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(co
 			for (uint32_t i = (uint32_t)tid; i < nwords; i += kThreads) {
 				const uint32_t e = smem_wl(s)[i];
 				const uint32_t widx = e & 1023u;
-				emit_word_descs(s, widx, reinterpret_cast<const uint32_t *>(s.S)[widx], di + (e >> 10));
+				emit_word_descs<HALO>(s, widx, reinterpret_cast<const uint32_t *>(s.S)[widx], di + (e >> 10));
 			}
 			if (tid == 0) p.cnt_i[c] = s.nq;
 		} else if (tid == 0) {

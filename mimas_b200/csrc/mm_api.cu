@@ -117,7 +117,8 @@ struct Targets {  // where a batch's vertices and range records go
 };
 Targets device_targets(const mm_ctx *c) { return Targets{c->d_out_i, c->d_out_t, c->cap_i, c->cap_t, c->d_ranges_i, c->d_ranges_t}; }
 
-int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, uint32_t n, bool timed, const Targets &tg) {
+int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, const unsigned char *d_halo, uint32_t n,
+           bool timed, const Targets &tg) {
 	int rc;
 	if ((rc = ensure_desc_capacity(c, n))) return rc;
 	c->last_timed = timed;
@@ -128,6 +129,7 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, ui
 		c->totals_slot ^= 1;
 		mm::AnalyseParams a;
 		a.chunks = d_chunks + (size_t)first * 4096u;
+		a.halo = d_halo ? d_halo + (size_t)first * MM_HALO_BYTES : nullptr;
 		a.n = m;
 		a.table = c->d_table;
 		a.flags = c->d_flags;
@@ -153,7 +155,8 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, ui
 			cfg.stream = c->stream;
 			cfg.attrs = attr;
 			cfg.numAttrs = 1;
-			MM_CUDA(c, cudaLaunchKernelEx(&cfg, mm::analyse_kernel, a));
+			if (d_halo) MM_CUDA(c, cudaLaunchKernelEx(&cfg, mm::analyse_kernel<true>, a));
+			else MM_CUDA(c, cudaLaunchKernelEx(&cfg, mm::analyse_kernel<false>, a));
 		}
 		c->ticket_base += (mm::u64)m + (mm::u64)grid;  // every CTA draws exactly one ticket >= m
 
@@ -219,11 +222,15 @@ int mm_ctx_create(int device, mm_ctx **out) {
 		MM_CUDA(c, cudaGetDeviceProperties(&prop, device));
 		if (prop.major < 10) return fail(c, MM_ERR_NO_DEVICE, "device %d is sm_%d%d; this library is built for sm_100a", device, prop.major, prop.minor);
 		c->sm_count = prop.multiProcessorCount;
-		MM_CUDA(c, cudaFuncSetAttribute(mm::analyse_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+		MM_CUDA(c, cudaFuncSetAttribute(mm::analyse_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+		MM_CUDA(c, cudaFuncSetAttribute(mm::analyse_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
 		MM_CUDA(c, cudaFuncSetAttribute(mm::expand_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mm::kExpandSmemBytes));
 		MM_CUDA(c, cudaFuncSetAttribute(mm::expand_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
 		int occ = 0;
-		MM_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mm::analyse_kernel, mm::kThreads, 0));
+		MM_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, mm::analyse_kernel<false>, mm::kThreads, 0));
+		int occh = 0;  // the halo instantiation runs on the same grid
+		MM_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occh, mm::analyse_kernel<true>, mm::kThreads, 0));
+		occ = std::min(occ, occh);
 		if (occ < 1) return fail(c, MM_ERR_CUDA, "analyse kernel does not fit on an SM");
 		c->ctas_per_sm = occ;
 		c->analyse_ctas_per_sm = occ;
@@ -265,7 +272,7 @@ int mm_ctx_destroy(mm_ctx *c) {
 	if (c->own_stream) cudaStreamSynchronize(c->own_stream);
 	cudaFree(c->d_table); cudaFree(c->d_out_i); cudaFree(c->d_out_t); cudaFree(c->d_ranges_i);
 	cudaFree(c->d_ranges_t); cudaFree(c->d_cnt); cudaFree(c->d_desc_i); cudaFree(c->d_desc_t); cudaFree(c->d_flags); cudaFree(c->d_ticket);
-	cudaFree(c->d_in_chunks); cudaFree(c->d_in_offs); cudaFree(c->d_trace);
+	cudaFree(c->d_in_chunks); cudaFree(c->d_in_offs); cudaFree(c->d_in_halo); cudaFree(c->d_trace);
 	if (c->h_totals) cudaFreeHost(c->h_totals);
 	if (c->h_in) cudaFreeHost(c->h_in);
 	if (c->h_small) cudaFreeHost(c->h_small);
@@ -375,20 +382,26 @@ int mm_reserve(mm_ctx *c, uint32_t max_chunks, uint64_t iv, uint64_t tv) {
 }
 
 int mm_mesh_batch_async(mm_ctx *c, const uint8_t *d_chunks, const int64_t *d_offs, uint32_t n) {
+	return mm_mesh_batch_halo_async(c, d_chunks, d_offs, nullptr, n);
+}
+
+int mm_mesh_batch_halo_async(mm_ctx *c, const uint8_t *d_chunks, const int64_t *d_offs, const uint8_t *d_halo, uint32_t n) {
 	if (!c || (n && (!d_chunks || !d_offs))) return MM_ERR_INVALID;
+	if (d_halo && ((uintptr_t)d_halo & 15u)) return fail(c, MM_ERR_INVALID, "halo must be 16-byte aligned");
 	if (!c->have_table) return fail(c, MM_ERR_NO_TABLE, "mm_set_block_table has not been called");
 	if (use_device(c)) return MM_ERR_CUDA;
 	c->finished = false;
 	c->pending = false;
 	c->last_chunks = d_chunks;
 	c->last_offs = (const long long *)d_offs;
+	c->last_halo = d_halo;
 	c->last_n = n;
 	c->last_launches = 0;
 	c->tot_i = c->tot_t = 0;
 	if (n == 0) { c->pending = true; return MM_OK; }
 	int rc;
 	if ((rc = ensure_chunk_capacity(c, n))) return rc;
-	if ((rc = launch(c, d_chunks, c->last_offs, n, c->time_next, device_targets(c)))) return rc;
+	if ((rc = launch(c, d_chunks, c->last_offs, d_halo, n, c->time_next, device_targets(c)))) return rc;
 	c->time_next = false;
 	c->pending = true;
 	return MM_OK;
@@ -408,7 +421,7 @@ int mm_batch_finish(mm_ctx *c, mm_batch_out *out) {
 			int rc;  // grow to fit (+1/8 head room) and run again: the inputs are still resident
 			if ((rc = ensure_arena(c, &c->d_out_i, &c->cap_i, c->tot_i + c->tot_i / 8))) return rc;
 			if ((rc = ensure_arena(c, &c->d_out_t, &c->cap_t, c->tot_t + c->tot_t / 8))) return rc;
-			if ((rc = launch(c, c->last_chunks, c->last_offs, c->last_n, c->last_timed, device_targets(c)))) return rc;
+			if ((rc = launch(c, c->last_chunks, c->last_offs, c->last_halo, c->last_n, c->last_timed, device_targets(c)))) return rc;
 		}
 		c->last_ms = 0.f;  // an untimed (mm_mesh_batch_async) batch enqueues kernels only
 		if (c->last_timed) MM_CUDA(c, cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1));
@@ -435,10 +448,22 @@ int mm_batch_finish(mm_ctx *c, mm_batch_out *out) {
 int mm_mesh_batch(mm_ctx *c, const uint8_t *chunks, const int64_t *offs, const uint8_t *halo, uint32_t n,
                   mm_batch_out *out) {
 	if (!c || (n && (!chunks || !offs))) return MM_ERR_INVALID;
-	if (halo) return fail(c, MM_ERR_UNSUPPORTED, "halo: the reference mesher has none (lib.rs:277-280)");
 	if (use_device(c)) return MM_ERR_CUDA;
 	const uint8_t *dc = chunks;
 	const int64_t *dof = offs;
+	const uint8_t *dh = halo;
+	if (n && halo && !is_device_ptr(halo)) {
+		if (n > c->cap_in_halo) {
+			MM_CUDA(c, cudaStreamSynchronize(c->stream));
+			cudaFree(c->d_in_halo);
+			c->d_in_halo = nullptr; c->cap_in_halo = 0;
+			const uint32_t nc = std::max<uint32_t>(n, 256u);
+			MM_CUDA(c, cudaMalloc(&c->d_in_halo, (size_t)nc * MM_HALO_BYTES));
+			c->cap_in_halo = nc;
+		}
+		MM_CUDA(c, cudaMemcpyAsync(c->d_in_halo, halo, (size_t)n * MM_HALO_BYTES, cudaMemcpyHostToDevice, c->stream));
+		dh = c->d_in_halo;
+	}
 	if (n && (!is_device_ptr(chunks) || !is_device_ptr(offs))) {
 		if (n > c->cap_in) {
 			MM_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -460,7 +485,7 @@ int mm_mesh_batch(mm_ctx *c, const uint8_t *chunks, const int64_t *offs, const u
 	}
 	int rc;
 	c->time_next = true;  // the synchronous call brackets its kernels with events: mm_batch_out.kernel_ms
-	if ((rc = mm_mesh_batch_async(c, dc, dof, n))) return rc;
+	if ((rc = mm_mesh_batch_halo_async(c, dc, dof, dh, n))) return rc;
 	return mm_batch_finish(c, out);
 }
 
@@ -533,7 +558,7 @@ static int small_batch_host(mm_ctx *c, const uint8_t *chunks, const int64_t *off
 		           (mm::Range *)(c->d_small + L.ranges_i), (mm::Range *)(c->d_small + L.ranges_t)};
 		c->pending = c->finished = false;  // the device arenas hold no batch of this call
 		c->last_launches = 0;
-		if ((rc = launch(c, d_chunks, d_offs, n, false, tg))) return rc;
+		if ((rc = launch(c, d_chunks, d_offs, nullptr, n, false, tg))) return rc;
 		MM_CUDA(c, cudaStreamSynchronize(c->stream));
 		const uint64_t ti = c->h_totals[0], tt = c->h_totals[1];
 		if (ti > c->mapped_qi || tt > c->mapped_qt) {  // nothing was written: grow the mapped arenas and run again

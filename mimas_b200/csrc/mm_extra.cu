@@ -107,6 +107,36 @@ __global__ void __launch_bounds__(256) gen_terrain_kernel(Region rg, uint32_t n,
 	}
 }
 
+// ---- halo slabs of a resident box of chunks (extension, see mm_mesh_batch) ------------------------
+// One CTA of 96 threads per chunk: thread t writes row t & 15 (16 ids) of slab t >> 4.  The x and y slabs
+// are 16-byte rows of the neighbour chunk; the z slabs gather its z = 15 / z = 0 layer (stride 16; the
+// box is L2-resident when it was just generated or uploaded).
+__global__ void __launch_bounds__(96) gather_halos_kernel(const uint8_t *chunks, uint32_t nx, uint32_t ny, uint32_t nz,
+                                                          uint32_t n, uint32_t outside, uint8_t *halo) {
+	for (uint32_t i = blockIdx.x; i < n; i += gridDim.x) {
+		const uint32_t cx = i % nx, cy = (i / nx) % ny, cz = i / (nx * ny);
+		const int t = threadIdx.x, slab = t >> 4, r = t & 15;
+		const int axis = slab >> 1;
+		const bool up = slab & 1;
+		const uint32_t pos = axis == 0 ? cx : axis == 1 ? cy : cz, lim = axis == 0 ? nx : axis == 1 ? ny : nz;
+		uint4 v = make_uint4(outside, outside, outside, outside);
+		if (up ? pos + 1 < lim : pos > 0) {
+			const size_t stride = axis == 0 ? 1 : axis == 1 ? nx : (size_t)nx * ny;
+			const uint8_t *nb = chunks + (up ? i + stride : i - stride) * 4096u;
+			const int edge = up ? 0 : 15;  // the neighbour's layer that touches this chunk
+			if (axis == 0) v = __ldg(reinterpret_cast<const uint4 *>(nb + edge * 256 + r * 16));       // (edge, y = r, z)
+			else if (axis == 1) v = __ldg(reinterpret_cast<const uint4 *>(nb + r * 256 + edge * 16));  // (x = r, edge, z)
+			else {                                                                                       // (x = r, y, edge)
+				uint32_t w[4] = {0, 0, 0, 0};
+#pragma unroll
+				for (int y = 0; y < 16; y++) w[y >> 2] |= (uint32_t)__ldg(nb + r * 256 + y * 16 + edge) << (8 * (y & 3));
+				v = make_uint4(w[0], w[1], w[2], w[3]);
+			}
+		}
+		reinterpret_cast<uint4 *>(halo + (size_t)i * MM_HALO_BYTES)[t] = v;
+	}
+}
+
 }  // namespace
 
 extern "C" {
@@ -165,6 +195,21 @@ int mm_gen_terrain_device(mm_ctx *c, uint64_t seed, int64_t cx0, int64_t cy0, in
 	const uint32_t n = (uint32_t)n64;
 	const uint32_t grid = n < (uint32_t)c->sm_count * 8u ? n : (uint32_t)c->sm_count * 8u;
 	gen_terrain_kernel<<<grid, 256, 0, c->stream>>>(rg, n, d_chunks, (long long *)d_offs);
+	MM_CUDA(c, cudaGetLastError());
+	return MM_OK;
+}
+
+int mm_gather_halos(mm_ctx *c, const uint8_t *d_chunks, uint32_t nx, uint32_t ny, uint32_t nz, uint8_t outside_id,
+                    uint8_t *d_halo) {
+	if (!c || !d_chunks || !d_halo || !nx || !ny || !nz) return MM_ERR_INVALID;
+	if (((uintptr_t)d_halo | (uintptr_t)d_chunks) & 15u) return fail(c, MM_ERR_INVALID, "chunks and halo must be 16-byte aligned");
+	MM_CUDA(c, cudaSetDevice(c->device));
+	const uint64_t n64 = (uint64_t)nx * ny * nz;
+	if (n64 > 0x7fffffffull) return fail(c, MM_ERR_INVALID, "region too large");
+	const uint32_t n = (uint32_t)n64;
+	const uint32_t grid = n < (uint32_t)c->sm_count * 16u ? n : (uint32_t)c->sm_count * 16u;
+	const uint32_t o = outside_id * 0x01010101u;
+	gather_halos_kernel<<<grid, 96, 0, c->stream>>>(d_chunks, nx, ny, nz, n, o, d_halo);
 	MM_CUDA(c, cudaGetLastError());
 	return MM_OK;
 }

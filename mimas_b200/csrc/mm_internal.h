@@ -50,6 +50,8 @@ struct mm_ctx {
 	unsigned char *d_in_chunks = nullptr;
 	long long *d_in_offs = nullptr;
 	uint32_t cap_in = 0;
+	unsigned char *d_in_halo = nullptr;  // halo mode: staging for halos handed in as host memory
+	uint32_t cap_in_halo = 0;
 	unsigned char *h_in = nullptr;  // pinned staging: chunks then offs
 	size_t h_in_bytes = 0;
 
@@ -66,6 +68,7 @@ struct mm_ctx {
 	// last batch
 	bool pending = false, finished = false;
 	const unsigned char *last_chunks = nullptr;
+	const unsigned char *last_halo = nullptr;
 	const long long *last_offs = nullptr;
 	uint32_t last_n = 0;
 	uint32_t last_launches = 0;

@@ -268,11 +268,19 @@ class Mesher:
                                              C.byref(pi), C.byref(ni), C.byref(pt), C.byref(nt)))
         return ChunkMesh(_copy_from(pi.value, ni.value, VERTEX_DTYPE), _copy_from(pt.value, nt.value, VERTEX_DTYPE))
 
-    def mesh_batch(self, offs, chunks) -> BatchMesh:
-        """Host in, host out: n chunks meshed in one call (batch form of mesh_for_chunk)."""
+    def mesh_batch(self, offs, chunks, halo=None) -> BatchMesh:
+        """Host in, host out: n chunks meshed in one call (batch form of mesh_for_chunk).
+        `halo` ([n, 6, 256] block ids, see mm_mesh_batch in the header) switches on the halo extension: faces
+        against blocky cells of the neighbouring chunks are culled.  None = the reference's semantics."""
         chunks = np.ascontiguousarray(chunks, dtype=np.uint8).reshape(-1, 4096)
         n = chunks.shape[0]
         offs = np.ascontiguousarray(offs, dtype=np.int64).reshape(n, 3)
+        if halo is not None:
+            halo = np.ascontiguousarray(halo, dtype=np.uint8).reshape(n, 1536)
+            out = _BatchOut()
+            self._ck(self._lib.mm_mesh_batch(self._ctx, C.c_void_p(chunks.ctypes.data), C.c_void_p(offs.ctypes.data),
+                                             C.c_void_p(halo.ctypes.data), n, C.byref(out)))
+            return self.copy_out(out)
         hm = _HostMesh()
         self._ck(self._lib.mm_mesh_batch_host(self._ctx, chunks.ctypes.data, offs.ctypes.data, n, C.byref(hm)))
         return BatchMesh(_copy_from(hm.intransparent, hm.n_intransparent, VERTEX_DTYPE),
@@ -306,14 +314,25 @@ class Mesher:
     def reserve(self, max_chunks: int, intransparent_vertices: int, transparent_vertices: int):
         self._ck(self._lib.mm_reserve(self._ctx, max_chunks, intransparent_vertices, transparent_vertices))
 
-    def mesh_batch_device(self, d_chunks: int, d_offs: int, n: int) -> _BatchOut:
+    def mesh_batch_device(self, d_chunks: int, d_offs: int, n: int, d_halo: Optional[int] = None) -> _BatchOut:
         """Synchronous mesh of device-resident inputs (raw device pointers)."""
         out = _BatchOut()
-        self._ck(self._lib.mm_mesh_batch(self._ctx, C.c_void_p(d_chunks), C.c_void_p(d_offs), None, n, C.byref(out)))
+        self._ck(self._lib.mm_mesh_batch(self._ctx, C.c_void_p(d_chunks), C.c_void_p(d_offs),
+                                         C.c_void_p(d_halo) if d_halo else None, n, C.byref(out)))
         return out
 
-    def mesh_batch_async(self, d_chunks: int, d_offs: int, n: int):
-        self._ck(self._lib.mm_mesh_batch_async(self._ctx, C.c_void_p(d_chunks), C.c_void_p(d_offs), n))
+    def mesh_batch_async(self, d_chunks: int, d_offs: int, n: int, d_halo: Optional[int] = None):
+        if d_halo:
+            self._ck(self._lib.mm_mesh_batch_halo_async(self._ctx, C.c_void_p(d_chunks), C.c_void_p(d_offs),
+                                                        C.c_void_p(d_halo), n))
+        else:
+            self._ck(self._lib.mm_mesh_batch_async(self._ctx, C.c_void_p(d_chunks), C.c_void_p(d_offs), n))
+
+    def gather_halos(self, d_chunks: int, dims, d_halo: int, outside_id: int = 0):
+        """Halo slabs (n * 1536 bytes at d_halo) of a device-resident box of dims = (nx, ny, nz) chunks in
+        gen_terrain order; `outside_id` is what lies beyond the box."""
+        self._ck(self._lib.mm_gather_halos(self._ctx, C.c_void_p(d_chunks), dims[0], dims[1], dims[2], outside_id,
+                                           C.c_void_p(d_halo)))
 
     def batch_finish(self) -> _BatchOut:
         out = _BatchOut()

@@ -263,11 +263,51 @@ def cfg_draw(m, stream):
     return res
 
 
+def cfg_halo(m, stream):
+    """Halo extension on the bench region (64x32x2 chunks at (-32,-16,-1), seed 78): slabs gathered on the device,
+    then the region meshed with and without them; streamed like bench.py (8 batches queued per measurement)."""
+    from tests.util import halos_for_box
+    dims, c0 = (64, 32, 2), (-32, -16, -1)
+    n = dims[0] * dims[1] * dims[2]
+    dc, do, dh = m.dev_alloc(n * 4096), m.dev_alloc(n * 24), m.dev_alloc(n * 1536)
+    m.gen_terrain_device(78, c0, dims, dc, do)
+    m.sync()
+    chunks = m.download(dc, n * 4096).reshape(n, 4096)
+    offs = m.download(do, n * 24).view(np.int64).reshape(n, 3)
+    m.set_stream(stream.cuda_stream)
+    with torch.cuda.stream(stream):
+        m.gather_halos(dc, dims, dh, 0)
+        t_gather = timed(stream, lambda: m.gather_halos(dc, dims, dh, 0), reps=20) * 1e-3
+        gather_ok = m.download(dh, n * 1536).tobytes() == halos_for_box(chunks, dims, 0).tobytes()
+        res = {}
+        for name, h in (("reference_mode", None), ("halo_mode", dh)):
+            m.mesh_batch_async(dc, do, n, d_halo=h)
+            out = m.batch_finish()
+            for _ in range(3):
+                timed(stream, lambda: m.mesh_batch_async(dc, do, n, d_halo=h), reps=8)
+            t = float(np.median([timed(stream, lambda: m.mesh_batch_async(dc, do, n, d_halo=h), reps=8) for _ in range(9)])) * 1e-3
+            out = m.batch_finish()
+            halo_host = None if h is None else m.download(dh, n * 1536).reshape(n, 6, 256)
+            want = oracle.mesh_batch(chunks, offs, OC, threads=CORES, halo=halo_host)
+            got = m.copy_out(out)
+            ok = (got.intransparent.tobytes() == want["intransparent"].tobytes()
+                  and got.transparent.tobytes() == want["transparent"].tobytes())
+            nv = int(out.n_intransparent + out.n_transparent)
+            alg = n * (4136 + (1536 if h else 0)) + 36 * nv + 2048
+            res[name] = {"ms_per_batch": t * 1e3, "chunks_per_s": n / t, "vertices": nv, "algorithmic_gbs": alg / t / 1e9,
+                         "frac_of_measured_peak": alg / t / 1e9 / PEAK, "bit_exact_vs_oracle": bool(ok)}
+    m.set_stream(0)
+    for p in (dc, do, dh):
+        m.dev_free(p)
+    return {"config": "halo extension: 4096 synthetic mapgen chunks (bench region), slabs gathered on the device",
+            "gather_ms": t_gather * 1e3, "gather_equals_numpy": bool(gather_ok), **res}
+
+
 def main():
-    which = [a for a in sys.argv[1:] if a.startswith("cfg")] or ["cfg1", "cfg3", "cfg4", "cfg5", "cfg_draw"]
+    which = [a for a in sys.argv[1:] if a.startswith("cfg")] or ["cfg1", "cfg3", "cfg4", "cfg5", "cfg_draw", "cfg_halo"]
     m = mimas_b200.Mesher(0, mimas_b200.default_cache())
     stream = torch.cuda.Stream()
-    fns = {"cfg1": cfg1, "cfg3": cfg3, "cfg4": cfg4, "cfg5": cfg5, "cfg_draw": cfg_draw}
+    fns = {"cfg1": cfg1, "cfg3": cfg3, "cfg4": cfg4, "cfg5": cfg5, "cfg_draw": cfg_draw, "cfg_halo": cfg_halo}
     for w in which:
         t0 = time.time()
         r = fns[w](m, stream)

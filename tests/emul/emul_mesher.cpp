@@ -42,9 +42,10 @@ extern "C" uint32_t emul_eq_mask16(const uint8_t a[16], const uint8_t b[16]) {
 	return eq_mask16(ca, cb);
 }
 
-extern "C" int emul_mesh_batch(const uint8_t *chunks, const int64_t *offs, uint32_t n, const TabEntry *tab,
-                               unsigned char *out_i, uint64_t cap_i, unsigned char *out_t, uint64_t cap_t,
-                               Range *ranges_i, Range *ranges_t, uint64_t *totals) {
+template <bool HALO>
+static int mesh_batch_t(const uint8_t *chunks, const int64_t *offs, uint32_t n, const TabEntry *tab,
+                        unsigned char *out_i, uint64_t cap_i, unsigned char *out_t, uint64_t cap_t,
+                        Range *ranges_i, Range *ranges_t, uint64_t *totals, const uint8_t *halo) {
 	ChunkSmem *sp = new ChunkSmem();
 	ChunkSmem &s = *sp;
 	memset(&s, 0xA5, sizeof(s));  // nothing may depend on stale shared memory
@@ -68,6 +69,8 @@ extern "C" int emul_mesh_batch(const uint8_t *chunks, const int64_t *offs, uint3
 			cnt_t[c] = 0;
 			continue;
 		}
+		if (HALO)
+			for (int tid = 0; tid < 96; tid++) halo_row(s, flags, load_col(halo + (size_t)c * 1536 + tid * 16), tid);
 		for (int j = 0; j < 2; j++)
 			for (int tid = 0; tid < 128; tid++) {
 				const int col = 128 * j + tid;
@@ -81,9 +84,11 @@ extern "C" int emul_mesh_batch(const uint8_t *chunks, const int64_t *offs, uint3
 		uint32_t *di = desc_i.data() + (size_t)c * kDescStrideI;
 		if (amb & kFlagBlocky) {
 			// B
-			for (int col = 0; col < 256; col++) col_starts(s, tab, raw, col >> 4, col & 15, amb);
+			for (int col = 0; col < 256; col++) col_starts<HALO>(s, tab, raw, col >> 4, col & 15, amb);
 			// C
 			for (int lane = 0; lane < kLanes; lane++) transpose_blocky(s, lane);
+			if (HALO)
+				for (int job = 0; job < 4; job++) transpose_halo(s, job);
 			uint32_t run = 0;
 			for (int m = 0; m < kGroups; m++) s.gcnt[m] = transpose_group(s, m);
 			for (int m = 0; m < kGroups; m++) {  // exclusive scan, quads (low half) and words (high half) at once
@@ -98,7 +103,7 @@ extern "C" int emul_mesh_batch(const uint8_t *chunks, const int64_t *offs, uint3
 			for (uint32_t i = 0; i < nwords; i++) {
 				const uint32_t e = smem_wl(s)[i];
 				const uint32_t widx = e & 1023u;
-				emit_word_descs(s, widx, reinterpret_cast<const uint32_t *>(s.S)[widx], di + (e >> 10));
+				emit_word_descs<HALO>(s, widx, reinterpret_cast<const uint32_t *>(s.S)[widx], di + (e >> 10));
 			}
 		}
 		if (amb & kFlagCrossed) {
@@ -151,4 +156,17 @@ extern "C" int emul_mesh_batch(const uint8_t *chunks, const int64_t *offs, uint3
 		}
 	}
 	return 0;
+}
+
+extern "C" int emul_mesh_batch(const uint8_t *chunks, const int64_t *offs, uint32_t n, const TabEntry *tab,
+                               unsigned char *out_i, uint64_t cap_i, unsigned char *out_t, uint64_t cap_t,
+                               Range *ranges_i, Range *ranges_t, uint64_t *totals) {
+	return mesh_batch_t<false>(chunks, offs, n, tab, out_i, cap_i, out_t, cap_t, ranges_i, ranges_t, totals, nullptr);
+}
+
+// halo: n * 1536 block ids (see halo_row in mesh_core.cuh), 16-byte aligned
+extern "C" int emul_mesh_batch_halo(const uint8_t *chunks, const int64_t *offs, uint32_t n, const TabEntry *tab,
+                                    unsigned char *out_i, uint64_t cap_i, unsigned char *out_t, uint64_t cap_t,
+                                    Range *ranges_i, Range *ranges_t, uint64_t *totals, const uint8_t *halo) {
+	return mesh_batch_t<true>(chunks, offs, n, tab, out_i, cap_i, out_t, cap_t, ranges_i, ranges_t, totals, halo);
 }

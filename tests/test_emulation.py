@@ -35,7 +35,7 @@ def emul():
     subprocess.run(["make", "-C", os.path.join(HERE, "emul"), "-s"], check=True)
     lib = C.CDLL(os.path.join(HERE, "emul", "libemul_mesher.so"))
 
-    def run(chunks, offs, tab, cap_quads=None):
+    def run(chunks, offs, tab, cap_quads=None, halo=None):
         chunks = np.ascontiguousarray(chunks, dtype=np.uint8).reshape(-1, 4096)
         n = len(chunks)
         offs = np.ascontiguousarray(offs, dtype=np.int64).reshape(n, 3)
@@ -45,10 +45,16 @@ def emul():
         ri = np.zeros((n, 2), dtype=np.uint64)
         rt = np.zeros((n, 2), dtype=np.uint64)
         tot = np.zeros(2, dtype=np.uint64)
-        lib.emul_mesh_batch(C.c_void_p(chunks.ctypes.data), C.c_void_p(offs.ctypes.data), C.c_uint32(n),
-                            C.c_void_p(tab.ctypes.data), C.c_void_p(ptrs[0]), C.c_uint64(cap), C.c_void_p(ptrs[1]),
-                            C.c_uint64(cap), C.c_void_p(ri.ctypes.data), C.c_void_p(rt.ctypes.data),
-                            C.c_void_p(tot.ctypes.data))
+        args = [C.c_void_p(chunks.ctypes.data), C.c_void_p(offs.ctypes.data), C.c_uint32(n),
+                C.c_void_p(tab.ctypes.data), C.c_void_p(ptrs[0]), C.c_uint64(cap), C.c_void_p(ptrs[1]),
+                C.c_uint64(cap), C.c_void_p(ri.ctypes.data), C.c_void_p(rt.ctypes.data), C.c_void_p(tot.ctypes.data)]
+        if halo is None:
+            lib.emul_mesh_batch(*args)
+        else:
+            hb = np.zeros(n * 1536 + 16, dtype=np.uint8)
+            ho = (-hb.ctypes.data) % 16
+            hb[ho:ho + n * 1536] = np.ascontiguousarray(halo, dtype=np.uint8).reshape(-1)
+            lib.emul_mesh_batch_halo(*args, C.c_void_p(hb.ctypes.data + ho))
         outs = []
         for b, p, t in zip(bufs, ptrs, tot):
             o = p - b.ctypes.data
@@ -128,5 +134,51 @@ def test_emulated_shared_textures(emul):
     offs = (rng.randint(-50, 50, size=(8, 3)) * 16).astype(np.int64)
     want = oracle.mesh_batch(chunks, offs, oracle.cache_from_entries(rows, len(rows), fb))
     i, t, _, _ = emul(chunks, offs, kernel_table(rows, fb))
+    assert first_diff(i, want["intransparent"].tobytes()) is None
+    assert first_diff(t, want["transparent"].tobytes()) is None
+
+
+# ---- halo mode (extension; oracle: blocked() with halo slabs) ----------------------------------------
+
+def test_emulated_halo_of_air_equals_reference_mode(emul):
+    c = G.cases["random_dense_ids"]
+    a = emul(c["chunk"], c["offs"], TAB)
+    h = emul(c["chunk"], c["offs"], TAB, halo=np.zeros((1, 6, 256), np.uint8))
+    assert a[0] == h[0] and a[1] == h[1]
+    assert first_diff(h[0], c["intr"]) is None
+
+
+def test_emulated_halo_regions_match_oracle(emul):
+    from tests.util import region_to_chunks_and_halos
+    oc = oracle_cache(G)
+    rng = np.random.RandomState(11)
+    # a region of every kind of id (blocky, crossed, undrawn, unknown) and random halos around random chunks
+    vol = rng.randint(0, 70, size=(32, 32, 32)).astype(np.uint8)
+    vol[rng.rand(32, 32, 32) < 0.4] = 0
+    chunks, offs, halo = region_to_chunks_and_halos(vol, outside=3)
+    rc = rng.randint(0, 256, size=(6, 4096)).astype(np.uint8)
+    rh = rng.randint(0, 256, size=(6, 6, 256)).astype(np.uint8)
+    rh[rng.rand(6, 6, 256) < 0.5] = 0
+    ro = (rng.randint(-2 ** 30, 2 ** 30, size=(6, 3)) * 16).astype(np.int64)
+    chunks = np.concatenate([chunks, rc])
+    offs = np.concatenate([offs, ro])
+    halo = np.concatenate([halo, rh])
+    want = oracle.mesh_batch(chunks, offs, oc, threads=4, halo=halo)
+    i, t, ri, rt = emul(chunks, offs, TAB, halo=halo)
+    assert first_diff(i, want["intransparent"].tobytes()) is None
+    assert first_diff(t, want["transparent"].tobytes()) is None
+    assert list(ri[:, 1] & 0xFFFFFFFF) == list(want["count_i"])
+
+
+def test_emulated_halo_shared_textures(emul):
+    rows = [(0, 0, 0, 0, 0), (1, 7, 8, 9, 0), (1, 7, 8, 10, 0), (1, 11, 8, 9, 0), (1, 7, 12, 9, 0), (2, 0, 0, 0, 5)]
+    fb = (7, 8, 9)
+    rng = np.random.RandomState(4)
+    pal = np.array([0, 1, 2, 3, 4, 5, 77], dtype=np.uint8)
+    chunks = pal[rng.randint(0, 7, size=(8, 4096))]
+    halo = pal[rng.randint(0, 7, size=(8, 6, 256))]
+    offs = (rng.randint(-50, 50, size=(8, 3)) * 16).astype(np.int64)
+    want = oracle.mesh_batch(chunks, offs, oracle.cache_from_entries(rows, len(rows), fb), halo=halo)
+    i, t, _, _ = emul(chunks, offs, kernel_table(rows, fb), halo=halo)
     assert first_diff(i, want["intransparent"].tobytes()) is None
     assert first_diff(t, want["transparent"].tobytes()) is None

@@ -214,11 +214,74 @@ def test_push_block_matches_oracle(mesher):
         assert first_diff(got.tobytes(), want.tobytes()) is None
 
 
-def test_halo_is_rejected(mesher):
-    """The reference has no halo (lib.rs:277-280); a non-NULL halo is not silently ignored."""
+# ---- halo mode: an extension (the reference has no halo, lib.rs:277-280); parity is against the oracle's
+# `blocked` with halo slabs, which tests/test_halo.py checks against a numpy face count ---------------------
+
+def test_halo_of_air_is_the_reference_mode(mesher, ocache):
+    chunks = np.stack([G.cases[n]["chunk"] for n in G.names])
+    offs = np.stack([G.cases[n]["offs"] for n in G.names])
+    got = mesher.mesh_batch(offs, chunks, halo=np.zeros((len(chunks), 6, 256), np.uint8))
+    assert got.intransparent.tobytes() == b"".join(G.cases[n]["intr"] for n in G.names)
+    assert got.transparent.tobytes() == b"".join(G.cases[n]["trans"] for n in G.names)
+
+
+def test_halo_random_slabs_match_oracle(mesher, ocache):
+    rng = np.random.RandomState(21)
+    n = 300
+    chunks = rng.randint(0, 256, size=(n, 4096)).astype(np.uint8)
+    chunks[rng.rand(n, 4096) < 0.3] = 0
+    chunks[:40] = 5  # solid chunks: only what the halo leaves open comes back
+    halo = rng.randint(0, 256, size=(n, 6, 256)).astype(np.uint8)
+    halo[rng.rand(n, 6, 256) < 0.5] = 0
+    halo[:8] = 5
+    offs = (rng.randint(-2 ** 30, 2 ** 30, size=(n, 3)) * 16).astype(np.int64)
+    got = mesher.mesh_batch(offs, chunks, halo=halo)
+    assert_batch_equal(got, oracle.mesh_batch(chunks, offs, ocache, threads=8, halo=halo))
+    assert list(got.ranges_i["vertex_count"][:8]) == [0] * 8
+
+
+def test_halo_terrain_box_gathered_on_device(mesher, ocache):
+    """mm_gather_halos on a resident box = the numpy gather; the halo mesh of the box = the oracle's, and it
+    has fewer faces than the reference mode (the chunk borders below ground vanish)."""
+    import mimas_b200
+    from tests.util import halos_for_box
+    dims, c0 = (12, 10, 5), (-6, -5, -2)
+    n = dims[0] * dims[1] * dims[2]
+    chunks, offs = mimas_b200.gen_terrain_host(78, c0, dims)
+    halo = halos_for_box(chunks, dims, outside=3)
+    d_c, d_o, d_h = mesher.dev_alloc(n * 4096), mesher.dev_alloc(n * 24), mesher.dev_alloc(n * 1536)
+    try:
+        mesher.upload(d_c, chunks)
+        mesher.upload(d_o, offs)
+        mesher.gather_halos(d_c, dims, d_h, outside_id=3)
+        mesher.sync()
+        assert mesher.download(d_h, n * 1536).tobytes() == halo.tobytes()
+        want = oracle.mesh_batch(chunks, offs, ocache, threads=8, halo=halo)
+        for _ in range(2):
+            mesher.mesh_batch_async(d_c, d_o, n, d_halo=d_h)
+        got = mesher.copy_out(mesher.batch_finish())
+        assert_batch_equal(got, want)
+        plain = mesher.copy_out(mesher.mesh_batch_device(d_c, d_o, n))
+        assert len(plain.intransparent) > len(got.intransparent)
+        # a second halo batch after a plain one (the two analyse kernels alternate on one stream)
+        assert_batch_equal(mesher.copy_out(mesher.mesh_batch_device(d_c, d_o, n, d_halo=d_h)), want)
+    finally:
+        for p in (d_c, d_o, d_h):
+            mesher.dev_free(p)
+
+
+def test_halo_batch_larger_than_one_launch_and_misaligned_halo(mesher, ocache):
     import ctypes as C
     from mimas_b200._lib import lib
-    chunk = np.zeros(4096, np.uint8)
-    offs = np.zeros(3, np.int64)
-    rc = lib().mm_mesh_batch(mesher._ctx, chunk.ctypes.data, offs.ctypes.data, chunk.ctypes.data, 1, None)
-    assert rc == 7
+    from tests.util import checkerboard_chunks
+    chunks, offs = checkerboard_chunks(4500)
+    rng = np.random.RandomState(2)
+    halo = np.where(rng.rand(4500, 6, 256) < 0.5, 5, 0).astype(np.uint8)
+    got = mesher.mesh_batch(offs, chunks, halo=halo)
+    assert_batch_equal(got, oracle.mesh_batch(chunks, offs, ocache, threads=8, halo=halo))
+    d = mesher.dev_alloc(4096 + 24 + 1536 + 64)
+    try:
+        rc = lib().mm_mesh_batch_halo_async(mesher._ctx, C.c_void_p(d), C.c_void_p(d + 4096), C.c_void_p(d + 4096 + 24 + 8), 1)
+        assert rc == 1  # MM_ERR_INVALID: device halos are read 16 bytes at a time
+    finally:
+        mesher.dev_free(d)

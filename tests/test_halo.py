@@ -102,3 +102,21 @@ def test_region_face_count_matches_numpy(seed, cache):
     # and without halos every chunk border is a surface: strictly more faces
     r0 = oracle.mesh_batch(chunks, offs, cache)
     assert int(r0["count_i"].sum() + r0["count_t"].sum()) > int(r["count_i"].sum() + r["count_t"].sum())
+
+
+def test_box_halo_helper_layout():
+    """halos_for_box (the numpy meaning of mm_gather_halos): slabs are the neighbours' touching layers."""
+    from tests.util import halos_for_box
+    rng = np.random.default_rng(0)
+    nx, ny, nz = 3, 2, 2
+    chunks = rng.integers(0, 256, size=(nx * ny * nz, 4096), dtype=np.uint8)
+    halo = halos_for_box(chunks, (nx, ny, nz), outside=9)
+    c = chunks.reshape(-1, 16, 16, 16)
+    idx = lambda cx, cy, cz: cx + nx * (cy + ny * cz)
+    i = idx(1, 0, 1)
+    assert (halo[i, 0].reshape(16, 16) == c[idx(0, 0, 1)][15, :, :]).all()   # x-: [y, z]
+    assert (halo[i, 1].reshape(16, 16) == c[idx(2, 0, 1)][0, :, :]).all()    # x+
+    assert (halo[i, 2] == 9).all()                                            # y-: outside the box
+    assert (halo[i, 3].reshape(16, 16) == c[idx(1, 1, 1)][:, 0, :]).all()    # y+: [x, z]
+    assert (halo[i, 4].reshape(16, 16) == c[idx(1, 0, 0)][:, :, 15]).all()   # z-: [x, y]
+    assert (halo[i, 5] == 9).all()

@@ -115,3 +115,14 @@ def region_to_chunks_and_halos(vol, outside=0):
                     pad[x0:x0 + 16, y0:y0 + 16, z0 - 1], pad[x0:x0 + 16, y0:y0 + 16, z0 + 16]]).reshape(6, 256))
     return (np.ascontiguousarray(np.stack(chunks)), np.array(offs, dtype=np.int64),
             np.ascontiguousarray(np.stack(halos)))
+
+
+def halos_for_box(chunks, dims, outside=0):
+    """Halo slabs [n, 6, 256] of a box of dims = (nx, ny, nz) chunks in gen_terrain order (chunk i at
+    (i % nx, (i // nx) % ny, i // (nx*ny))) -- the numpy meaning of mm_gather_halos."""
+    nx, ny, nz = dims
+    c = np.asarray(chunks, dtype=np.uint8).reshape(nz, ny, nx, 16, 16, 16)  # [cz, cy, cx, x, y, z]
+    vol = c.transpose(2, 3, 1, 4, 0, 5).reshape(nx * 16, ny * 16, nz * 16)
+    _, _, halo = region_to_chunks_and_halos(vol, outside)                     # cx-major order
+    halo = halo.reshape(nx, ny, nz, 6, 256).transpose(2, 1, 0, 3, 4)
+    return np.ascontiguousarray(halo.reshape(nx * ny * nz, 6, 256))
