@@ -281,7 +281,7 @@ def test_halo_batch_larger_than_one_launch_and_misaligned_halo(mesher, ocache):
     assert_batch_equal(got, oracle.mesh_batch(chunks, offs, ocache, threads=8, halo=halo))
     d = mesher.dev_alloc(4096 + 24 + 1536 + 64)
     try:
-        rc = lib().mm_mesh_batch_halo_async(mesher._ctx, C.c_void_p(d), C.c_void_p(d + 4096), C.c_void_p(d + 4096 + 24 + 8), 1)
+        rc = lib().mm_mesh_batch_halo_async(mesher._ctx, C.c_void_p(d), C.c_void_p(d + 4096), C.c_void_p(d + 4096 + 32 + 8), 1)
         assert rc == 1  # MM_ERR_INVALID: device halos are read 16 bytes at a time
     finally:
         mesher.dev_free(d)
