@@ -89,6 +89,18 @@ int ensure_pinned(mm_ctx *c, unsigned char **p, size_t *have, size_t want) {
 	return MM_OK;
 }
 
+int ensure_in_capacity(mm_ctx *c, uint32_t n) {  // device staging of host inputs
+	if (n <= c->cap_in) return MM_OK;
+	MM_CUDA(c, cudaStreamSynchronize(c->stream));
+	cudaFree(c->d_in_chunks); cudaFree(c->d_in_offs);
+	c->d_in_chunks = nullptr; c->d_in_offs = nullptr; c->cap_in = 0;
+	const uint32_t nc = std::max<uint32_t>(n, 256u);
+	MM_CUDA(c, cudaMalloc(&c->d_in_chunks, (size_t)nc * 4096));
+	MM_CUDA(c, cudaMalloc(&c->d_in_offs, (size_t)nc * 24));
+	c->cap_in = nc;
+	return MM_OK;
+}
+
 // Descriptor slots for launches of up to n chunks (64 KiB per chunk; only the touched lines cost
 // bandwidth, and they are re-read from L2 by the expand kernel).
 int ensure_desc_capacity(mm_ctx *c, uint32_t n) {
@@ -118,12 +130,12 @@ struct Targets {  // where a batch's vertices and range records go
 Targets device_targets(const mm_ctx *c) { return Targets{c->d_out_i, c->d_out_t, c->cap_i, c->cap_t, c->d_ranges_i, c->d_ranges_t}; }
 
 int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, const unsigned char *d_halo, uint32_t n,
-           bool timed, const Targets &tg) {
+           bool timed, const Targets &tg, const mm::u64 *carry0 = nullptr) {
 	int rc;
 	if ((rc = ensure_desc_capacity(c, n))) return rc;
 	c->last_timed = timed;
 	if (timed) MM_CUDA(c, cudaEventRecord(c->ev0, c->stream));
-	const mm::u64 *carry = nullptr;
+	const mm::u64 *carry = carry0;  // totals of an earlier piece of the same batch, or NULL
 	for (uint32_t first = 0; first < n; first += mm::kMaxLaunchChunks) {
 		const uint32_t m = std::min<uint32_t>(n - first, mm::kMaxLaunchChunks);
 		c->totals_slot ^= 1;
@@ -240,6 +252,7 @@ int mm_ctx_create(int device, mm_ctx **out) {
 		if (occ2 < 1) return fail(c, MM_ERR_CUDA, "expand kernel does not fit on an SM");
 		c->expand_grid = c->sm_count * occ2;
 		c->use_pdl = getenv("MM_NO_PDL") == nullptr;
+		if (const char *e = getenv("MM_PIPE_MIN_CHUNKS")) c->pipe_min_chunks = (uint32_t)std::max(0, atoi(e));
 		c->no_small = getenv("MM_NO_SMALL_PATH") != nullptr;
 		if (const char *e = getenv("MM_MAPPED_MAX_CHUNKS")) c->mapped_max_chunks = (uint32_t)strtoul(e, nullptr, 10);
 		MM_CUDA(c, cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
@@ -281,6 +294,10 @@ int mm_ctx_destroy(mm_ctx *c) {
 	if (c->ev2) cudaEventDestroy(c->ev2);
 	if (c->ev3) cudaEventDestroy(c->ev3);
 	if (c->h_out) cudaFreeHost(c->h_out);
+	if (c->s_in) cudaStreamDestroy(c->s_in);
+	if (c->s_out) cudaStreamDestroy(c->s_out);
+	for (cudaEvent_t e : c->ev_in)
+		if (e) cudaEventDestroy(e);
 	if (c->ev0) cudaEventDestroy(c->ev0);
 	if (c->ev1) cudaEventDestroy(c->ev1);
 	if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -465,15 +482,8 @@ int mm_mesh_batch(mm_ctx *c, const uint8_t *chunks, const int64_t *offs, const u
 		dh = c->d_in_halo;
 	}
 	if (n && (!is_device_ptr(chunks) || !is_device_ptr(offs))) {
-		if (n > c->cap_in) {
-			MM_CUDA(c, cudaStreamSynchronize(c->stream));
-			cudaFree(c->d_in_chunks); cudaFree(c->d_in_offs);
-			c->d_in_chunks = nullptr; c->d_in_offs = nullptr; c->cap_in = 0;
-			const uint32_t nc = std::max<uint32_t>(n, 256u);
-			MM_CUDA(c, cudaMalloc(&c->d_in_chunks, (size_t)nc * 4096));
-			MM_CUDA(c, cudaMalloc(&c->d_in_offs, (size_t)nc * 24));
-			c->cap_in = nc;
-		}
+		int rc0;
+		if ((rc0 = ensure_in_capacity(c, n))) return rc0;
 		if (!is_device_ptr(chunks)) {
 			MM_CUDA(c, cudaMemcpyAsync(c->d_in_chunks, chunks, (size_t)n * 4096, cudaMemcpyHostToDevice, c->stream));
 			dc = c->d_in_chunks;
@@ -583,6 +593,94 @@ static int small_batch_host(mm_ctx *c, const uint8_t *chunks, const int64_t *off
 	}
 }
 
+// The pipelined path.  A large host batch is PCIe-bound (per chunk 4 KiB go in, some 43 KiB of vertices
+// come back), so the batch is cut into pieces: all pieces are sent on one stream, each is meshed as soon as
+// it has arrived -- continuing the packed streams of the piece before it -- and its share of the vertex
+// streams starts its way back on a third stream while the next piece is meshed.  Both DMA directions and
+// the kernels overlap; the call costs little more than the device-to-host copy alone.  Inputs must be
+// page-locked (the caller stages pageable ones).  *done = false: the arenas are not sized yet or turned out
+// too small; the caller takes the plain path, which grows them.
+static int pipelined_batch_host(mm_ctx *c, const uint8_t *hc, const int64_t *ho, uint32_t n, mm_host_mesh *out, bool *done) {
+	*done = false;
+	if (!c->have_table) return fail(c, MM_ERR_NO_TABLE, "mm_set_block_table has not been called");
+	if (!c->cap_i && !c->cap_t) return MM_OK;
+	int rc;
+	if ((rc = ensure_in_capacity(c, n))) return rc;
+	if ((rc = ensure_chunk_capacity(c, n))) return rc;
+	const auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+	const size_t br = (size_t)n * 16;
+	const size_t oi = 0, ot = up(c->cap_i * mm::kQuadBytes), ori = up(ot + c->cap_t * mm::kQuadBytes), ort = ori + up(br);
+	if ((rc = ensure_pinned(c, &c->h_out, &c->h_out_bytes, ort + br + 256))) return rc;
+	if (!c->s_in) {
+		MM_CUDA(c, cudaStreamCreateWithFlags(&c->s_in, cudaStreamNonBlocking));
+		MM_CUDA(c, cudaStreamCreateWithFlags(&c->s_out, cudaStreamNonBlocking));
+		for (cudaEvent_t &e : c->ev_in) MM_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+	}
+	MM_CUDA(c, cudaStreamSynchronize(c->stream));  // earlier batches are done with the staging buffers and the arenas
+	const uint32_t piece = std::min<uint32_t>(mm::kMaxLaunchChunks, std::max<uint32_t>(512u, ((n + 7u) / 8u + 255u) & ~255u));
+	const uint32_t pieces = (n + piece - 1) / piece;
+	const uint32_t ahead = 8;  // pieces sent before their kernels are enqueued (one event each)
+	auto send = [&](uint32_t k) -> int {
+		const uint32_t first = k * piece, m = std::min(piece, n - first);
+		MM_CUDA(c, cudaMemcpyAsync(c->d_in_chunks + (size_t)first * 4096, hc + (size_t)first * 4096, (size_t)m * 4096, cudaMemcpyHostToDevice, c->s_in));
+		MM_CUDA(c, cudaMemcpyAsync(c->d_in_offs + (size_t)first * 3, ho + (size_t)first * 3, (size_t)m * 24, cudaMemcpyHostToDevice, c->s_in));
+		MM_CUDA(c, cudaEventRecord(c->ev_in[k % ahead], c->s_in));
+		return MM_OK;
+	};
+	for (uint32_t k = 0; k < std::min(pieces, ahead); k++)
+		if ((rc = send(k))) return rc;
+	c->pending = c->finished = false;
+	c->last_launches = 0;
+	const mm::u64 *carry = nullptr;
+	uint64_t pi = 0, pt = 0;  // quads already on their way back
+	bool fits = true;
+	for (uint32_t k = 0; k < pieces && fits; k++) {
+		const uint32_t first = k * piece, m = std::min(piece, n - first);
+		MM_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_in[k % ahead], 0));
+		const Targets tg{c->d_out_i, c->d_out_t, c->cap_i, c->cap_t, c->d_ranges_i + first, c->d_ranges_t + first};
+		if ((rc = launch(c, c->d_in_chunks + (size_t)first * 4096, c->d_in_offs + (size_t)first * 3, nullptr, m, false, tg, carry))) return rc;
+		carry = c->d_ticket + 2 + 2 * c->totals_slot;
+		MM_CUDA(c, cudaStreamSynchronize(c->stream));
+		if (k + ahead < pieces && (rc = send(k + ahead))) return rc;  // its event is free again
+		const uint64_t ti = c->h_totals[0], tt = c->h_totals[1];
+		if (ti > c->cap_i || tt > c->cap_t) {
+			fits = false;
+			break;
+		}
+		if (ti > pi) MM_CUDA(c, cudaMemcpyAsync(c->h_out + oi + pi * mm::kQuadBytes, c->d_out_i + pi * mm::kQuadBytes, (ti - pi) * mm::kQuadBytes, cudaMemcpyDeviceToHost, c->s_out));
+		if (tt > pt) MM_CUDA(c, cudaMemcpyAsync(c->h_out + ot + pt * mm::kQuadBytes, c->d_out_t + pt * mm::kQuadBytes, (tt - pt) * mm::kQuadBytes, cudaMemcpyDeviceToHost, c->s_out));
+		pi = ti;
+		pt = tt;
+	}
+	if (!fits) {  // the plain path grows the arenas and runs the whole batch again
+		MM_CUDA(c, cudaStreamSynchronize(c->s_in));
+		MM_CUDA(c, cudaStreamSynchronize(c->s_out));
+		return MM_OK;
+	}
+	MM_CUDA(c, cudaMemcpyAsync(c->h_out + ori, c->d_ranges_i, br, cudaMemcpyDeviceToHost, c->s_out));
+	MM_CUDA(c, cudaMemcpyAsync(c->h_out + ort, c->d_ranges_t, br, cudaMemcpyDeviceToHost, c->s_out));
+	MM_CUDA(c, cudaStreamSynchronize(c->s_out));
+	c->tot_i = pi;
+	c->tot_t = pt;
+	c->last_chunks = c->d_in_chunks;
+	c->last_offs = c->d_in_offs;
+	c->last_halo = nullptr;
+	c->last_n = n;
+	c->last_ms = 0.f;
+	c->last_timed = false;
+	c->finished = true;  // the device arenas hold this batch: mm_copy_out works
+	out->intransparent = (const mm_vertex *)(c->h_out + oi);
+	out->transparent = (const mm_vertex *)(c->h_out + ot);
+	out->ranges_i = (const mm_range *)(c->h_out + ori);
+	out->ranges_t = (const mm_range *)(c->h_out + ort);
+	out->n_intransparent = pi * 6;
+	out->n_transparent = pt * 6;
+	out->n_chunks = n;
+	out->reserved = 0;
+	*done = true;
+	return MM_OK;
+}
+
 int mm_mesh_batch_host(mm_ctx *c, const uint8_t *chunks, const int64_t *offs, uint32_t n, mm_host_mesh *out) {
 	if (!c || !out || (n && (!chunks || !offs))) return MM_ERR_INVALID;
 	if (use_device(c)) return MM_ERR_CUDA;
@@ -603,6 +701,11 @@ int mm_mesh_batch_host(mm_ctx *c, const uint8_t *chunks, const int64_t *offs, ui
 		memcpy(c->h_in + (size_t)n * 4096, offs, (size_t)n * 24);
 		hc = c->h_in;
 		ho = (const int64_t *)(c->h_in + (size_t)n * 4096);
+	}
+	if (c->pipe_min_chunks && n >= c->pipe_min_chunks) {
+		bool done = false;
+		if ((rc = pipelined_batch_host(c, hc, ho, n, out, &done))) return rc;
+		if (done) return MM_OK;
 	}
 	mm_batch_out bo;
 	if ((rc = mm_mesh_batch(c, hc, ho, nullptr, n, &bo))) return rc;

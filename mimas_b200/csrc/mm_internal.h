@@ -64,6 +64,10 @@ struct mm_ctx {
 	// host results (pinned)
 	unsigned char *h_out = nullptr;
 	size_t h_out_bytes = 0;
+	// pipelined host path (large batches): pieces go in on s_in, come back on s_out, kernels between on `stream`
+	cudaStream_t s_in = nullptr, s_out = nullptr;
+	cudaEvent_t ev_in[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+	uint32_t pipe_min_chunks = 1024;  // 0: off (MM_PIPE_MIN_CHUNKS)
 
 	// last batch
 	bool pending = false, finished = false;

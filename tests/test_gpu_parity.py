@@ -203,6 +203,30 @@ def test_batch_larger_than_one_launch(mesher, ocache):
     assert_batch_equal(mesher.mesh_batch(offs, chunks), oracle.mesh_batch(chunks, offs, ocache, threads=8))
 
 
+def test_pipelined_host_path_pieces_overflow_and_sizes(ocache):
+    """Host batches of >= 1024 chunks are cut into pieces whose copies and kernels overlap
+    (pipelined_batch_host); the bytes are those of the plain path, also when the arenas overflow
+    half-way (fall back, grow, run again) and for sizes that are no multiple of the piece."""
+    import mimas_b200
+    rng = np.random.RandomState(9)
+    tc, to = mimas_b200.gen_terrain_host(31, (-8, -8, -2), (16, 16, 5))
+    cc, co = checkerboard_chunks(600)
+    with mimas_b200.Mesher(0, product_cache(G)) as m:
+        # arenas sized by a small sparse batch first, then a dense one that overflows them in a later piece
+        sparse = np.zeros((1100, 4096), np.uint8)
+        sparse[:, 7] = 5
+        assert_batch_equal(m.mesh_batch(to[:1100], sparse), oracle.mesh_batch(sparse, to[:1100], ocache, threads=8))
+        chunks = np.concatenate([sparse[:900], cc, tc[:777]])
+        offs = np.concatenate([to[:900], co, to[:777]])
+        want = oracle.mesh_batch(chunks, offs, ocache, threads=8)
+        assert_batch_equal(m.mesh_batch(offs, chunks), want)   # overflow -> plain path
+        assert_batch_equal(m.mesh_batch(offs, chunks), want)   # now pipelined
+        for n in (1024, 1025, 1537, 2277):
+            sel = rng.choice(len(chunks), n, replace=n > len(chunks))
+            assert_batch_equal(m.mesh_batch(offs[sel], chunks[sel]),
+                               oracle.mesh_batch(chunks[sel], offs[sel], ocache, threads=8))
+
+
 def test_push_block_matches_oracle(mesher):
     """push_block (lib.rs:183-219) for every blocked-face combination."""
     from mimas_b200.meshgen import BlockTextureIds
