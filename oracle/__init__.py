@@ -225,3 +225,30 @@ def frustum_planes(vmatrix, pmatrix) -> np.ndarray:
     p = np.ascontiguousarray(pmatrix, dtype=np.float32).reshape(-1)
     _render().ro_frustum(v.ctypes.data_as(C.c_void_p), p.ctypes.data_as(C.c_void_p), pl.ctypes.data_as(C.c_void_p))
     return pl
+
+
+# ---- raster oracle (oracle/raster_oracle.c): clipping, rasterisation, depth test, fragment shader --------
+class RaFrame(C.Structure):
+    _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("fog_near", C.c_float), ("fog_far", C.c_float),
+                ("clear", C.c_float * 4)]
+
+
+CLEAR_COLOR = (0.05, 0.01, 0.6, 0.0)  # client.rs:675
+
+
+def raster_frame(shaded, width, height, fog_near, fog_far, tex, clear=CLEAR_COLOR, want_keys=False):
+    """shaded: SHADED_DTYPE triangle list; tex: [layers, size, size, 4] float32.  Returns the image as
+    uint32 [height, width] (R | G<<8 | B<<16 | A<<24, row 0 at the bottom) and optionally the
+    depth24 << 32 | colour keys."""
+    shaded = np.ascontiguousarray(shaded, dtype=SHADED_DTYPE)
+    tex = np.ascontiguousarray(tex, dtype=np.float32)
+    assert tex.ndim == 4 and tex.shape[1] == tex.shape[2] and tex.shape[3] == 4
+    f = RaFrame(width, height, fog_near, fog_far)
+    f.clear[:] = [float(c) for c in clear]
+    img = np.zeros((height, width), dtype=np.uint32)
+    keys = np.zeros((height, width), dtype=np.uint64)
+    rc = _render().ra_raster_frame(shaded.ctypes.data_as(C.c_void_p), C.c_uint64(len(shaded)), C.byref(f),
+                                   tex.ctypes.data_as(C.c_void_p), C.c_uint32(tex.shape[0]), C.c_uint32(tex.shape[1]),
+                                   img.ctypes.data_as(C.c_void_p), keys.ctypes.data_as(C.c_void_p))
+    assert rc == 0
+    return (img, keys) if want_keys else img
