@@ -254,6 +254,25 @@ int mm_cull_chunks(mm_ctx *ctx, const int64_t *offs, uint32_t n, const mm_camera
  * visible ones.  Results stay in library-owned device memory until the next call. */
 int mm_draw_batch(mm_ctx *ctx, const mm_camera *cam, mm_draw_out *out);
 
+/* What GL does with the shaded vertices, headless: primitive assembly, clipping, back-face culling
+ * (CullCounterClockwise), rasterisation, depth test IfLess and the fragment shader
+ * (mimas-client/fragment-shader.glsl:14-24) under the draw state of mimas-client/client.rs:661-675, into an
+ * RGBA8 image.  Parity to the reference is unpinned (GL leaves the rasterisation rules to the driver); the
+ * kernels are bit-exact to oracle/raster_oracle.c, which states the rules chosen and the simplifications
+ * (nearest texel at level 0, no sRGB conversion, no blending of surviving fragments). */
+typedef struct mm_frame {
+	uint32_t width, height;    /* 1..8192 */
+	float fog_near, fog_far;   /* uniform fog_near_far, client.rs:618; fog_near > 0 */
+	float clear[4];            /* (0.05, 0.01, 0.6, 0.0), client.rs:675 */
+} mm_frame;
+/* The texture array (mimas-client/assets.rs:194-211): `layers` square images of size x size float RGBA texels,
+ * layer = TextureId, row 0 at v = 0.  Host memory; copied. */
+int mm_set_textures(mm_ctx *ctx, const float *rgba, uint32_t layers, uint32_t size);
+/* n_vertices (a triangle list, device memory, e.g. mm_draw_out.d_shaded) -> d_image[height][width], packed
+ * R | G << 8 | B << 16 | A << 24, row 0 at the bottom as in GL (device memory).  Synchronous. */
+int mm_raster_frame(mm_ctx *ctx, const mm_shaded_vertex *d_verts, uint64_t n_vertices, const mm_frame *frame,
+                    uint32_t *d_image, float *kernel_ms);
+
 /* Development aid, no reference counterpart: device timeline (%globaltimer, ns) of the launch pairs since
  * the previous call, as a ring of `pairs` records of 8 words: analyse {first CTA start, -, last CTA out of
  * work, last CTA end}, expand {first CTA start, first CTA past its dependency wait, -, last CTA end}.

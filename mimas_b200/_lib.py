@@ -22,7 +22,7 @@ SYMBOLS = (
     "mm_gen_terrain_host", "mm_gen_terrain_device", "mm_dev_alloc", "mm_dev_free", "mm_dev_upload",
     "mm_dev_download", "mm_ctx_sync", "mm_device_info", "mm_host_alloc", "mm_host_free", "mm_launch_count",
     "mm_debug_trace", "mm_vertex_stage", "mm_cull_chunks", "mm_draw_batch", "mm_mesh_batch_halo_async",
-    "mm_gather_halos",
+    "mm_gather_halos", "mm_set_textures", "mm_raster_frame",
 )
 
 
@@ -57,6 +57,8 @@ def lib() -> C.CDLL:
     l.mm_mesh_batch_async.argtypes = [vp, vp, vp, u32]
     l.mm_mesh_batch_halo_async.argtypes = [vp, vp, vp, vp, u32]
     l.mm_gather_halos.argtypes = [vp, vp, u32, u32, u32, C.c_uint8, vp]
+    l.mm_set_textures.argtypes = [vp, vp, u32, u32]
+    l.mm_raster_frame.argtypes = [vp, vp, u64, vp, vp, vp]
     l.mm_batch_finish.argtypes = [vp, vp]
     l.mm_copy_out.argtypes = [vp, vp, vp, vp, vp]
     l.mm_mesh_batch_host.argtypes = [vp, vp, vp, u32, vp]

@@ -291,6 +291,7 @@ int mm_ctx_destroy(mm_ctx *c) {
 	if (c->h_small) cudaFreeHost(c->h_small);
 	if (c->h_draw_totals) cudaFreeHost(c->h_draw_totals);
 	cudaFree(c->d_cull); cudaFree(c->d_shaded);
+	cudaFree(c->d_tex); cudaFree(c->d_fb); cudaFree(c->d_big); cudaFree(c->d_big_count);
 	if (c->ev2) cudaEventDestroy(c->ev2);
 	if (c->ev3) cudaEventDestroy(c->ev3);
 	if (c->h_out) cudaFreeHost(c->h_out);

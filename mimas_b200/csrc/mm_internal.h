@@ -86,6 +86,12 @@ struct mm_ctx {
 	unsigned char *d_shaded = nullptr;
 	size_t shaded_bytes = 0;
 	cudaEvent_t ev2 = nullptr, ev3 = nullptr;
+	// software rasteriser (mm_raster.cu): texture array, 64-bit key frame buffer, queue of large triangles
+	float *d_tex = nullptr;
+	uint32_t tex_layers = 0, tex_size = 0;
+	unsigned char *d_fb = nullptr;
+	size_t fb_pixels = 0;
+	unsigned char *d_big = nullptr, *d_big_count = nullptr;
 	unsigned long long *h_draw_totals = nullptr, *d_h_draw_totals = nullptr;  // mapped pinned: drawn chunks, vertices i, t
 
 	char err[512] = {0};

@@ -314,8 +314,10 @@ int ensure_draw_totals(mm_ctx *c) {
 	if (c->h_draw_totals) return MM_OK;
 	MM_CUDA(c, cudaHostAlloc(&c->h_draw_totals, 4 * sizeof(unsigned long long), cudaHostAllocMapped));
 	MM_CUDA(c, cudaHostGetDevicePointer((void **)&c->d_h_draw_totals, c->h_draw_totals, 0));
-	MM_CUDA(c, cudaEventCreate(&c->ev2));
-	MM_CUDA(c, cudaEventCreate(&c->ev3));
+	if (!c->ev2) {  // mm_raster_frame may have made them already
+		MM_CUDA(c, cudaEventCreate(&c->ev2));
+		MM_CUDA(c, cudaEventCreate(&c->ev3));
+	}
 	return MM_OK;
 }
 }  // namespace

@@ -405,6 +405,37 @@ class Mesher:
         self._ck(self._lib.mm_draw_batch(self._ctx, C.byref(cc), C.byref(out)))
         return out
 
+    # -- headless rasteriser + fragment shader (csrc/mm_raster.cu) ---------------------------------------
+    def set_textures(self, tex):
+        """The texture array (assets.rs:194-211): [layers, size, size, 4] float32, layer = TextureId."""
+        tex = np.ascontiguousarray(tex, dtype=np.float32)
+        if tex.ndim != 4 or tex.shape[1] != tex.shape[2] or tex.shape[3] != 4:
+            raise ValueError("textures must be [layers, size, size, 4]")
+        self._ck(self._lib.mm_set_textures(self._ctx, tex.ctypes.data, tex.shape[0], tex.shape[1]))
+
+    def raster_frame(self, d_verts: int, n_vertices: int, width: int, height: int, fog_near: float = 40.0,
+                     fog_far: float = 60.0, clear=(0.05, 0.01, 0.6, 0.0), want_ms: bool = False):
+        """Shaded triangle list in device memory -> uint32 [height, width] image (R | G<<8 | B<<16 | A<<24,
+        row 0 at the bottom as in GL): clipping, culling, rasterisation, depth test, fragment-shader.glsl."""
+        from .render import CFrame
+        f = CFrame(width, height, fog_near, fog_far)
+        f.clear[:] = [float(c) for c in clear]
+        d_img = self.dev_alloc(4 * width * height)
+        try:
+            ms = C.c_float()
+            self._ck(self._lib.mm_raster_frame(self._ctx, C.c_void_p(d_verts), C.c_uint64(n_vertices), C.byref(f),
+                                               C.c_void_p(d_img), C.byref(ms)))
+            img = self.download(d_img, 4 * width * height).view(np.uint32).reshape(height, width).copy()
+        finally:
+            self.dev_free(d_img)
+        return (img, ms.value) if want_ms else img
+
+    def render_frame(self, cam, width: int, height: int, fog_near: float = 40.0, fog_far: float = 60.0, want_ms=False):
+        """A whole headless frame over the last finished device batch: cull, vertex shader, rasterise."""
+        d = self.draw_batch(cam)
+        return self.raster_frame(d.d_shaded or 0, int(d.n_shaded_i + d.n_shaded_t), width, height, fog_near, fog_far,
+                                 want_ms=want_ms)
+
     def debug_trace(self, pairs: int) -> np.ndarray:
         """Device timeline (ns) of the launch pairs since the previous call, shape (k, 2, 4): see
         mm_debug_trace in the header.  Re-arms the ring with `pairs` records (0 = off)."""

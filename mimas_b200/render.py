@@ -25,6 +25,42 @@ class DrawOut(C.Structure):
                 ("kernel_ms", C.c_float), ("reserved", C.c_uint32)]
 
 
+class CFrame(C.Structure):  # mm_frame
+    _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("fog_near", C.c_float), ("fog_far", C.c_float),
+                ("clear", C.c_float * 4)]
+
+
+def synthetic_textures(layers: int, size: int = 16, seed: int = 7, crossed=()) -> np.ndarray:
+    """A stand-in texture array [layers, size, size, 4] (the game's PNGs are not shipped here): per layer a
+    base colour with per-texel variation; layers in `crossed` get alpha holes like the plant textures
+    (fragment-shader.glsl:16-18 discards alpha < 0.5)."""
+    rng = np.random.RandomState(seed)
+    base = rng.rand(layers, 1, 1, 3).astype(np.float32) * 0.7 + 0.2
+    var = (rng.rand(layers, size, size, 1).astype(np.float32) - 0.5) * 0.25
+    tex = np.ones((layers, size, size, 4), dtype=np.float32)
+    tex[..., :3] = np.clip(base + var, 0.0, 1.0)
+    for l in crossed:
+        if l < layers:
+            tex[l, :, :, 3] = (rng.rand(size, size) < 0.45).astype(np.float32)
+    return tex
+
+
+def write_png(path: str, img: np.ndarray):
+    """uint32 [height, width] image from raster_frame (row 0 at the bottom) -> 8-bit RGB PNG, top row first
+    (stdlib only: zlib + the three mandatory chunks)."""
+    import struct
+    import zlib
+    rgb = np.stack([(img >> s) & 0xFF for s in (0, 8, 16)], axis=-1).astype(np.uint8)[::-1]
+    h, w = img.shape
+    raw = np.concatenate([np.zeros((h, 1), np.uint8), rgb.reshape(h, w * 3)], axis=1).tobytes()  # filter byte 0 per row
+
+    def chunk(tag, data):
+        return struct.pack(">I", len(data)) + tag + data + struct.pack(">I", zlib.crc32(tag + data) & 0xFFFFFFFF)
+    with open(path, "wb") as f:
+        f.write(b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, 8, 2, 0, 0, 0))
+                + chunk(b"IDAT", zlib.compress(raw, 6)) + chunk(b"IEND", b""))
+
+
 def _f32(x):
     return np.float32(x)
 

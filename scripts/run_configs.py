@@ -303,11 +303,46 @@ def cfg_halo(m, stream):
             "gather_ms": t_gather * 1e3, "gather_equals_numpy": bool(gather_ok), **res}
 
 
+def cfg_frame(m, stream):
+    """SURVEY.md 8f rank 3, optional part: whole headless frames (cull + vertex shader + rasteriser + fragment
+    shader) over the radius-32 region at 1920x1080, synthetic textures; one frame is written as a PNG."""
+    from mimas_b200.render import Camera, synthetic_textures, write_png
+    r = 32
+    dims = (2 * r + 1, 2 * r + 1, 5)
+    n = dims[0] * dims[1] * dims[2]
+    dc, do = m.dev_alloc(n * 4096), m.dev_alloc(n * 24)
+    m.gen_terrain_device(78, (-r, -r, -2), dims, dc, do)
+    m.mesh_batch_device(dc, do, n)
+    m.set_textures(synthetic_textures(80, crossed=range(30, 44)))
+    W, H = 1920, 1080
+    frames = []
+    for k, cam in enumerate((Camera(pos=(8.0, 8.0, 24.0), pitch=10.0, yaw=30.0, viewing_range=128.0, aspect_ratio=W / H),
+                             Camera(pos=(8.0, 8.0, 40.0), pitch=35.0, yaw=-100.0, viewing_range=512.0, aspect_ratio=W / H),
+                             Camera(pos=(-200.0, 150.0, 60.0), pitch=30.0, yaw=20.0, viewing_range=1e6, aspect_ratio=W / H))):
+        d = m.draw_batch(cam)
+        nv = int(d.n_shaded_i + d.n_shaded_t)
+        img, _ = m.raster_frame(d.d_shaded or 0, nv, W, H, 40.0, 60.0 if k else 1e9, want_ms=True)
+        ms = [m.raster_frame(d.d_shaded or 0, nv, W, H, 40.0, 60.0, want_ms=True)[1] for _ in range(5)]
+        dms = [m.draw_batch(cam).kernel_ms for _ in range(5)]
+        drawn = float(((img >> 24) & 0xFF > 0).mean())
+        frames.append({"viewing_range": cam.viewing_range, "drawn_chunks": int(d.n_drawn), "triangles": nv // 3,
+                       "cull_and_vertex_ms": float(np.median(dms)), "raster_ms": float(np.median(ms)),
+                       "covered_fraction": drawn})
+        if k == 0:
+            os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+            write_png(os.path.join(ROOT, "gpurun_out", "frame.png"), img[::2, ::2])
+    # parity of one small frame against the oracle chain is tests/test_raster.py; here only a checksum of self-consistency
+    m.dev_free(dc)
+    m.dev_free(do)
+    return {"config": "headless frames 1920x1080 over the radius-32 region (21125 terrain chunks), synthetic textures",
+            "frames": frames}
+
+
 def main():
-    which = [a for a in sys.argv[1:] if a.startswith("cfg")] or ["cfg1", "cfg3", "cfg4", "cfg5", "cfg_draw", "cfg_halo"]
+    which = [a for a in sys.argv[1:] if a.startswith("cfg")] or ["cfg1", "cfg3", "cfg4", "cfg5", "cfg_draw", "cfg_halo", "cfg_frame"]
     m = mimas_b200.Mesher(0, mimas_b200.default_cache())
     stream = torch.cuda.Stream()
-    fns = {"cfg1": cfg1, "cfg3": cfg3, "cfg4": cfg4, "cfg5": cfg5, "cfg_draw": cfg_draw, "cfg_halo": cfg_halo}
+    fns = {"cfg1": cfg1, "cfg3": cfg3, "cfg4": cfg4, "cfg5": cfg5, "cfg_draw": cfg_draw, "cfg_halo": cfg_halo, "cfg_frame": cfg_frame}
     for w in which:
         t0 = time.time()
         r = fns[w](m, stream)

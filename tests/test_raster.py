@@ -1,6 +1,7 @@
 """The raster oracle (oracle/raster_oracle.c: clipping, rasterisation, depth test, fragment-shader.glsl:14-24)
-against hand-derived cases and an independent numpy ray cast.  CPU only; the CUDA kernels are compared with
-the same oracle in tests/test_render_gpu.py."""
+against hand-derived cases and an independent numpy ray cast (CPU), and the CUDA rasteriser
+(csrc/mm_raster.cu) against that oracle, bit for bit (-m gpu).  Parity to the reference's GL output is
+unpinned: see the oracle's header."""
 import numpy as np
 
 import oracle
@@ -138,3 +139,104 @@ def test_perspective_ground_plane_against_ray_cast():
             checked += 1
     # float32 interpolation vs the float64 ray: near the horizon a texel is a small fraction of a pixel
     assert checked > 3000 and bad <= 3, (checked, bad)
+
+
+# ---- GPU: the CUDA rasteriser (csrc/mm_raster.cu) is bit-exact with the oracle -------------------------------
+import pytest  # noqa: E402
+
+
+@pytest.fixture(scope="module")
+def mesher():
+    import mimas_b200
+    from tests.util import load_golden, product_cache
+    m = mimas_b200.Mesher(0, product_cache(load_golden()))
+    yield m
+    m.close()
+
+
+def gpu_raster(m, shaded, w, h, fog_near, fog_far, tex):
+    m.set_textures(tex)
+    shaded = np.ascontiguousarray(shaded, dtype=oracle.SHADED_DTYPE)
+    d = m.dev_alloc(max(48 * len(shaded), 48))
+    try:
+        if len(shaded):
+            m.upload(d, shaded.view(np.uint8))
+        return m.raster_frame(d, len(shaded), w, h, fog_near, fog_far)
+    finally:
+        m.dev_free(d)
+
+
+@pytest.mark.gpu
+def test_gpu_hand_cases_equal_oracle(mesher):
+    tex = flat_tex((1, 0, 0, 1), (0, 1, 0, 1), (0, 0, 1, 0.4))
+    scenes = [make_shaded(np.zeros((0, 3, 4))),
+              make_shaded(cw_quad(-1, -1, 1, 1), lamb=0.8),
+              np.concatenate([make_shaded(cw_quad(-1, -1, 0, 1, z=-0.5), layer=0), make_shaded(cw_quad(-1, -1, 1, 1, z=0.5), layer=1),
+                              make_shaded(cw_quad(-1, -1, 1, 1, z=-0.9), layer=2)]),
+              make_shaded(cw_quad(-1, -1, 1, 1), layer=1, vpos=[(0, 0, -70, 1)] * 6)]
+    for s in scenes:
+        for (w, h) in ((8, 4), (64, 48), (333, 17)):
+            want = oracle.raster_frame(s, w, h, 40.0, 60.0, tex)
+            got = gpu_raster(mesher, s, w, h, 40.0, 60.0, tex)
+            assert (got == want).all()
+
+
+@pytest.mark.gpu
+def test_gpu_random_triangles_equal_oracle(mesher):
+    """Random clip-space triangles of every kind: behind the camera, crossing the near / far / guard-band planes,
+    sub-pixel, screen-filling, degenerate, with random attributes and alpha holes."""
+    rng = np.random.RandomState(5)
+    n = 4000
+    tris = rng.randn(n, 3, 4).astype(np.float32)
+    tris[:, :, 3] = np.abs(tris[:, :, 3]) + 0.05
+    tris[: n // 4, :, 3] = rng.randn(n // 4, 3) * 0.7                 # w of either sign: near-plane clipping
+    tris[n // 4: n // 2] *= rng.rand(n // 4, 1, 1).astype(np.float32) * 30  # huge: guard band, queue of big triangles
+    small = slice(n // 2, 3 * n // 4)
+    tris[small, 1:, :2] = tris[small, :1, :2] + rng.randn(n // 4, 2, 2).astype(np.float32) * 0.01  # tiny
+    tris[-50:, 2] = tris[-50:, 1]                                                                  # degenerate
+    s = make_shaded(tris)
+    s["vlamb"] = rng.rand(3 * n) * 1.4
+    s["vtex_pos"] = rng.randn(3 * n, 2) * 3
+    s["vtex_ind"] = rng.randint(0, 9, 3 * n)                                                        # beyond the last layer too
+    s["vposition"] = rng.randn(3 * n, 4) * 30
+    tex = rng.rand(6, 16, 16, 4).astype(np.float32)
+    tex[..., 3] = (rng.rand(6, 16, 16) < 0.8)
+    for (w, h, fn, ff) in ((160, 90, 40.0, 60.0), (97, 131, 5.0, 10.0)):
+        want = oracle.raster_frame(s, w, h, fn, ff, tex)
+        got = gpu_raster(mesher, s, w, h, fn, ff, tex)
+        bad = np.argwhere(got != want)
+        assert len(bad) == 0, (len(bad), bad[:5], got[tuple(bad[0])], want[tuple(bad[0])])
+
+
+@pytest.mark.gpu
+def test_gpu_frame_of_a_meshed_region_equals_oracle(mesher):
+    """The whole headless frame: mesh a terrain region, cull + vertex-shade on the device, rasterise; against the
+    oracle chain (CPU mesher -> culling -> vertex stage -> raster oracle) fed with the same camera."""
+    import mimas_b200
+    from mimas_b200.render import synthetic_textures
+    from tests.util import load_golden, oracle_cache
+    chunks, offs = mimas_b200.gen_terrain_host(78, (-3, -3, -1), (6, 6, 3))
+    tex = synthetic_textures(80, crossed=range(30, 44))
+    mesher.set_textures(tex)
+    n = len(chunks)
+    d_c, d_o = mesher.dev_alloc(n * 4096), mesher.dev_alloc(n * 24)
+    try:
+        mesher.upload(d_c, chunks)
+        mesher.upload(d_o, offs)
+        mesher.mesh_batch_device(d_c, d_o, n)
+        oc = oracle_cache(load_golden())
+        want_mesh = oracle.mesh_batch(chunks, offs, oc, threads=8)
+        for cam in (Camera(pos=(5.0, 3.0, 30.0), pitch=40.0, yaw=30.0, viewing_range=200.0),
+                    Camera(pos=(-20.0, 10.0, 22.0), pitch=10.0, yaw=-60.0, viewing_range=60.0)):
+            got = mesher.render_frame(cam, 200, 150, 40.0, 60.0)
+            vis = oracle.cull_chunks(offs, cam.get_matrix(), cam.get_perspective(), cam.pos, cam.viewing_range)
+            parts = [want_mesh["intransparent"][want_mesh["first_i"][c]:want_mesh["first_i"][c] + want_mesh["count_i"][c]] for c in vis]
+            parts += [want_mesh["transparent"][want_mesh["first_t"][c]:want_mesh["first_t"][c] + want_mesh["count_t"][c]] for c in vis]
+            verts = np.concatenate(parts) if parts else np.zeros(0, oracle.VERTEX_DTYPE)
+            shaded = oracle.vertex_stage(verts, cam.get_matrix(), cam.get_perspective())
+            want = oracle.raster_frame(shaded, 200, 150, 40.0, 60.0, tex)
+            assert (got == want).all(), int((got != want).sum())
+            assert (unpack(got)[..., 3] > 0).mean() > 0.2   # the frame is not empty
+    finally:
+        mesher.dev_free(d_c)
+        mesher.dev_free(d_o)
