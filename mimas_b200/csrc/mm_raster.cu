@@ -13,8 +13,9 @@
 // Shape: the frame buffer is one 64-bit key per pixel, depth24 << 32 | RGBA8; a fragment is one atomicMin
 // (depth test IfLess + colour write in one step, independent of the order triangles arrive in).
 //   raster_tris_kernel  one thread per triangle: clip, set up, and rasterise it if its bounding box is small;
-//                       larger ones go to a queue
-//   raster_big_kernel   one CTA per queued triangle, threads stride over its bounding box
+//                       larger ones go to a list, cut into 64 x 64 pixel tiles (tiles wholly outside one
+//                       edge are dropped), one queue entry per tile
+//   raster_big_kernel   one CTA per queued (triangle, tile), threads stride over the tile's share of the box
 //   resolve_kernel      keys -> RGBA8 image (clear colour where nothing was drawn)
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -31,7 +32,10 @@ constexpr int kNAttr = 7;          // vlamb, u, v, vposition.xyzw
 constexpr float kGuard = 16.0f;    // guard band: clip x, y at +-kGuard * w
 constexpr int kMaxPoly = 12;
 constexpr int kSmallBox = 64;      // bounding boxes up to this many pixels are rasterised by the triangle's own thread
-constexpr uint32_t kBigCap = 1u << 18;
+constexpr uint32_t kBigCap = 1u << 19;   // listed triangles
+constexpr uint32_t kTileCap = 1u << 22;  // queued (triangle, tile) pairs
+constexpr int kTileShift = 6;            // 64 x 64 pixels
+constexpr uint32_t kNoTri = 0xffffffffu;
 constexpr int kTriThreads = 128;
 constexpr int kBigThreads = 128;
 
@@ -59,7 +63,8 @@ struct RasterParams {
 	uint32_t layers, ts;
 	unsigned long long *fb;
 	BigTri *big;
-	uint32_t *big_count;
+	uint2 *tiles;         // x = slot in big (kNoTri: empty entry), y = tile x | tile y << 16
+	uint32_t *big_count;  // [0] triangles listed, [1] tile entries queued
 };
 
 __device__ __forceinline__ float plane_dist(const ClipV &v, int p) {
@@ -145,25 +150,28 @@ __device__ __forceinline__ bool fragment(const float *at, uint32_t layer, const 
 
 struct Edges {  // per triangle constants of the inner loop
 	bool oa, ob, oc;
-	float fa;
+	float rfa;  // 1 / (twice the area)
 };
 
-// one pixel of the triangle a, b, c (positive area)
+// one pixel of the triangle a, b, c (positive area); COVERED: the caller knows the pixel is inside
+template <bool COVERED>
 __device__ __forceinline__ void pixel(const ScreenV &a, const ScreenV &b, const ScreenV &c, const Edges &e, uint32_t layer,
                                       int32_t x, int32_t y, const RasterParams &p) {
 	const int32_t px = x * 256 + 128, py = y * 256 + 128;
 	const long long wa = edge(b, c, px, py), wb = edge(c, a, px, py), wc = edge(a, b, px, py);
-	if (wa < 0 || wb < 0 || wc < 0) return;
-	if ((wa == 0 && !e.oa) || (wb == 0 && !e.ob) || (wc == 0 && !e.oc)) return;
-	const float la = (float)wa / e.fa, lb = (float)wb / e.fa, lc = (float)wc / e.fa;
+	if (!COVERED) {
+		if (wa < 0 || wb < 0 || wc < 0) return;
+		if ((wa == 0 && !e.oa) || (wb == 0 && !e.ob) || (wc == 0 && !e.oc)) return;
+	}
+	const float la = (float)wa * e.rfa, lb = (float)wb * e.rfa, lc = (float)wc * e.rfa;
 	const float depth = la * a.z + lb * b.z + lc * c.z;
 	const uint32_t d24 = (uint32_t)(clamp01(depth) * 16777215.0f + 0.5f);
 	if (d24 >= 0xFFFFFFu) return;  // IfLess against the cleared 1.0
 	const float qa = la * a.invw, qb = lb * b.invw, qc = lc * c.invw;
-	const float qs = qa + qb + qc;
+	const float rq = 1.0f / (qa + qb + qc);
 	float at[kNAttr];
 #pragma unroll
-	for (int k = 0; k < kNAttr; k++) at[k] = (qa * a.a[k] + qb * b.a[k] + qc * c.a[k]) / qs;
+	for (int k = 0; k < kNAttr; k++) at[k] = (qa * a.a[k] + qb * b.a[k] + qc * c.a[k]) * rq;
 	uint32_t rgba;
 	if (!fragment(at, layer, p, rgba)) return;
 	atomicMin(p.fb + (size_t)y * p.width + x, ((unsigned long long)d24 << 32) | rgba);
@@ -172,6 +180,27 @@ __device__ __forceinline__ void pixel(const ScreenV &a, const ScreenV &b, const 
 struct Box {
 	int32_t x0, x1, y0, y1;
 };
+
+__device__ __forceinline__ long long floor_div(long long n, long long d) {  // d > 0
+	const long long q = n / d;
+	return (n % d != 0 && n < 0) ? q - 1 : q;
+}
+// The pixels x of row y with edge(u, w, centre) >= 0 (> 0 unless `owns`), intersected with [x0, x1]: the same
+// integers the per-pixel test accepts, solved for x.  edge = C - dy * 256 * x with C as below.
+__device__ __forceinline__ void clip_span(const ScreenV &u, const ScreenV &w, bool owns, int32_t y, int32_t &x0, int32_t &x1) {
+	const long long dx = w.X - u.X, dy = w.Y - u.Y;
+	const long long C = dx * (long long)(y * 256 + 128 - u.Y) - dy * (long long)(128 - u.X);
+	const long long slack = owns ? 0 : 1;
+	if (dy > 0) {          // dy * 256 * x <= C - slack
+		const long long hi = floor_div(C - slack, dy * 256);
+		if (hi < x1) x1 = (int32_t)max(hi, (long long)x0 - 1);
+	} else if (dy < 0) {   // -dy * 256 * x >= slack - C
+		const long long lo = -floor_div(C - slack, -dy * 256);  // ceil((slack - C) / (-dy * 256))
+		if (lo > x0) x0 = (int32_t)min(lo, (long long)x1 + 1);
+	} else if (C - slack < 0) {
+		x1 = x0 - 1;
+	}
+}
 __device__ __forceinline__ Box bbox(const ScreenV &a, const ScreenV &b, const ScreenV &c, uint32_t width, uint32_t height) {
 	const int32_t minX = min(a.X, min(b.X, c.X)), maxX = max(a.X, max(b.X, c.X));
 	const int32_t minY = min(a.Y, min(b.Y, c.Y)), maxY = max(a.Y, max(b.Y, c.Y));
@@ -191,20 +220,38 @@ __device__ void emit_triangle(const ScreenV &p0, const ScreenV &p1, const Screen
 	const Box bx = bbox(a, b, c, p.width, p.height);
 	if (bx.x1 < bx.x0 || bx.y1 < bx.y0) return;
 	const long long npx = (long long)(bx.x1 - bx.x0 + 1) * (bx.y1 - bx.y0 + 1);
+	Edges e;
+	e.oa = owns_edge(b, c); e.ob = owns_edge(c, a); e.oc = owns_edge(a, b);
+	e.rfa = 1.0f / (float)(-area);
 	if (npx > kSmallBox) {
+		const int32_t tx0 = bx.x0 >> kTileShift, tx1 = bx.x1 >> kTileShift, ty0 = bx.y0 >> kTileShift, ty1 = bx.y1 >> kTileShift;
+		const uint32_t ntiles = (uint32_t)(tx1 - tx0 + 1) * (uint32_t)(ty1 - ty0 + 1);
 		const uint32_t slot = atomicAdd(p.big_count, 1u);
-		if (slot < kBigCap) {
+		const uint32_t base = slot < kBigCap ? atomicAdd(p.big_count + 1, ntiles) : kTileCap;
+		if (base < kTileCap && ntiles <= kTileCap - base) {
 			BigTri &t = p.big[slot];
 			t.v[0] = a; t.v[1] = b; t.v[2] = c;
 			t.layer = layer;
+			uint32_t k = base;
+			for (int32_t ty = ty0; ty <= ty1; ty++)
+				for (int32_t tx = tx0; tx <= tx1; tx++, k++) {
+					// the pixel centres of the tile span [lo, hi]; wholly outside one edge -> nothing to draw there
+					const int32_t lx = (tx << kTileShift) * 256 + 128, hx = lx + ((1 << kTileShift) - 1) * 256;
+					const int32_t ly = (ty << kTileShift) * 256 + 128, hy = ly + ((1 << kTileShift) - 1) * 256;
+					bool keep = true;
+#pragma unroll
+					for (int q = 0; q < 3; q++) {
+						const ScreenV &u = q == 0 ? b : q == 1 ? c : a, &w = q == 0 ? c : q == 1 ? a : b;
+						const long long e0 = edge(u, w, lx, ly), e1 = edge(u, w, hx, ly), e2 = edge(u, w, lx, hy), e3 = edge(u, w, hx, hy);
+						keep = keep && !(e0 < 0 && e1 < 0 && e2 < 0 && e3 < 0);
+					}
+					p.tiles[k] = make_uint2(keep ? slot : kNoTri, (uint32_t)tx | ((uint32_t)ty << 16));
+				}
 			return;
-		}  // queue full: this thread does the work itself
+		}  // lists full: this thread does the work itself
 	}
-	Edges e;
-	e.oa = owns_edge(b, c); e.ob = owns_edge(c, a); e.oc = owns_edge(a, b);
-	e.fa = (float)(-area);
 	for (int32_t y = bx.y0; y <= bx.y1; y++)
-		for (int32_t x = bx.x0; x <= bx.x1; x++) pixel(a, b, c, e, layer, x, y, p);
+		for (int32_t x = bx.x0; x <= bx.x1; x++) pixel<false>(a, b, c, e, layer, x, y, p);
 }
 
 __global__ void __launch_bounds__(kTriThreads) raster_tris_kernel(const RasterParams p) {
@@ -249,27 +296,62 @@ __global__ void __launch_bounds__(kTriThreads) raster_tris_kernel(const RasterPa
 
 __global__ void __launch_bounds__(kBigThreads) raster_big_kernel(const RasterParams p) {
 	__shared__ BigTri t;
-	const uint32_t n = min(*p.big_count, kBigCap);
+	constexpr int kRows = 1 << kTileShift;
+	__shared__ int32_t span_x0[kRows];
+	__shared__ uint32_t incl[kRows];  // covered pixels of rows 0..r (rows 0..31) resp. 32..r (rows 32..63)
+	const uint32_t n = min(p.big_count[1], kTileCap);
 	for (uint32_t i = blockIdx.x; i < n; i += gridDim.x) {
+		const uint2 ent = __ldg(p.tiles + i);
+		if (ent.x == kNoTri) continue;
 		__syncthreads();
-		if (threadIdx.x < sizeof(BigTri) / 4) reinterpret_cast<uint32_t *>(&t)[threadIdx.x] = reinterpret_cast<const uint32_t *>(p.big + i)[threadIdx.x];
+		if (threadIdx.x < sizeof(BigTri) / 4) reinterpret_cast<uint32_t *>(&t)[threadIdx.x] = reinterpret_cast<const uint32_t *>(p.big + ent.x)[threadIdx.x];
 		__syncthreads();
 		const ScreenV &a = t.v[0], &b = t.v[1], &c = t.v[2];
-		const Box bx = bbox(a, b, c, p.width, p.height);
+		Box bx = bbox(a, b, c, p.width, p.height);
+		const int32_t tx = (int32_t)(ent.y & 0xffffu) << kTileShift, ty = (int32_t)(ent.y >> 16) << kTileShift;
+		bx.x0 = max(bx.x0, tx); bx.x1 = min(bx.x1, tx + (1 << kTileShift) - 1);
+		bx.y0 = max(bx.y0, ty); bx.y1 = min(bx.y1, ty + (1 << kTileShift) - 1);
 		Edges e;
 		e.oa = owns_edge(b, c); e.ob = owns_edge(c, a); e.oc = owns_edge(a, b);
-		e.fa = (float)edge(a, b, c.X, c.Y);
-		const int32_t w = bx.x1 - bx.x0 + 1;
-		const long long npx = (long long)w * (bx.y1 - bx.y0 + 1);
-		for (long long k = threadIdx.x; k < npx; k += kBigThreads)
-			pixel(a, b, c, e, t.layer, bx.x0 + (int32_t)(k % w), bx.y0 + (int32_t)(k / w), p);
+		e.rfa = 1.0f / (float)edge(a, b, c.X, c.Y);
+		// thread <-> row of the tile: the covered span of the row, exactly
+		if (threadIdx.x < kRows) {
+			const int32_t y = bx.y0 + (int32_t)threadIdx.x;
+			int32_t x0 = bx.x0, x1 = y <= bx.y1 ? bx.x1 : bx.x0 - 1;
+			if (x1 >= x0) clip_span(b, c, e.oa, y, x0, x1);
+			if (x1 >= x0) clip_span(c, a, e.ob, y, x0, x1);
+			if (x1 >= x0) clip_span(a, b, e.oc, y, x0, x1);
+			span_x0[threadIdx.x] = x0;
+			// exclusive prefix of the span lengths over the 64 rows (two warps)
+			const uint32_t len = x1 >= x0 ? (uint32_t)(x1 - x0 + 1) : 0u;
+			uint32_t inc = len;
+#pragma unroll
+			for (int d = 1; d < 32; d <<= 1) {
+				const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
+				if ((int)(threadIdx.x & 31) >= d) inc += o;
+			}
+			incl[threadIdx.x] = inc;
+		}
+		__syncthreads();
+		const uint32_t half = incl[31], total = half + incl[kRows - 1];
+		// thread <-> covered pixel; its row = the first one of its half whose inclusive count exceeds the index
+		for (uint32_t k = threadIdx.x; k < total; k += kBigThreads) {
+			const int base = k >= half ? 32 : 0;
+			const uint32_t kk = k - (base ? half : 0u);
+			int r = base;
+#pragma unroll
+			for (int step = 16; step > 0; step >>= 1)
+				if (incl[r + step - 1] <= kk) r += step;
+			const uint32_t before = r == base ? 0u : incl[r - 1];
+			pixel<true>(a, b, c, e, t.layer, span_x0[r] + (int32_t)(kk - before), bx.y0 + r, p);
+		}
 	}
 }
 
 __global__ void clear_kernel(unsigned long long *fb, size_t n, uint32_t *big_count) {
 	const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (i < n) fb[i] = ~0ull;
-	if (i == 0) *big_count = 0;
+	if (i == 0) big_count[0] = big_count[1] = 0;
 }
 __global__ void resolve_kernel(const unsigned long long *fb, size_t n, uint32_t clear, uint32_t *image) {
 	const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -319,7 +401,7 @@ int mm_raster_frame(mm_ctx *c, const mm_shaded_vertex *d_verts, uint64_t n_verti
 		c->fb_pixels = npx;
 	}
 	if (!c->d_big) {
-		MM_CUDA(c, cudaMalloc(&c->d_big, sizeof(BigTri) * (size_t)kBigCap + 256));
+		MM_CUDA(c, cudaMalloc(&c->d_big, sizeof(BigTri) * (size_t)kBigCap + sizeof(uint2) * (size_t)kTileCap + 256));
 		MM_CUDA(c, cudaMalloc(&c->d_big_count, 256));
 	}
 	if (!c->ev2) {
@@ -334,6 +416,7 @@ int mm_raster_frame(mm_ctx *c, const mm_shaded_vertex *d_verts, uint64_t n_verti
 	p.tex = c->d_tex; p.layers = c->tex_layers; p.ts = c->tex_size;
 	p.fb = (unsigned long long *)c->d_fb;
 	p.big = (BigTri *)c->d_big;
+	p.tiles = (uint2 *)(c->d_big + sizeof(BigTri) * (size_t)kBigCap);
 	p.big_count = (uint32_t *)c->d_big_count;
 	const uint32_t clear = host_u8(f->clear[0]) | (host_u8(f->clear[1]) << 8) | (host_u8(f->clear[2]) << 16) | (host_u8(f->clear[3]) << 24);
 	const unsigned pxblocks = (unsigned)((npx + 255) / 256);
@@ -343,7 +426,7 @@ int mm_raster_frame(mm_ctx *c, const mm_shaded_vertex *d_verts, uint64_t n_verti
 		const uint64_t want = (p.n_tris + kTriThreads - 1) / kTriThreads;
 		const unsigned grid = (unsigned)std::min<uint64_t>(want, (uint64_t)c->sm_count * 64);
 		raster_tris_kernel<<<grid, kTriThreads, 0, c->stream>>>(p);
-		raster_big_kernel<<<c->sm_count * 16, kBigThreads, 0, c->stream>>>(p);
+		raster_big_kernel<<<c->sm_count * 32, kBigThreads, 0, c->stream>>>(p);
 	}
 	resolve_kernel<<<pxblocks, 256, 0, c->stream>>>(p.fb, npx, clear, d_image);
 	MM_CUDA(c, cudaGetLastError());

@@ -168,21 +168,21 @@ static void raster_tri(const sv *p0, const sv *p1, const sv *p2, uint32_t layer,
 	if (x1 > (int32_t)f->width - 1) x1 = (int32_t)f->width - 1;
 	if (y1 > (int32_t)f->height - 1) y1 = (int32_t)f->height - 1;
 	const int oa = owns_edge(b, c), ob = owns_edge(c, a), oc = owns_edge(a, b);
-	const float fa = (float)A;
+	const float rfa = 1.0f / (float)A;
 	for (int32_t y = y0; y <= y1; y++)
 		for (int32_t x = x0; x <= x1; x++) {
 			const int64_t px = (int64_t)x * 256 + 128, py = (int64_t)y * 256 + 128;
 			const int64_t wa = edge(b, c, px, py), wb = edge(c, a, px, py), wc = edge(a, b, px, py);
 			if (wa < 0 || wb < 0 || wc < 0) continue;
 			if ((wa == 0 && !oa) || (wb == 0 && !ob) || (wc == 0 && !oc)) continue;
-			const float la = (float)wa / fa, lb = (float)wb / fa, lc = (float)wc / fa;
+			const float la = (float)wa * rfa, lb = (float)wb * rfa, lc = (float)wc * rfa;
 			const float depth = la * a->z + lb * b->z + lc * c->z;
 			const uint32_t d24 = (uint32_t)(clamp01(depth) * 16777215.0f + 0.5f);
 			if (d24 >= 0xFFFFFFu) continue;  /* IfLess against the cleared 1.0 */
 			const float qa = la * a->invw, qb = lb * b->invw, qc = lc * c->invw;
-			const float qs = qa + qb + qc;
+			const float rq = 1.0f / (qa + qb + qc);
 			float at[NATTR];
-			for (int k = 0; k < NATTR; k++) at[k] = (qa * a->a[k] + qb * b->a[k] + qc * c->a[k]) / qs;
+			for (int k = 0; k < NATTR; k++) at[k] = (qa * a->a[k] + qb * b->a[k] + qc * c->a[k]) * rq;
 			uint32_t rgba;
 			if (!fragment(at, layer, f, tex, layers, ts, &rgba)) continue;
 			const uint64_t key = ((uint64_t)d24 << 32) | rgba;
