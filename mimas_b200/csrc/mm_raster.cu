@@ -15,7 +15,10 @@
 //   raster_tris_kernel  one thread per triangle: clip, set up, and rasterise it if its bounding box is small;
 //                       larger ones go to a list, cut into 64 x 64 pixel tiles (tiles wholly outside one
 //                       edge are dropped), one queue entry per tile
-//   raster_big_kernel   one CTA per queued (triangle, tile), threads stride over the tile's share of the box
+//   raster_mid_kernel   one warp per listed triangle of at most 32 rows x 128 columns
+//   raster_big_kernel   one CTA per queued (triangle, tile)
+//                       both: thread <-> row solves the covered span of the row exactly from the three edge
+//                       functions, a scan flattens the spans, thread <-> covered pixel shades
 //   resolve_kernel      keys -> RGBA8 image (clear colour where nothing was drawn)
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -31,8 +34,10 @@ namespace {
 constexpr int kNAttr = 7;          // vlamb, u, v, vposition.xyzw
 constexpr float kGuard = 16.0f;    // guard band: clip x, y at +-kGuard * w
 constexpr int kMaxPoly = 12;
-constexpr int kSmallBox = 64;      // bounding boxes up to this many pixels are rasterised by the triangle's own thread
-constexpr uint32_t kBigCap = 1u << 19;   // listed triangles
+constexpr int kSmallBox = 32;      // bounding boxes up to this many pixels are rasterised by the triangle's own thread
+constexpr int kMidRows = 32, kMidCols = 128;  // up to this box a listed triangle is one warp's job
+constexpr uint32_t kBigCap = 1u << 20;   // listed triangles
+constexpr uint32_t kMidCap = 1u << 20;   // of which queued for the warp kernel
 constexpr uint32_t kTileCap = 1u << 22;  // queued (triangle, tile) pairs
 constexpr int kTileShift = 6;            // 64 x 64 pixels
 constexpr uint32_t kNoTri = 0xffffffffu;
@@ -64,7 +69,8 @@ struct RasterParams {
 	unsigned long long *fb;
 	BigTri *big;
 	uint2 *tiles;         // x = slot in big (kNoTri: empty entry), y = tile x | tile y << 16
-	uint32_t *big_count;  // [0] triangles listed, [1] tile entries queued
+	uint32_t *mid;        // slots in big
+	uint32_t *big_count;  // [0] triangles listed, [1] tile entries queued, [2] mid entries queued
 };
 
 __device__ __forceinline__ float plane_dist(const ClipV &v, int p) {
@@ -181,9 +187,17 @@ struct Box {
 	int32_t x0, x1, y0, y1;
 };
 
-__device__ __forceinline__ long long floor_div(long long n, long long d) {  // d > 0
-	const long long q = n / d;
-	return (n % d != 0 && n < 0) ? q - 1 : q;
+// floor(n / d) for d > 0, saturated at +-2^20 (the caller clamps to a box within +-8192): a float estimate made
+// exact with the integer products -- a 64-bit division costs some hundred instructions, and this runs three
+// times per row of every listed triangle.  |n|, d < 2^52: the estimate is off by less than one.
+__device__ __forceinline__ long long floor_div(long long n, long long d) {
+	const float qf = floorf((float)n / (float)d);
+	if (qf >= 1048576.0f) return 1 << 20;
+	if (qf <= -1048576.0f) return -(1 << 20);
+	long long q = (long long)qf;
+	while (q * d > n) q--;
+	while ((q + 1) * d <= n) q++;
+	return q;
 }
 // The pixels x of row y with edge(u, w, centre) >= 0 (> 0 unless `owns`), intersected with [x0, x1]: the same
 // integers the per-pixel test accepts, solved for x.  edge = C - dy * 256 * x with C as below.
@@ -227,6 +241,16 @@ __device__ void emit_triangle(const ScreenV &p0, const ScreenV &p1, const Screen
 		const int32_t tx0 = bx.x0 >> kTileShift, tx1 = bx.x1 >> kTileShift, ty0 = bx.y0 >> kTileShift, ty1 = bx.y1 >> kTileShift;
 		const uint32_t ntiles = (uint32_t)(tx1 - tx0 + 1) * (uint32_t)(ty1 - ty0 + 1);
 		const uint32_t slot = atomicAdd(p.big_count, 1u);
+		if (slot < kBigCap && bx.y1 - bx.y0 < kMidRows && bx.x1 - bx.x0 < kMidCols) {
+			const uint32_t at = atomicAdd(p.big_count + 2, 1u);
+			if (at < kMidCap) {
+				BigTri &t = p.big[slot];
+				t.v[0] = a; t.v[1] = b; t.v[2] = c;
+				t.layer = layer;
+				p.mid[at] = slot;
+				return;
+			}
+		}
 		const uint32_t base = slot < kBigCap ? atomicAdd(p.big_count + 1, ntiles) : kTileCap;
 		if (base < kTileCap && ntiles <= kTileCap - base) {
 			BigTri &t = p.big[slot];
@@ -294,6 +318,53 @@ __global__ void __launch_bounds__(kTriThreads) raster_tris_kernel(const RasterPa
 	}
 }
 
+constexpr int kMidWarps = 4;
+__global__ void __launch_bounds__(kMidWarps * 32) raster_mid_kernel(const RasterParams p) {
+	__shared__ BigTri ts[kMidWarps];
+	__shared__ int32_t span_x0[kMidWarps][32];
+	__shared__ uint32_t incl[kMidWarps][32];
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const unsigned full = 0xffffffffu;
+	const uint32_t n = min(p.big_count[2], kMidCap);
+	for (uint32_t i = blockIdx.x * kMidWarps + warp; i < n; i += gridDim.x * kMidWarps) {
+		const uint32_t *src = reinterpret_cast<const uint32_t *>(p.big + __ldg(p.mid + i));
+		__syncwarp();
+		for (int k = lane; k < (int)(sizeof(BigTri) / 4); k += 32) reinterpret_cast<uint32_t *>(&ts[warp])[k] = src[k];
+		__syncwarp();
+		const BigTri &t = ts[warp];
+		const ScreenV &a = t.v[0], &b = t.v[1], &c = t.v[2];
+		const Box bx = bbox(a, b, c, p.width, p.height);
+		Edges e;
+		e.oa = owns_edge(b, c); e.ob = owns_edge(c, a); e.oc = owns_edge(a, b);
+		e.rfa = 1.0f / (float)edge(a, b, c.X, c.Y);
+		// lane <-> row
+		const int32_t y = bx.y0 + lane;
+		int32_t x0 = bx.x0, x1 = y <= bx.y1 ? bx.x1 : bx.x0 - 1;
+		if (x1 >= x0) clip_span(b, c, e.oa, y, x0, x1);
+		if (x1 >= x0) clip_span(c, a, e.ob, y, x0, x1);
+		if (x1 >= x0) clip_span(a, b, e.oc, y, x0, x1);
+		uint32_t inc = x1 >= x0 ? (uint32_t)(x1 - x0 + 1) : 0u;
+#pragma unroll
+		for (int d = 1; d < 32; d <<= 1) {
+			const uint32_t o = __shfl_up_sync(full, inc, d);
+			if (lane >= d) inc += o;
+		}
+		span_x0[warp][lane] = x0;
+		incl[warp][lane] = inc;
+		const uint32_t total = __shfl_sync(full, inc, 31);
+		__syncwarp();
+		// lane <-> covered pixel
+		for (uint32_t k = lane; k < total; k += 32) {
+			int r = 0;
+#pragma unroll
+			for (int step = 16; step > 0; step >>= 1)
+				if (incl[warp][r + step - 1] <= k) r += step;
+			const uint32_t before = r == 0 ? 0u : incl[warp][r - 1];
+			pixel<true>(a, b, c, e, t.layer, span_x0[warp][r] + (int32_t)(k - before), bx.y0 + r, p);
+		}
+	}
+}
+
 __global__ void __launch_bounds__(kBigThreads) raster_big_kernel(const RasterParams p) {
 	__shared__ BigTri t;
 	constexpr int kRows = 1 << kTileShift;
@@ -351,7 +422,7 @@ __global__ void __launch_bounds__(kBigThreads) raster_big_kernel(const RasterPar
 __global__ void clear_kernel(unsigned long long *fb, size_t n, uint32_t *big_count) {
 	const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (i < n) fb[i] = ~0ull;
-	if (i == 0) big_count[0] = big_count[1] = 0;
+	if (i == 0) big_count[0] = big_count[1] = big_count[2] = 0;
 }
 __global__ void resolve_kernel(const unsigned long long *fb, size_t n, uint32_t clear, uint32_t *image) {
 	const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -401,7 +472,7 @@ int mm_raster_frame(mm_ctx *c, const mm_shaded_vertex *d_verts, uint64_t n_verti
 		c->fb_pixels = npx;
 	}
 	if (!c->d_big) {
-		MM_CUDA(c, cudaMalloc(&c->d_big, sizeof(BigTri) * (size_t)kBigCap + sizeof(uint2) * (size_t)kTileCap + 256));
+		MM_CUDA(c, cudaMalloc(&c->d_big, sizeof(BigTri) * (size_t)kBigCap + sizeof(uint2) * (size_t)kTileCap + 4 * (size_t)kMidCap + 256));
 		MM_CUDA(c, cudaMalloc(&c->d_big_count, 256));
 	}
 	if (!c->ev2) {
@@ -417,6 +488,7 @@ int mm_raster_frame(mm_ctx *c, const mm_shaded_vertex *d_verts, uint64_t n_verti
 	p.fb = (unsigned long long *)c->d_fb;
 	p.big = (BigTri *)c->d_big;
 	p.tiles = (uint2 *)(c->d_big + sizeof(BigTri) * (size_t)kBigCap);
+	p.mid = (uint32_t *)(c->d_big + sizeof(BigTri) * (size_t)kBigCap + sizeof(uint2) * (size_t)kTileCap);
 	p.big_count = (uint32_t *)c->d_big_count;
 	const uint32_t clear = host_u8(f->clear[0]) | (host_u8(f->clear[1]) << 8) | (host_u8(f->clear[2]) << 16) | (host_u8(f->clear[3]) << 24);
 	const unsigned pxblocks = (unsigned)((npx + 255) / 256);
@@ -426,6 +498,7 @@ int mm_raster_frame(mm_ctx *c, const mm_shaded_vertex *d_verts, uint64_t n_verti
 		const uint64_t want = (p.n_tris + kTriThreads - 1) / kTriThreads;
 		const unsigned grid = (unsigned)std::min<uint64_t>(want, (uint64_t)c->sm_count * 64);
 		raster_tris_kernel<<<grid, kTriThreads, 0, c->stream>>>(p);
+		raster_mid_kernel<<<c->sm_count * 16, kMidWarps * 32, 0, c->stream>>>(p);
 		raster_big_kernel<<<c->sm_count * 32, kBigThreads, 0, c->stream>>>(p);
 	}
 	resolve_kernel<<<pxblocks, 256, 0, c->stream>>>(p.fb, npx, clear, d_image);
