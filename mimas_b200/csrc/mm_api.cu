@@ -605,12 +605,17 @@ static int pipelined_batch_host(mm_ctx *c, const uint8_t *hc, const int64_t *ho,
 	*done = false;
 	if (!c->have_table) return fail(c, MM_ERR_NO_TABLE, "mm_set_block_table has not been called");
 	if (!c->cap_i && !c->cap_t) return MM_OK;
+	if (c->host_qi_per_chunk < 0.0) return MM_OK;  // no earlier host batch to size the pinned result by
 	int rc;
 	if ((rc = ensure_in_capacity(c, n))) return rc;
 	if ((rc = ensure_chunk_capacity(c, n))) return rc;
 	const auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
 	const size_t br = (size_t)n * 16;
-	const size_t oi = 0, ot = up(c->cap_i * mm::kQuadBytes), ori = up(ot + c->cap_t * mm::kQuadBytes), ort = ori + up(br);
+	// room in the pinned result: what the last host batch needed per chunk plus a quarter, never more than the
+	// device arenas hold (those may be far larger after a big device-resident batch)
+	const uint64_t room_i = std::min<uint64_t>(c->cap_i, (uint64_t)(c->host_qi_per_chunk * 1.25 * n) + 4096);
+	const uint64_t room_t = std::min<uint64_t>(c->cap_t, (uint64_t)(c->host_qt_per_chunk * 1.25 * n) + 4096);
+	const size_t oi = 0, ot = up(room_i * mm::kQuadBytes), ori = up(ot + room_t * mm::kQuadBytes), ort = ori + up(br);
 	if ((rc = ensure_pinned(c, &c->h_out, &c->h_out_bytes, ort + br + 256))) return rc;
 	if (!c->s_in) {
 		MM_CUDA(c, cudaStreamCreateWithFlags(&c->s_in, cudaStreamNonBlocking));
@@ -644,7 +649,7 @@ static int pipelined_batch_host(mm_ctx *c, const uint8_t *hc, const int64_t *ho,
 		MM_CUDA(c, cudaStreamSynchronize(c->stream));
 		if (k + ahead < pieces && (rc = send(k + ahead))) return rc;  // its event is free again
 		const uint64_t ti = c->h_totals[0], tt = c->h_totals[1];
-		if (ti > c->cap_i || tt > c->cap_t) {
+		if (ti > room_i || tt > room_t) {
 			fits = false;
 			break;
 		}
@@ -670,6 +675,8 @@ static int pipelined_batch_host(mm_ctx *c, const uint8_t *hc, const int64_t *ho,
 	c->last_ms = 0.f;
 	c->last_timed = false;
 	c->finished = true;  // the device arenas hold this batch: mm_copy_out works
+	c->host_qi_per_chunk = (double)pi / n;
+	c->host_qt_per_chunk = (double)pt / n;
 	out->intransparent = (const mm_vertex *)(c->h_out + oi);
 	out->transparent = (const mm_vertex *)(c->h_out + ot);
 	out->ranges_i = (const mm_range *)(c->h_out + ori);
@@ -724,6 +731,10 @@ int mm_mesh_batch_host(mm_ctx *c, const uint8_t *chunks, const int64_t *offs, ui
 	out->n_transparent = bo.n_transparent;
 	out->n_chunks = n;
 	out->reserved = 0;
+	if (n) {
+		c->host_qi_per_chunk = (double)(bo.n_intransparent / 6) / n;
+		c->host_qt_per_chunk = (double)(bo.n_transparent / 6) / n;
+	}
 	return MM_OK;
 }
 

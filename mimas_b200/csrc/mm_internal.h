@@ -68,6 +68,7 @@ struct mm_ctx {
 	cudaStream_t s_in = nullptr, s_out = nullptr;
 	cudaEvent_t ev_in[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 	uint32_t pipe_min_chunks = 1024;  // 0: off (MM_PIPE_MIN_CHUNKS)
+	double host_qi_per_chunk = -1.0, host_qt_per_chunk = -1.0;  // quads per chunk of the last large host batch
 
 	// last batch
 	bool pending = false, finished = false;
