@@ -38,6 +38,9 @@ constexpr int kThreads = kWarpsPerCta * 32;
 #ifndef MM_EXPAND_MINBLOCKS
 #define MM_EXPAND_MINBLOCKS 3
 #endif
+#ifndef MM_ANALYSE_PREFETCH
+#define MM_ANALYSE_PREFETCH 1
+#endif
 #ifndef MM_EXPAND_PREFETCH
 #define MM_EXPAND_PREFETCH 0
 #endif
@@ -98,6 +101,10 @@ __device__ __forceinline__ void bulk_load_g2s(void *sdst, const void *gsrc, uint
 	asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(d),
 	             "l"(gsrc), "r"(bytes), "r"(b)
 	             : "memory");
+}
+// pulls a chunk into L2 ahead of its bulk load (no destination, no completion to wait for)
+__device__ __forceinline__ void bulk_prefetch_l2(const void *gsrc, uint32_t bytes) {
+	asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gsrc), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(unsigned long long *mbar, uint32_t parity) {
 	const uint32_t b = (uint32_t)__cvta_generic_to_shared(mbar);
@@ -196,8 +203,12 @@ __global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(co
 		if (tid == 0) {
 			bulk_load_g2s(raw, p.chunks + (size_t)c * 4096u, 4096u, &s.mbar);  // TMA: 4 KiB chunk -> shared memory
 			// the next ticket travels while this chunk is analysed
-			s.ticket[par ^ 1u] = (uint32_t)min(atomicAdd(p.ticket, 1ull) - p.ticket_base, (u64)0xffffffffu);
+			const uint32_t nxt = (uint32_t)min(atomicAdd(p.ticket, 1ull) - p.ticket_base, (u64)0xffffffffu);
+			s.ticket[par ^ 1u] = nxt;
 			s.amb[par ^ 1u] = 0;
+#if MM_ANALYSE_PREFETCH
+			if (nxt < p.n) bulk_prefetch_l2(p.chunks + (size_t)nxt * 4096u, 4096u);  // and its chunk comes as far as L2
+#endif
 		}
 		Col hrow;
 		if (HALO && tid < 96) {  // one 16-byte row of the halo slabs per thread, in flight beside the chunk

@@ -250,7 +250,7 @@ int mm_ctx_create(int device, mm_ctx **out) {
 		int occ2 = 0;
 		MM_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, mm::expand_kernel, mm::kExpandThreads, mm::kExpandSmemBytes));
 		if (occ2 < 1) return fail(c, MM_ERR_CUDA, "expand kernel does not fit on an SM");
-		c->expand_grid = c->sm_count * occ2;
+		c->expand_grid = c->sm_count;  // one expanding CTA per SM, whatever would fit: the rest of the SM is the analysis's
 		c->use_pdl = getenv("MM_NO_PDL") == nullptr;
 		if (const char *e = getenv("MM_PIPE_MIN_CHUNKS")) c->pipe_min_chunks = (uint32_t)std::max(0, atoi(e));
 		c->no_small = getenv("MM_NO_SMALL_PATH") != nullptr;
