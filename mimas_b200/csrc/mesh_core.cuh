@@ -101,7 +101,6 @@ struct alignas(128) ChunkSmem {
 	// (Hm[0..15] x- over y, Hm[16..31] x+ over y, Hm[32..47] y- over x, Hm[48..63] y+ over x)
 	alignas(16) uint16_t Hz[32];
 	alignas(16) uint16_t Hm[64];
-	uint32_t nq, nwords, npl;                  // totals of the chunk
 	uint32_t amb[2];                           // OR of the flag bytes of the chunk's cells (double buffered)
 	uint32_t ticket[2];                        // chunk index of this / the next round (double buffered)
 	alignas(8) unsigned long long mbar;        // mbarrier of the chunk load (device only)

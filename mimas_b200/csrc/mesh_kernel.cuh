@@ -38,6 +38,9 @@ constexpr int kThreads = kWarpsPerCta * 32;
 #ifndef MM_EXPAND_MINBLOCKS
 #define MM_EXPAND_MINBLOCKS 3
 #endif
+#ifndef MM_ANALYSE_UNIFORM_EXIT
+#define MM_ANALYSE_UNIFORM_EXIT 1
+#endif
 #ifndef MM_ANALYSE_PREFETCH
 #define MM_ANALYSE_PREFETCH 1
 #endif
@@ -229,7 +232,7 @@ __global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(co
 			          w0 == __byte_perm(w0, 0, 0) && w0 == *reinterpret_cast<const uint32_t *>(raw);
 		}
 		// a chunk of one undrawn id (all air: a quarter of a terrain region) is done here
-		if (__syncthreads_and(uniform) && (flags[raw[0]] & (kFlagBlocky | kFlagCrossed)) == 0) {
+		if (MM_ANALYSE_UNIFORM_EXIT && __syncthreads_and(uniform) && (flags[raw[0]] & (kFlagBlocky | kFlagCrossed)) == 0) {
 			if (tid == 0) {
 				p.cnt_i[c] = 0;
 				p.cnt_t[c] = 0;
@@ -264,32 +267,28 @@ __global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(co
 			else s.gcnt[tid - 32] = transpose_group(s, tid - 32);
 			if (HALO && tid >= 124) transpose_halo(s, tid - 124);  // Bzp's border is read-only here
 			__syncthreads();
-			if (warp == 0) {  // exclusive scan of quads (low half) and non-empty words (high half) over the groups
-				uint32_t run = 0;
+			// exclusive scan of quads (low half) and non-empty words (high half) over the 96 groups, by every warp
+			// for itself (no hand-over through shared memory, one barrier less): the thread of group
+			// m = tid - 32 = (warp - 1) * 32 + lane finds its own prefix in round warp - 1
+			uint32_t run = 0, mine = 0;
 #pragma unroll
-				for (int k = 0; k < 3; k++) {
-					const uint32_t v = s.gcnt[lane + 32 * k];
-					const uint32_t inc = warp_incl_scan(v, lane);
-					s.gcnt[lane + 32 * k] = run + inc - v;
-					run += __shfl_sync(full, inc, 31);
-				}
-				if (lane == 0) {
-					s.nq = run & 0xffffu;
-					s.nwords = run >> 16;
-				}
+			for (int k = 0; k < 3; k++) {
+				const uint32_t v = s.gcnt[lane + 32 * k];
+				const uint32_t inc = warp_incl_scan(v, lane);
+				if (k == warp - 1) mine = run + inc - v;
+				run += __shfl_sync(full, inc, 31);
 			}
-			__syncthreads();
-			if (tid >= 32) list_group_words(s, tid - 32, s.gcnt[tid - 32]);
+			if (tid >= 32) list_group_words(s, tid - 32, mine);
 			__syncthreads();
 			// D. descriptors: thread <-> non-empty word (two rows)
-			const uint32_t nwords = s.nwords;
+			const uint32_t nwords = run >> 16;
 #pragma unroll 1
 			for (uint32_t i = (uint32_t)tid; i < nwords; i += kThreads) {
 				const uint32_t e = smem_wl(s)[i];
 				const uint32_t widx = e & 1023u;
 				emit_word_descs<HALO>(s, widx, reinterpret_cast<const uint32_t *>(s.S)[widx], di + (e >> 10));
 			}
-			if (tid == 0) p.cnt_i[c] = s.nq;
+			if (tid == 0) p.cnt_i[c] = run & 0xffffu;
 		} else if (tid == 0) {
 			p.cnt_i[c] = 0;
 		}
