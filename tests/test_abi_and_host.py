@@ -105,3 +105,26 @@ def test_terrain_generator_is_deterministic_and_plausible():
     assert c.tobytes() == a[64:128].tobytes() and oc.tobytes() == oa[64:128].tobytes()
     ids = set(np.unique(a))
     assert {0, 1, 5} <= ids and ids <= set(range(56))
+
+
+def test_header_compiles_as_c_and_struct_sizes_match_the_bindings(tmp_path):
+    """include/mimas_meshgen_cuda.h is plain C (the cgo / Rust-FFI side needs nothing else), and the ctypes
+    mirrors of its structs have the sizes the C compiler gives them."""
+    import subprocess
+    from mimas_b200 import meshgen as mg
+    from mimas_b200 import render as rd
+    names = ["mm_vertex", "mm_range", "mm_block_entry", "mm_cube", "mm_batch_out", "mm_host_mesh", "mm_camera",
+             "mm_shaded_vertex", "mm_draw_out", "mm_frame"]
+    src = tmp_path / "sizes.c"
+    src.write_text('#include <stdio.h>\n#include "mimas_meshgen_cuda.h"\nint main(void) {\n'
+                   + "".join(f'\tprintf("{n} %zu\\n", sizeof({n}));\n' for n in names) + "\treturn 0;\n}\n")
+    exe = tmp_path / "sizes"
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)],
+                   check=True)
+    got = dict(line.split() for line in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.splitlines())
+    want = {"mm_vertex": mg.VERTEX_DTYPE.itemsize, "mm_range": mg.RANGE_DTYPE.itemsize,
+            "mm_block_entry": mg.BLOCK_ENTRY_DTYPE.itemsize, "mm_cube": mg.CUBE_DTYPE.itemsize,
+            "mm_batch_out": C.sizeof(mg._BatchOut), "mm_host_mesh": C.sizeof(mg._HostMesh),
+            "mm_camera": C.sizeof(rd.CCamera), "mm_shaded_vertex": rd.SHADED_DTYPE.itemsize,
+            "mm_draw_out": C.sizeof(rd.DrawOut), "mm_frame": C.sizeof(rd.CFrame)}
+    assert {k: int(v) for k, v in got.items()} == want
