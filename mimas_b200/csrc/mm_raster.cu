@@ -34,7 +34,10 @@ namespace {
 constexpr int kNAttr = 7;          // vlamb, u, v, vposition.xyzw
 constexpr float kGuard = 16.0f;    // guard band: clip x, y at +-kGuard * w
 constexpr int kMaxPoly = 12;
-constexpr int kSmallBox = 32;      // bounding boxes up to this many pixels are rasterised by the triangle's own thread
+#ifndef MM_RASTER_SMALL
+#define MM_RASTER_SMALL 32
+#endif
+constexpr int kSmallBox = MM_RASTER_SMALL;  // bounding boxes up to this many pixels are rasterised by the triangle's own thread
 constexpr int kMidRows = 32, kMidCols = 128;  // up to this box a listed triangle is one warp's job
 constexpr uint32_t kBigCap = 1u << 20;   // listed triangles
 constexpr uint32_t kMidCap = 1u << 20;   // of which queued for the warp kernel
