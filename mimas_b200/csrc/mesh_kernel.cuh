@@ -38,6 +38,9 @@ constexpr int kThreads = kWarpsPerCta * 32;
 #ifndef MM_EXPAND_MINBLOCKS
 #define MM_EXPAND_MINBLOCKS 3
 #endif
+#ifndef MM_EXPERIMENT_SKIP_EMIT
+#define MM_EXPERIMENT_SKIP_EMIT 0  // timing experiments only: leaves the descriptors unwritten
+#endif
 #ifndef MM_ANALYSE_UNIFORM_EXIT
 #define MM_ANALYSE_UNIFORM_EXIT 1
 #endif
@@ -283,7 +286,7 @@ __global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(co
 			// D. descriptors: thread <-> non-empty word (two rows)
 			const uint32_t nwords = run >> 16;
 #pragma unroll 1
-			for (uint32_t i = (uint32_t)tid; i < nwords; i += kThreads) {
+			for (uint32_t i = (uint32_t)tid; i < (MM_EXPERIMENT_SKIP_EMIT ? 0u : nwords); i += kThreads) {
 				const uint32_t e = smem_wl(s)[i];
 				const uint32_t widx = e & 1023u;
 				emit_word_descs<HALO>(s, widx, reinterpret_cast<const uint32_t *>(s.S)[widx], di + (e >> 10));

@@ -167,6 +167,10 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, co
 			cfg.stream = c->stream;
 			cfg.attrs = attr;
 			cfg.numAttrs = 1;
+#if MM_EXPERIMENT_SKIP_ANALYSE  // timing experiments only: expansion alone, on stale descriptors
+			if (c->total_launches >= 64) {
+			} else
+#endif
 			if (d_halo) MM_CUDA(c, cudaLaunchKernelEx(&cfg, mm::analyse_kernel<true>, a));
 			else MM_CUDA(c, cudaLaunchKernelEx(&cfg, mm::analyse_kernel<false>, a));
 		}
