@@ -485,13 +485,17 @@ MM_HD uint32_t transpose_group(ChunkSmem &s, int m) {
 }
 
 // Appends the non-empty words of group m to wl.  `pre` = quads | words << 16 of the groups before m.
+struct alignas(16) Word4 {
+	uint32_t v[4];
+};
 MM_HD void list_group_words(ChunkSmem &s, int m, uint32_t pre) {
-	const uint32_t *p = reinterpret_cast<const uint32_t *>(s.S + m * 16);
+	// the group's eight words as two 16-byte loads: word by word the lanes (32 bytes apart) collide eight-fold
+	const Word4 lo = *reinterpret_cast<const Word4 *>(s.S + m * 16), hi = *reinterpret_cast<const Word4 *>(s.S + m * 16 + 8);
 	uint32_t *wl = smem_wl(s);
 	uint32_t o = pre >> 16, q = pre & 0xffffu;
 #pragma unroll
 	for (int k = 0; k < 8; k++) {
-		const uint32_t w = p[k];
+		const uint32_t w = k < 4 ? lo.v[k] : hi.v[k - 4];
 		if (w) {
 			wl[o++] = (uint32_t)(m * 8 + k) | (q << 10);
 			q += (uint32_t)popc32(w);
