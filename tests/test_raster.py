@@ -240,3 +240,26 @@ def test_gpu_frame_of_a_meshed_region_equals_oracle(mesher):
     finally:
         mesher.dev_free(d_c)
         mesher.dev_free(d_o)
+
+
+def test_png_writer_and_synthetic_textures(tmp_path):
+    import struct
+    import zlib
+    from mimas_b200.render import synthetic_textures, write_png
+    tex = synthetic_textures(10, crossed=(3,))
+    assert tex.shape == (10, 16, 16, 4) and tex.dtype == np.float32 and tex.min() >= 0 and tex.max() <= 1
+    assert set(np.unique(tex[3, :, :, 3])) <= {0.0, 1.0} and (tex[2, :, :, 3] == 1).all()
+    img = (np.arange(6, dtype=np.uint32).reshape(2, 3) * 0x010203 + 0xFF000000)
+    path = tmp_path / "t.png"
+    write_png(str(path), img)
+    data = path.read_bytes()
+    assert data[:8] == b"\x89PNG\r\n\x1a\n"
+    w, h, depth, ctype = struct.unpack(">IIBB", data[16:26])
+    assert (w, h, depth, ctype) == (3, 2, 8, 2)
+    at = data.index(b"IDAT")
+    n = struct.unpack(">I", data[at - 4:at])[0]
+    raw = zlib.decompress(data[at + 4:at + 4 + n])
+    rows = [raw[i * 10 + 1:(i + 1) * 10] for i in range(2)]
+    # top row of the file = row 1 of the image (GL's origin is at the bottom)
+    assert rows[0] == bytes([3 * 3, 3 * 2, 3 * 1, 4 * 3, 4 * 2, 4 * 1, 5 * 3, 5 * 2, 5 * 1])
+    assert rows[1][:3] == bytes([0, 0, 0])
