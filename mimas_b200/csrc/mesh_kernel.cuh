@@ -59,21 +59,6 @@ constexpr uint32_t kMaxLaunchChunks = 4096;      // the prefix of one launch liv
 constexpr size_t kExpandPrefixWords = kMaxLaunchChunks + 4;
 constexpr size_t kExpandSmemBytes = 2048 + 2 * 4 * kExpandPrefixWords + 256 + kExpandWarps * (size_t)(kStageBytes + 16);
 
-struct AnalyseParams {
-	const unsigned char *chunks;  // n * 4096
-	const unsigned char *halo;    // halo mode: n * 1536 (see halo_row in mesh_core.cuh), 16-byte aligned; else unused
-	uint32_t n;                   // <= kMaxLaunchChunks
-	const TabEntry *table;        // 256 entries
-	const unsigned char *flags;   // 256 flag bytes (kFlagBlocky / kFlagCrossed)
-	uint32_t *desc_i;             // n * kDescStrideI descriptor words
-	uint32_t *desc_t;             // n * kDescStrideT
-	uint32_t *cnt_i;              // quads per chunk
-	uint32_t *cnt_t;              // transparent quad slots per chunk (4 per plant)
-	u64 *ticket;                  // monotonically increasing across launches
-	u64 ticket_base;              // its value at launch
-	u64 *trace;                   // NULL, or 4 words of this launch: first CTA start, -, last CTA work done, last CTA end (ns)
-};
-
 struct ExpandParams {
 	const long long *offs;        // n * 3
 	uint32_t n;
@@ -88,6 +73,23 @@ struct ExpandParams {
 	u64 *host_totals;             // the same two words in mapped pinned host memory
 	u64 *trace;                   // NULL, or 4 words of this launch: first CTA start, first CTA past the wait, -, last CTA end (ns)
 };
+
+struct AnalyseParams {
+	const unsigned char *chunks;  // n * 4096
+	const unsigned char *halo;    // halo mode: n * 1536 (see halo_row in mesh_core.cuh), 16-byte aligned; else unused
+	uint32_t n;                   // <= kMaxLaunchChunks
+	const TabEntry *table;        // 256 entries
+	const unsigned char *flags;   // 256 flag bytes (kFlagBlocky / kFlagCrossed)
+	uint32_t *desc_i;             // n * kDescStrideI descriptor words
+	uint32_t *desc_t;             // n * kDescStrideT
+	uint32_t *cnt_i;              // quads per chunk
+	uint32_t *cnt_t;              // transparent quad slots per chunk (4 per plant)
+	u64 *ticket;                  // monotonically increasing across launches
+	u64 ticket_base;              // its value at launch
+	u64 *trace;                   // NULL, or 4 words of this launch: first CTA start, -, last CTA work done, last CTA end (ns)
+	ExpandParams x;               // FUSED instantiation only: where the one chunk's vertices go
+};
+
 
 __device__ __forceinline__ Col lds_col(const unsigned char *p) {
 	const uint4 v = *reinterpret_cast<const uint4 *>(p);
@@ -182,7 +184,9 @@ __device__ __forceinline__ void store_tile(unsigned char *g, const unsigned char
 // HALO = the optional mode in which the touching layers of the six neighbour chunks occlude faces (an
 // extension; false = the reference's semantics, lib.rs:277-280, and the instantiation every number in
 // DESIGN.md is measured on).
-template <bool HALO>
+// FUSED = the single-chunk form (the reference's own call pattern, one chunk per call, client.rs:259-267): a grid
+// of one CTA analyses the chunk and expands it right away -- one launch instead of two and no hand-over.
+template <bool HALO, bool FUSED = false>
 __global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(const AnalyseParams p) {
 	__shared__ ChunkSmem s;
 	__shared__ __align__(16) unsigned char flags[256];
@@ -321,6 +325,45 @@ __global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(co
 	if (tid == 0) trace_mark(p.trace, 2);
 	pdl_wait();
 	if (tid == 0) trace_mark(p.trace, 3);
+	if (FUSED) {  // p.n == 1, one CTA: the chunk's descriptors and counts are this CTA's own writes
+		__shared__ __align__(16) unsigned char stage_all[kWarpsPerCta * (kStageBytes + 16)];
+		__syncthreads();
+		const ExpandParams &x = p.x;
+		const uint32_t nq = p.cnt_i[0], nt = p.cnt_t[0];
+		if (tid == 0) {
+			Range ri, rt;
+			ri.first_vertex = 0; ri.vertex_count = nq * 6u; ri.reserved = 0;
+			rt.first_vertex = 0; rt.vertex_count = nt * 6u; rt.reserved = 0;
+			x.ranges_i[0] = ri;
+			x.ranges_t[0] = rt;
+			x.totals[0] = nq; x.totals[1] = nt;
+			x.host_totals[0] = nq; x.host_totals[1] = nt;
+			__threadfence_system();
+		}
+		const uint32_t tiles_i = nq <= x.cap_i ? (nq + kTileQuads - 1) / kTileQuads : 0u;
+		const uint32_t tiles_t = nt <= x.cap_t ? (nt + kTileQuads - 1) / kTileQuads : 0u;
+		const long long ox = __ldg(x.offs), oy = __ldg(x.offs + 1), oz = __ldg(x.offs + 2);
+		unsigned char *stage = stage_all + (size_t)warp * (kStageBytes + 16);
+#pragma unroll 1
+		for (uint32_t t = (uint32_t)warp; t < tiles_i + tiles_t; t += kWarpsPerCta) {
+			const bool face = t < tiles_i;
+			const uint32_t q0 = (face ? t : t - tiles_i) * kTileQuads;
+			const uint32_t tn = min((uint32_t)kTileQuads, (face ? nq : nt) - q0);
+			unsigned char *g = face ? x.out_i + (u64)q0 * kQuadBytes : x.out_t + (u64)q0 * kQuadBytes;
+			unsigned char *sp = stage + ((uintptr_t)g & 8u);
+			if (lane == 0) bulk_wait_read_all();
+			__syncwarp();
+			if ((uint32_t)lane < tn) {
+				const uint32_t q = q0 + (uint32_t)lane;
+				if (face) expand_face_desc(tab, ox, oy, oz, p.desc_i[q], sp + lane * kQuadBytes);
+				else expand_plant_desc(tab, ox, oy, oz, p.desc_t[q >> 2], lane & 3, sp + lane * kQuadBytes);
+			}
+			fence_proxy_async_smem();
+			__syncwarp();
+			if (lane == 0) store_tile(g, sp, tn * kQuadBytes);
+		}
+		if (lane == 0) bulk_wait_all();
+	}
 }
 
 // ---- kernel 2: expansion -------------------------------------------------------------------

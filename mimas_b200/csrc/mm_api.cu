@@ -155,10 +155,36 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, co
 		a.ticket_base = c->ticket_base;
 		mm::u64 *tr = c->d_trace ? c->d_trace + 8 * (c->trace_next++ % c->trace_pairs) : nullptr;
 		a.trace = tr;
-		const uint32_t grid = std::min<uint32_t>(m, (uint32_t)(c->sm_count * c->analyse_ctas_per_sm));
 		cudaLaunchAttribute attr[1];
 		attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
 		attr[0].val.programmaticStreamSerializationAllowed = c->use_pdl ? 1 : 0;
+		// one chunk (the reference's call pattern): one CTA analyses and expands it, one launch
+		const bool fused = n == 1 && !d_halo && carry == nullptr && c->fuse_single;
+		const uint32_t grid = std::min<uint32_t>(m, (uint32_t)(c->sm_count * c->analyse_ctas_per_sm));
+		if (fused) {
+			mm::ExpandParams &e = a.x;
+			e.offs = d_offs;
+			e.n = 1;
+			e.table = c->d_table;
+			e.desc_i = a.desc_i; e.desc_t = a.desc_t; e.cnt_i = a.cnt_i; e.cnt_t = a.cnt_t;
+			e.out_i = tg.out_i; e.out_t = tg.out_t; e.cap_i = tg.cap_i; e.cap_t = tg.cap_t;
+			e.ranges_i = tg.ranges_i; e.ranges_t = tg.ranges_t;
+			e.carry_in = nullptr;
+			e.totals = c->d_ticket + 2 + 2 * c->totals_slot;
+			e.host_totals = c->d_h_totals;
+			e.trace = nullptr;
+			cudaLaunchConfig_t cfg = {};
+			cfg.gridDim = dim3(1);
+			cfg.blockDim = dim3(mm::kThreads);
+			cfg.stream = c->stream;
+			cfg.attrs = attr;
+			cfg.numAttrs = 1;
+			MM_CUDA(c, (cudaLaunchKernelEx(&cfg, mm::analyse_kernel<false, true>, a)));
+			c->ticket_base += 2;  // the chunk's ticket and the one that ends the loop
+			c->last_launches += 1;
+			c->total_launches += 1;
+			break;
+		}
 		{
 			cudaLaunchConfig_t cfg = {};
 			cfg.gridDim = dim3(grid);
@@ -256,6 +282,7 @@ int mm_ctx_create(int device, mm_ctx **out) {
 		if (occ2 < 1) return fail(c, MM_ERR_CUDA, "expand kernel does not fit on an SM");
 		c->expand_grid = c->sm_count;  // one expanding CTA per SM, whatever would fit: the rest of the SM is the analysis's
 		c->use_pdl = getenv("MM_NO_PDL") == nullptr;
+		c->fuse_single = getenv("MM_NO_FUSED_SINGLE") == nullptr;
 		if (const char *e = getenv("MM_PIPE_MIN_CHUNKS")) c->pipe_min_chunks = (uint32_t)std::max(0, atoi(e));
 		c->no_small = getenv("MM_NO_SMALL_PATH") != nullptr;
 		if (const char *e = getenv("MM_MAPPED_MAX_CHUNKS")) c->mapped_max_chunks = (uint32_t)strtoul(e, nullptr, 10);

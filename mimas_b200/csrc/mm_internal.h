@@ -34,6 +34,7 @@ struct mm_ctx {
 	int pair_parity = 0;
 	int expand_grid = 0;
 	bool use_pdl = true;
+	bool fuse_single = true;  // n == 1: analysis and expansion in one launch (MM_NO_FUSED_SINGLE)
 	mm::u64 *d_ticket = nullptr;      // [0] ticket counter, [2..3] and [4..5] alternating totals slots
 	int totals_slot = 0;              // slot the last launch wrote
 	mm::u64 ticket_base = 0;
