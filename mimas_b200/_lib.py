@@ -75,9 +75,18 @@ def lib() -> C.CDLL:
     l.mm_host_free.argtypes = [vp, vp]
     l.mm_launch_count.argtypes = [vp, C.POINTER(u64)]
     l.mm_device_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    l.mm_cull_chunks.argtypes = [vp, vp, u32, vp, vp, C.POINTER(u32)]
+    l.mm_debug_trace.argtypes = [vp, u32, vp, C.POINTER(u64)]
+    l.mm_vertex_stage.argtypes = [vp, vp, u64, vp, vp]
+    l.mm_draw_batch.argtypes = [vp, vp, vp]
+    l.mm_abi_version.argtypes = []
     for s in SYMBOLS:
+        f = getattr(l, s)
+        # a symbol without argtypes would pass Python ints as 32-bit C ints and truncate every pointer
+        if f.argtypes is None:
+            raise ImportError(f"_lib.py declares no argument types for {s}")
         if s not in ("mm_abi_version", "mm_last_error_string"):
-            getattr(l, s).restype = C.c_int
+            f.restype = C.c_int
     if l.mm_abi_version() != 1:
         raise ImportError("libmimas_meshgen_cuda.so: ABI version mismatch")
     _lib = l

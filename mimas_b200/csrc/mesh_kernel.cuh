@@ -193,14 +193,18 @@ __global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(co
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 	const unsigned full = 0xffffffffu;
 
-	pdl_launch_dependents();  // the expand kernel may set itself up while this one works
+	// the expand kernel may set itself up while this one works.  Not so in the FUSED form: it owns no expand
+	// kernel whose wait would hold the next launch back until the hand-over buffers are free again, so it lets
+	// its dependents go only once everything before it has completed (below, after its own wait).
+	if (!FUSED) pdl_launch_dependents();
 	if (tid == 0) trace_mark(p.trace, 0);
 	if (tid < 16) reinterpret_cast<uint4 *>(flags)[tid] = __ldg(reinterpret_cast<const uint4 *>(p.flags) + tid);
 	if (warp == 1) init_warp_smem(s, lane);
 	if (tid == 0) {
 		mbar_init(&s.mbar);
 		fence_proxy_async_smem();  // the barrier is visible to the bulk-copy engine
-		s.ticket[0] = (uint32_t)min(atomicAdd(p.ticket, 1ull) - p.ticket_base, (u64)0xffffffffu);
+		// FUSED: one CTA, one chunk -- no ticket is drawn, so a following launch may draw its own at once
+		s.ticket[0] = FUSED ? 0u : (uint32_t)min(atomicAdd(p.ticket, 1ull) - p.ticket_base, (u64)0xffffffffu);
 		s.amb[0] = 0;
 	}
 	unsigned char *raw = smem_raw(s);
@@ -213,7 +217,7 @@ __global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(co
 		if (tid == 0) {
 			bulk_load_g2s(raw, p.chunks + (size_t)c * 4096u, 4096u, &s.mbar);  // TMA: 4 KiB chunk -> shared memory
 			// the next ticket travels while this chunk is analysed
-			const uint32_t nxt = (uint32_t)min(atomicAdd(p.ticket, 1ull) - p.ticket_base, (u64)0xffffffffu);
+			const uint32_t nxt = FUSED ? 0xffffffffu : (uint32_t)min(atomicAdd(p.ticket, 1ull) - p.ticket_base, (u64)0xffffffffu);
 			s.ticket[par ^ 1u] = nxt;
 			s.amb[par ^ 1u] = 0;
 #if MM_ANALYSE_PREFETCH
@@ -325,6 +329,7 @@ __global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(co
 	if (tid == 0) trace_mark(p.trace, 2);
 	pdl_wait();
 	if (tid == 0) trace_mark(p.trace, 3);
+	if (FUSED) pdl_launch_dependents();
 	if (FUSED) {  // p.n == 1, one CTA: the chunk's descriptors and counts are this CTA's own writes
 		__shared__ __align__(16) unsigned char stage_all[kWarpsPerCta * (kStageBytes + 16)];
 		__syncthreads();

@@ -180,7 +180,7 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, co
 			cfg.attrs = attr;
 			cfg.numAttrs = 1;
 			MM_CUDA(c, (cudaLaunchKernelEx(&cfg, mm::analyse_kernel<false, true>, a)));
-			c->ticket_base += 2;  // the chunk's ticket and the one that ends the loop
+			// the fused form draws no tickets
 			c->last_launches += 1;
 			c->total_launches += 1;
 			break;
@@ -436,6 +436,9 @@ int mm_mesh_batch_async(mm_ctx *c, const uint8_t *d_chunks, const int64_t *d_off
 
 int mm_mesh_batch_halo_async(mm_ctx *c, const uint8_t *d_chunks, const int64_t *d_offs, const uint8_t *d_halo, uint32_t n) {
 	if (!c || (n && (!d_chunks || !d_offs))) return MM_ERR_INVALID;
+	// the chunks are fetched by bulk async copies, the halo rows as 16-byte loads
+	if (n && ((uintptr_t)d_chunks & 15u)) return fail(c, MM_ERR_INVALID, "chunks must be 16-byte aligned");
+	if (n && ((uintptr_t)d_offs & 7u)) return fail(c, MM_ERR_INVALID, "offs must be 8-byte aligned");
 	if (d_halo && ((uintptr_t)d_halo & 15u)) return fail(c, MM_ERR_INVALID, "halo must be 16-byte aligned");
 	if (!c->have_table) return fail(c, MM_ERR_NO_TABLE, "mm_set_block_table has not been called");
 	if (use_device(c)) return MM_ERR_CUDA;
@@ -586,7 +589,7 @@ static int small_batch_host(mm_ctx *c, const uint8_t *chunks, const int64_t *off
 		// inputs in page-locked memory (mm_host_alloc) are read in place; pageable ones are copied into the block
 		const unsigned char *d_chunks = nullptr;
 		const long long *d_offs = nullptr;
-		if (is_pinned_ptr(chunks) && is_pinned_ptr(offs) &&
+		if (((uintptr_t)chunks & 15u) == 0 && ((uintptr_t)offs & 7u) == 0 && is_pinned_ptr(chunks) && is_pinned_ptr(offs) &&
 		    cudaHostGetDevicePointer((void **)&d_chunks, (void *)chunks, 0) == cudaSuccess &&
 		    cudaHostGetDevicePointer((void **)&d_offs, (void *)offs, 0) == cudaSuccess) {
 		} else {

@@ -275,7 +275,9 @@ __device__ void emit_triangle(const ScreenV &p0, const ScreenV &p1, const Screen
 					p.tiles[k] = make_uint2(keep ? slot : kNoTri, (uint32_t)tx | ((uint32_t)ty << 16));
 				}
 			return;
-		}  // lists full: this thread does the work itself
+		}
+		// lists full: this thread does the work itself; what it had reserved of the tile list stays empty
+		for (uint32_t k = base; k < kTileCap && k - base < ntiles; k++) p.tiles[k] = make_uint2(kNoTri, 0u);
 	}
 	for (int32_t y = bx.y0; y <= bx.y1; y++)
 		for (int32_t x = bx.x0; x <= bx.x1; x++) pixel<false>(a, b, c, e, layer, x, y, p);

@@ -229,9 +229,9 @@ def mesh_for_chunk(offs, chunk, cache: PyCache):  # lib.rs:231-446
 
 def to_structured(verts, dtype):
     out = np.zeros(len(verts), dtype=dtype)
-    for i, (t, uv, p, n) in enumerate(verts):
-        out[i]["tex_ind"] = t
-        out[i]["tex_pos"] = uv
-        out[i]["position"] = p
-        out[i]["normal"] = n
+    if verts:
+        out["tex_ind"] = np.array([v[0] for v in verts], dtype=np.uint16)
+        out["tex_pos"] = np.array([v[1] for v in verts], dtype=np.float32)
+        out["position"] = np.array([v[2] for v in verts], dtype=np.float32)
+        out["normal"] = np.array([v[3] for v in verts], dtype=np.float32)
     return out

@@ -181,6 +181,75 @@ def test_overlapping_batches_do_not_disturb_each_other(ocache):
             m.dev_free(do)
 
 
+def test_single_chunk_async_batches_mixed_with_larger_ones(ocache):
+    """n == 1 takes the fused single-CTA launch (analyse_kernel<., FUSED>); queued back to back with ordinary
+    launch pairs, without a finish in between, it must neither disturb their chunk tickets nor overwrite
+    hand-over buffers that an earlier launch still reads.  Whatever comes last must be exact."""
+    import mimas_b200
+    rng = np.random.RandomState(44)
+    big_c, big_o = mimas_b200.gen_terrain_host(78, (-8, -8, -2), (16, 16, 3))          # 768 chunks
+    cb_c, cb_o = checkerboard_chunks(3)
+    ones = [(np.full((1, 4096), 5, np.uint8), np.array([[16, 32, 48]], np.int64)),
+            (cb_c[:1], cb_o[:1]),
+            (rng.randint(0, 256, size=(1, 4096)).astype(np.uint8), np.array([[-160, 2 ** 30, 0]], np.int64)),
+            (G.cases["layered_terrain"]["chunk"][None], G.cases["layered_terrain"]["offs"][None])]
+    sets = ones + [(big_c, big_o), (cb_c, cb_o)]
+    want = [oracle.mesh_batch(c, o, ocache, threads=8) for c, o in sets]
+    with mimas_b200.Mesher(0, product_cache(G)) as m:
+        dev = []
+        for c, o in sets:
+            dc, do = m.dev_alloc(c.size), m.dev_alloc(o.size * 8)
+            m.upload(dc, np.ascontiguousarray(c))
+            m.upload(do, np.ascontiguousarray(o))
+            dev.append((dc, do, len(c)))
+        m.reserve(1024, 3 * 73728 + 768 * 4000, 4096 * 24)
+        for trial in range(12):
+            seq = list(rng.randint(0, len(sets), size=10))
+            seq += [int(rng.randint(0, 4))] * int(rng.randint(1, 4))     # a run of single-chunk batches ...
+            last = trial % len(sets)                                     # ... then the batch that is checked
+            for k in seq + [last]:
+                m.mesh_batch_async(*dev[k])
+            assert_batch_equal(m.copy_out(m.batch_finish()), want[last])
+        for dc, do, _ in dev:
+            m.dev_free(dc)
+            m.dev_free(do)
+
+
+def test_misaligned_device_chunks_are_rejected(mesher):
+    """The chunks are fetched with bulk async copies (16-byte aligned source): a misaligned device pointer is
+    an argument error, not a device fault that poisons the context."""
+    import ctypes as C
+    from mimas_b200._lib import lib
+    d = mesher.dev_alloc(2 * 4096 + 64)
+    try:
+        rc = lib().mm_mesh_batch_async(mesher._ctx, C.c_void_p(d + 8), C.c_void_p(d + 4096 + 16), 1)
+        assert rc == 1  # MM_ERR_INVALID
+        c = G.cases["single_stone_origin"]
+        m = mesher.mesh_for_chunk(c["offs"], c["chunk"])      # the context still works
+        assert first_diff(m.intransparent.tobytes(), c["intr"]) is None
+    finally:
+        mesher.dev_free(d)
+
+
+def test_misaligned_pinned_host_input(mesher, ocache):
+    """Pinned host chunks at an odd address: the mapped path copies them instead of reading them in place."""
+    buf = mesher.host_alloc(3 * 4096 + 3 * 24 + 64)
+    try:
+        rng = np.random.RandomState(5)
+        chunks = rng.randint(0, 60, size=(3, 4096)).astype(np.uint8)
+        offs = np.array([[0, 0, 0], [16, -16, 32], [-2 ** 24, 2 ** 24, 16]], np.int64)
+        buf[4:4 + chunks.size] = chunks.reshape(-1)
+        o0 = 4 + chunks.size + 4   # 8-byte aligned offset for the origins, chunks at +4
+        buf[o0:o0 + 72] = offs.reshape(-1).view(np.uint8)
+        hm = mesher.mesh_batch_host_raw(buf.ctypes.data + 4, buf.ctypes.data + o0, 3)
+        want = oracle.mesh_batch(chunks, offs, ocache, threads=2)
+        import ctypes as C
+        got = bytes((C.c_uint8 * (36 * hm.n_intransparent)).from_address(hm.intransparent)) if hm.n_intransparent else b""
+        assert first_diff(got, want["intransparent"].tobytes()) is None
+    finally:
+        mesher.host_free(buf)
+
+
 def test_full_size_terrain_batch_4096(mesher, ocache):
     """BASELINE.json configs[1] at full size: 4096 terrain chunks, every byte compared."""
     import mimas_b200

@@ -78,6 +78,19 @@ def test_cuda_culling_matches_restatement(mesher):
 
 
 @pytest.mark.gpu
+def test_cuda_culling_large_batch(mesher):
+    """60000 chunk origins: 1.4 MB of offsets and 240 KB of draw list, i.e. numpy buffers that live in mmap'ed
+    memory above 4 GiB -- every pointer must cross the ctypes boundary at full width (_lib.py argtypes)."""
+    rng = np.random.RandomState(10)
+    offs = (rng.randint(-60, 60, size=(60000, 3)) * 16).astype(np.int64)
+    cam = Camera(pos=(5.5, -3.25, 9.0), pitch=-10.0, yaw=77.0, viewing_range=600.0)
+    want = oracle.cull_chunks(offs, cam.get_matrix(), cam.get_perspective(), cam.pos, cam.viewing_range)
+    got = mesher.cull_chunks(offs, cam)
+    assert 1000 < len(want) < len(offs)
+    assert got.tolist() == want.tolist()
+
+
+@pytest.mark.gpu
 def test_cuda_draw_batch_matches_restatement(mesher):
     """One frame: cull the chunks of a meshed terrain region, shade the visible ones; every output byte equals
     culling + vertex stage of the restatement on the oracle-checked meshes."""
