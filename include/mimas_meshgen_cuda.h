@@ -140,11 +140,33 @@ int mm_reserve(mm_ctx *ctx, uint32_t max_chunks, uint64_t intransparent_vertices
 int mm_mesh_batch(mm_ctx *ctx, const uint8_t *chunks, const int64_t *offs,
                   const uint8_t *halo, uint32_t n, mm_batch_out *out);
 
-/* Stream-ordered variant for device-resident inputs: enqueues the mesher kernel and
- * returns immediately.  mm_batch_finish synchronises, grows + re-runs if the
- * arenas were too small, and reports totals.  Several _async calls may be queued
- * back to back; only the last one's result is retrievable. */
+/* Stream-ordered variant for device-resident inputs (16-byte aligned chunks, 8-byte aligned offs):
+ * enqueues the mesher kernels and returns immediately.  mm_batch_finish waits for the most recent
+ * batch, grows + re-runs it if its arenas were too small, and reports totals.  Several _async calls
+ * may be queued back to back: consecutive batches overlap on the device.  With the default ring of one
+ * output slot only the last one's result is retrievable; see mm_ring_configure / mm_mesh_batch_submit. */
 int mm_mesh_batch_async(mm_ctx *ctx, const uint8_t *d_chunks, const int64_t *d_offs, uint32_t n);
+
+/* Output ring (new; the batch submission path for mapgen chunks of the north star): `slots` (1..8) library-owned
+ * sets of arenas.  Every batch -- mm_mesh_batch_submit, and equally mm_mesh_batch / _async -- takes the next
+ * ticket t = 1, 2, ... and writes its packed streams and range records to slot t % slots, so up to `slots`
+ * batches are retrievable at once while later ones are being meshed.  mm_batch_wait(t) blocks until batch t has
+ * landed (the device signals completion per batch through mapped host memory: no stream synchronisation, the
+ * batches behind it keep running), grows + re-runs it if its slot was too small (its inputs must still be
+ * resident), and fills `out`; the pointers stay valid until ticket t + slots is submitted, after which
+ * mm_batch_wait(t) answers MM_ERR_NO_BATCH.  mm_reserve sizes every slot.  Reconfiguring drops outstanding tickets. */
+int mm_ring_configure(mm_ctx *ctx, uint32_t slots);
+int mm_mesh_batch_submit(mm_ctx *ctx, const uint8_t *d_chunks, const int64_t *d_offs, const uint8_t *d_halo, uint32_t n,
+                         uint64_t *ticket);
+/* k batches (repeated `repeat` >= 1 times round robin) enqueued by one call, so that a host language with slow
+ * foreign calls is not in the 30 us launch cadence; *first_ticket receives the first batch's ticket. */
+int mm_mesh_batches_submit(mm_ctx *ctx, const uint8_t *const *d_chunks, const int64_t *const *d_offs, const uint32_t *n,
+                           uint32_t k, uint32_t repeat, uint64_t *first_ticket);
+int mm_batch_wait(mm_ctx *ctx, uint64_t ticket, mm_batch_out *out);
+int mm_batch_poll(mm_ctx *ctx, uint64_t ticket, int *done);
+/* mm_copy_out for the batch of `ticket` (waits for it first), on the context's consumer stream. */
+int mm_copy_out_ticket(mm_ctx *ctx, uint64_t ticket, mm_vertex *intransparent, mm_vertex *transparent,
+                       mm_range *ranges_i, mm_range *ranges_t);
 /* The same with halo slabs (device memory, 16-byte aligned; NULL = mm_mesh_batch_async). */
 int mm_mesh_batch_halo_async(mm_ctx *ctx, const uint8_t *d_chunks, const int64_t *d_offs, const uint8_t *d_halo,
                              uint32_t n);
@@ -171,8 +193,11 @@ typedef struct mm_host_mesh {
 	const mm_range *ranges_t;
 	uint64_t n_intransparent, n_transparent;
 	uint32_t n_chunks;
-	uint32_t reserved;
+	uint32_t path;      /* MM_PATH_*: which host path the call took */
 } mm_host_mesh;
+#define MM_PATH_MAPPED 1u     /* small batch: kernels read and write mapped pinned host memory, no copies */
+#define MM_PATH_PIPELINED 2u  /* large batch cut into pieces: H2D, kernels and D2H overlap */
+#define MM_PATH_PLAIN 3u      /* H2D, kernels, D2H one after the other (first large call, or after an arena overflow) */
 int mm_mesh_batch_host(mm_ctx *ctx, const uint8_t *chunks, const int64_t *offs, uint32_t n,
                        mm_host_mesh *out);
 
@@ -253,6 +278,9 @@ int mm_cull_chunks(mm_ctx *ctx, const int64_t *offs, uint32_t n, const mm_camera
 /* one frame over the last finished device batch (mm_mesh_batch / mm_batch_finish): cull its chunks, shade the
  * visible ones.  Results stay in library-owned device memory until the next call. */
 int mm_draw_batch(mm_ctx *ctx, const mm_camera *cam, mm_draw_out *out);
+/* the same over the batch of a ring ticket (waits for it), on the context's consumer stream: batches queued
+ * behind it keep meshing while this one is drawn. */
+int mm_draw_ticket(mm_ctx *ctx, uint64_t ticket, const mm_camera *cam, mm_draw_out *out);
 
 /* What GL does with the shaded vertices, headless: primitive assembly, clipping, back-face culling
  * (CullCounterClockwise), rasterisation, depth test IfLess and the fragment shader

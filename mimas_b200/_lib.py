@@ -22,7 +22,8 @@ SYMBOLS = (
     "mm_gen_terrain_host", "mm_gen_terrain_device", "mm_dev_alloc", "mm_dev_free", "mm_dev_upload",
     "mm_dev_download", "mm_ctx_sync", "mm_device_info", "mm_host_alloc", "mm_host_free", "mm_launch_count",
     "mm_debug_trace", "mm_vertex_stage", "mm_cull_chunks", "mm_draw_batch", "mm_mesh_batch_halo_async",
-    "mm_gather_halos", "mm_set_textures", "mm_raster_frame",
+    "mm_gather_halos", "mm_set_textures", "mm_raster_frame", "mm_ring_configure", "mm_mesh_batch_submit",
+    "mm_mesh_batches_submit", "mm_batch_wait", "mm_batch_poll", "mm_copy_out_ticket", "mm_draw_ticket",
 )
 
 
@@ -79,6 +80,13 @@ def lib() -> C.CDLL:
     l.mm_debug_trace.argtypes = [vp, u32, vp, C.POINTER(u64)]
     l.mm_vertex_stage.argtypes = [vp, vp, u64, vp, vp]
     l.mm_draw_batch.argtypes = [vp, vp, vp]
+    l.mm_ring_configure.argtypes = [vp, u32]
+    l.mm_mesh_batch_submit.argtypes = [vp, vp, vp, vp, u32, C.POINTER(u64)]
+    l.mm_mesh_batches_submit.argtypes = [vp, vp, vp, vp, u32, u32, C.POINTER(u64)]
+    l.mm_batch_wait.argtypes = [vp, u64, vp]
+    l.mm_batch_poll.argtypes = [vp, u64, C.POINTER(C.c_int)]
+    l.mm_copy_out_ticket.argtypes = [vp, u64, vp, vp, vp, vp]
+    l.mm_draw_ticket.argtypes = [vp, u64, vp, vp]
     l.mm_abi_version.argtypes = []
     for s in SYMBOLS:
         f = getattr(l, s)

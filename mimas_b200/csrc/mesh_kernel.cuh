@@ -38,9 +38,6 @@ constexpr int kThreads = kWarpsPerCta * 32;
 #ifndef MM_EXPAND_MINBLOCKS
 #define MM_EXPAND_MINBLOCKS 3
 #endif
-#ifndef MM_EXPERIMENT_SKIP_EMIT
-#define MM_EXPERIMENT_SKIP_EMIT 0  // timing experiments only: leaves the descriptors unwritten
-#endif
 #ifndef MM_ANALYSE_UNIFORM_EXIT
 #define MM_ANALYSE_UNIFORM_EXIT 1
 #endif
@@ -72,7 +69,25 @@ struct ExpandParams {
 	u64 *totals;                  // [0] quads in out_i, [1] quad slots in out_t after this launch
 	u64 *host_totals;             // the same two words in mapped pinned host memory
 	u64 *trace;                   // NULL, or 4 words of this launch: first CTA start, first CTA past the wait, -, last CTA end (ns)
+	uint32_t *done_count;         // CTAs of this launch that have finished (the last one signals and resets it)
+	u64 *h_done;                  // NULL, or mapped pinned host word that receives done_ticket once every vertex has landed
+	u64 done_ticket;
 };
+
+// Called by every thread of a CTA after its last store has completed: the last CTA of the grid to get here tells
+// the host (mm_batch_wait polls the word), so that a batch can be handed to a consumer while later ones still run.
+__device__ __forceinline__ void signal_batch_done(uint32_t *done_count, u64 *h_done, u64 ticket, uint32_t ctas) {
+	if (h_done == nullptr) return;
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		__threadfence();
+		if (ctas == 1u || atomicAdd(done_count, 1u) == ctas - 1u) {
+			if (ctas != 1u) *done_count = 0;
+			__threadfence_system();
+			*reinterpret_cast<volatile u64 *>(h_done) = ticket;  // posted write; nothing waits for it here
+		}
+	}
+}
 
 struct AnalyseParams {
 	const unsigned char *chunks;  // n * 4096
@@ -294,7 +309,7 @@ __global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(co
 			// D. descriptors: thread <-> non-empty word (two rows)
 			const uint32_t nwords = run >> 16;
 #pragma unroll 1
-			for (uint32_t i = (uint32_t)tid; i < (MM_EXPERIMENT_SKIP_EMIT ? 0u : nwords); i += kThreads) {
+			for (uint32_t i = (uint32_t)tid; i < nwords; i += kThreads) {
 				const uint32_t e = smem_wl(s)[i];
 				const uint32_t widx = e & 1023u;
 				emit_word_descs<HALO>(s, widx, reinterpret_cast<const uint32_t *>(s.S)[widx], di + (e >> 10));
@@ -368,6 +383,7 @@ __global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(co
 			if (lane == 0) store_tile(g, sp, tn * kQuadBytes);
 		}
 		if (lane == 0) bulk_wait_all();
+		signal_batch_done(x.done_count, x.h_done, x.done_ticket, 1u);
 	}
 }
 
@@ -553,6 +569,7 @@ __global__ void __launch_bounds__(kExpandThreads, MM_EXPAND_MINBLOCKS) expand_ke
 		if (MM_EXPAND_PREFETCH) cur = nxt;
 	}
 	if (lane == 0) bulk_wait_all();  // all bulk stores of this warp have landed before it exits
+	signal_batch_done(p.done_count, p.h_done, p.done_ticket, gridDim.x);
 	if (tid == 0) trace_mark(p.trace, 3);
 }
 

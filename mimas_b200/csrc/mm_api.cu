@@ -12,6 +12,7 @@
 
 #include <algorithm>
 #include <new>
+#include <thread>
 #include <vector>
 
 #include "../../include/mimas_meshgen_cuda.h"
@@ -51,17 +52,31 @@ bool is_pinned_ptr(const void *p) {
 	return a.type == cudaMemoryTypeHost;
 }
 
-int ensure_chunk_capacity(mm_ctx *c, uint32_t n) {
-	if (n <= c->cap_chunks) return MM_OK;
+int ensure_chunk_capacity(mm_ctx *c, mm_slot *sl, uint32_t n) {
+	if (n <= sl->cap_chunks) return MM_OK;
 	const uint32_t nc = std::max<uint32_t>(n, 1024u);
 	MM_CUDA(c, cudaStreamSynchronize(c->stream));
-	cudaFree(c->d_ranges_i); cudaFree(c->d_ranges_t);
-	c->d_ranges_i = c->d_ranges_t = nullptr;
-	c->cap_chunks = 0;
-	MM_CUDA(c, cudaMalloc(&c->d_ranges_i, sizeof(mm::Range) * (size_t)nc));
-	MM_CUDA(c, cudaMalloc(&c->d_ranges_t, sizeof(mm::Range) * (size_t)nc));
-	c->cap_chunks = nc;
+	cudaFree(sl->d_ranges_i); cudaFree(sl->d_ranges_t);
+	sl->d_ranges_i = sl->d_ranges_t = nullptr;
+	sl->cap_chunks = 0;
+	MM_CUDA(c, cudaMalloc(&sl->d_ranges_i, sizeof(mm::Range) * (size_t)nc));
+	MM_CUDA(c, cudaMalloc(&sl->d_ranges_t, sizeof(mm::Range) * (size_t)nc));
+	sl->cap_chunks = nc;
 	return MM_OK;
+}
+
+int ensure_slot_totals(mm_ctx *c, mm_slot *sl) {  // the two mapped words a slot's totals reach the host through
+	if (sl->h_totals) return MM_OK;
+	MM_CUDA(c, cudaHostAlloc(&sl->h_totals, sizeof(mm::u64) * 2, cudaHostAllocMapped));
+	MM_CUDA(c, cudaHostGetDevicePointer((void **)&sl->d_h_totals, sl->h_totals, 0));
+	sl->h_totals[0] = sl->h_totals[1] = 0;
+	return MM_OK;
+}
+
+void free_slot(mm_slot *sl) {
+	cudaFree(sl->d_out_i); cudaFree(sl->d_out_t); cudaFree(sl->d_ranges_i); cudaFree(sl->d_ranges_t);
+	if (sl->h_totals) cudaFreeHost(sl->h_totals);
+	*sl = mm_slot();
 }
 
 int ensure_arena(mm_ctx *c, unsigned char **p, uint64_t *cap, uint64_t quads) {
@@ -122,18 +137,22 @@ int ensure_desc_capacity(mm_ctx *c, uint32_t n) {
 // previous one ended.
 // Nothing but kernels is enqueued for an untimed batch (the totals reach the host through mapped
 // pinned memory), so that back-to-back batches chain by programmatic dependent launch.
-struct Targets {  // where a batch's vertices and range records go
+struct Targets {  // where a batch's vertices, range records and totals go
 	unsigned char *out_i, *out_t;
 	uint64_t cap_i, cap_t;
 	mm::Range *ranges_i, *ranges_t;
+	mm::u64 *host_totals;  // mapped pinned, 2 words
 };
-Targets device_targets(const mm_ctx *c) { return Targets{c->d_out_i, c->d_out_t, c->cap_i, c->cap_t, c->d_ranges_i, c->d_ranges_t}; }
+Targets slot_targets(const mm_slot *sl) {
+	return Targets{sl->d_out_i, sl->d_out_t, sl->cap_i, sl->cap_t, sl->d_ranges_i, sl->d_ranges_t, sl->d_h_totals};
+}
 
+// `signal` != 0: the last kernel of the batch writes it to c->h_done once every vertex has landed (mm_batch_wait).
 int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, const unsigned char *d_halo, uint32_t n,
-           bool timed, const Targets &tg, const mm::u64 *carry0 = nullptr) {
+           bool timed, const Targets &tg, const mm::u64 *carry0 = nullptr, uint64_t signal = 0, uint32_t *launches = nullptr) {
 	int rc;
 	if ((rc = ensure_desc_capacity(c, n))) return rc;
-	c->last_timed = timed;
+	uint32_t launched = 0;
 	if (timed) MM_CUDA(c, cudaEventRecord(c->ev0, c->stream));
 	const mm::u64 *carry = carry0;  // totals of an earlier piece of the same batch, or NULL
 	for (uint32_t first = 0; first < n; first += mm::kMaxLaunchChunks) {
@@ -171,8 +190,11 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, co
 			e.ranges_i = tg.ranges_i; e.ranges_t = tg.ranges_t;
 			e.carry_in = nullptr;
 			e.totals = c->d_ticket + 2 + 2 * c->totals_slot;
-			e.host_totals = c->d_h_totals;
+			e.host_totals = tg.host_totals;
 			e.trace = nullptr;
+			e.done_count = c->d_done_count;
+			e.h_done = signal ? c->d_h_done : nullptr;
+			e.done_ticket = signal;
 			cudaLaunchConfig_t cfg = {};
 			cfg.gridDim = dim3(1);
 			cfg.blockDim = dim3(mm::kThreads);
@@ -181,7 +203,7 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, co
 			cfg.numAttrs = 1;
 			MM_CUDA(c, (cudaLaunchKernelEx(&cfg, mm::analyse_kernel<false, true>, a)));
 			// the fused form draws no tickets
-			c->last_launches += 1;
+			launched += 1;
 			c->total_launches += 1;
 			break;
 		}
@@ -193,10 +215,6 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, co
 			cfg.stream = c->stream;
 			cfg.attrs = attr;
 			cfg.numAttrs = 1;
-#if MM_EXPERIMENT_SKIP_ANALYSE  // timing experiments only: expansion alone, on stale descriptors
-			if (c->total_launches >= 64) {
-			} else
-#endif
 			if (d_halo) MM_CUDA(c, cudaLaunchKernelEx(&cfg, mm::analyse_kernel<true>, a));
 			else MM_CUDA(c, cudaLaunchKernelEx(&cfg, mm::analyse_kernel<false>, a));
 		}
@@ -218,8 +236,12 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, co
 		e.ranges_t = tg.ranges_t + first;
 		e.carry_in = carry;
 		e.totals = c->d_ticket + 2 + 2 * c->totals_slot;
-		e.host_totals = c->d_h_totals;
+		e.host_totals = tg.host_totals;
 		e.trace = tr ? tr + 4 : nullptr;
+		const bool last_pair = first + m >= n;
+		e.done_count = c->d_done_count;
+		e.h_done = signal && last_pair ? c->d_h_done : nullptr;
+		e.done_ticket = signal;
 		// programmatic dependent launch (see the kernels): analysis of batch k+1 beside expansion of batch k
 		cudaLaunchConfig_t cfg = {};
 		cfg.gridDim = dim3((unsigned)c->expand_grid);
@@ -230,11 +252,41 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, co
 		cfg.numAttrs = 1;
 		MM_CUDA(c, cudaLaunchKernelEx(&cfg, mm::expand_kernel, e));
 		carry = e.totals;
-		c->last_launches += 2;
+		launched += 2;
 		c->total_launches += 2;
 	}
 	if (timed) MM_CUDA(c, cudaEventRecord(c->ev1, c->stream));
+	if (launches) *launches += launched;
 	return MM_OK;
+}
+
+// Blocks until the device has signalled `seq` (written by the last kernel of a batch to mapped host memory).
+// The newest batch is simply waited for on the stream; an older one is polled for, so that the batches behind
+// it keep running.
+int wait_signal(mm_ctx *c, uint64_t seq) {
+	volatile mm::u64 *done = c->h_done;
+	if (c->no_signal) {  // MM_NO_SIGNAL: every wait is a stream synchronisation
+		MM_CUDA(c, cudaStreamSynchronize(c->stream));
+		return MM_OK;
+	}
+	if (*done >= seq) return MM_OK;
+	if (seq == c->last_signal_ticket) {
+		MM_CUDA(c, cudaStreamSynchronize(c->stream));
+		if (*done < seq) return fail(c, MM_ERR_CUDA, "batch %llu: stream idle but completion not signalled", (unsigned long long)seq);
+		return MM_OK;
+	}
+	for (uint32_t spin = 0;; spin++) {
+		if (*done >= seq) return MM_OK;
+		if ((spin & 1023u) == 1023u) {
+			const cudaError_t e = cudaStreamQuery(c->stream);
+			if (e == cudaSuccess) {
+				if (*done >= seq) return MM_OK;
+				return fail(c, MM_ERR_CUDA, "batch %llu: stream idle but completion not signalled", (unsigned long long)seq);
+			}
+			if (e != cudaErrorNotReady) return fail(c, MM_ERR_CUDA, "cudaStreamQuery: %s", cudaGetErrorString(e));
+		}
+		std::this_thread::yield();
+	}
 }
 
 }  // namespace
@@ -285,6 +337,7 @@ int mm_ctx_create(int device, mm_ctx **out) {
 		c->fuse_single = getenv("MM_NO_FUSED_SINGLE") == nullptr;
 		if (const char *e = getenv("MM_PIPE_MIN_CHUNKS")) c->pipe_min_chunks = (uint32_t)std::max(0, atoi(e));
 		c->no_small = getenv("MM_NO_SMALL_PATH") != nullptr;
+		c->no_signal = getenv("MM_NO_SIGNAL") != nullptr;
 		if (const char *e = getenv("MM_MAPPED_MAX_CHUNKS")) c->mapped_max_chunks = (uint32_t)strtoul(e, nullptr, 10);
 		MM_CUDA(c, cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
 		c->stream = c->own_stream;
@@ -296,8 +349,16 @@ int mm_ctx_create(int device, mm_ctx **out) {
 		MM_CUDA(c, cudaMalloc(&c->d_flags, 256));
 		MM_CUDA(c, cudaMalloc(&c->d_cnt, sizeof(uint32_t) * 4 * mm::kMaxLaunchChunks));
 		MM_CUDA(c, cudaMemset(c->d_cnt, 0, sizeof(uint32_t) * 4 * mm::kMaxLaunchChunks));
-		MM_CUDA(c, cudaHostAlloc(&c->h_totals, sizeof(mm::u64) * 2, cudaHostAllocMapped));
-		MM_CUDA(c, cudaHostGetDevicePointer((void **)&c->d_h_totals, c->h_totals, 0));
+		{
+			const int rs = ensure_slot_totals(c, &c->ring[0]);
+			if (rs) return rs;
+		}
+		MM_CUDA(c, cudaHostAlloc(&c->h_done, sizeof(mm::u64), cudaHostAllocMapped));
+		MM_CUDA(c, cudaHostGetDevicePointer((void **)&c->d_h_done, c->h_done, 0));
+		*c->h_done = 0;
+		MM_CUDA(c, cudaMalloc(&c->d_done_count, sizeof(uint32_t)));
+		MM_CUDA(c, cudaMemset(c->d_done_count, 0, sizeof(uint32_t)));
+		MM_CUDA(c, cudaStreamCreateWithFlags(&c->s_draw, cudaStreamNonBlocking));
 		return MM_OK;
 	};
 	rc = body();
@@ -314,10 +375,13 @@ int mm_ctx_destroy(mm_ctx *c) {
 	if (!c) return MM_ERR_INVALID;
 	cudaSetDevice(c->device);
 	if (c->own_stream) cudaStreamSynchronize(c->own_stream);
-	cudaFree(c->d_table); cudaFree(c->d_out_i); cudaFree(c->d_out_t); cudaFree(c->d_ranges_i);
-	cudaFree(c->d_ranges_t); cudaFree(c->d_cnt); cudaFree(c->d_desc_i); cudaFree(c->d_desc_t); cudaFree(c->d_flags); cudaFree(c->d_ticket);
+	if (c->s_draw) cudaStreamSynchronize(c->s_draw);
+	for (uint32_t k = 0; k < kMaxRingSlots; k++) free_slot(&c->ring[k]);
+	cudaFree(c->d_table); cudaFree(c->d_cnt); cudaFree(c->d_desc_i); cudaFree(c->d_desc_t); cudaFree(c->d_flags); cudaFree(c->d_ticket);
+	cudaFree(c->d_done_count);
+	if (c->h_done) cudaFreeHost(c->h_done);
+	if (c->s_draw) cudaStreamDestroy(c->s_draw);
 	cudaFree(c->d_in_chunks); cudaFree(c->d_in_offs); cudaFree(c->d_in_halo); cudaFree(c->d_trace);
-	if (c->h_totals) cudaFreeHost(c->h_totals);
 	if (c->h_in) cudaFreeHost(c->h_in);
 	if (c->h_small) cudaFreeHost(c->h_small);
 	if (c->h_draw_totals) cudaFreeHost(c->h_draw_totals);
@@ -424,17 +488,34 @@ int mm_reserve(mm_ctx *c, uint32_t max_chunks, uint64_t iv, uint64_t tv) {
 	if (!c) return MM_ERR_INVALID;
 	if (use_device(c)) return MM_ERR_CUDA;
 	int rc;
-	if ((rc = ensure_chunk_capacity(c, max_chunks))) return rc;
-	if ((rc = ensure_arena(c, &c->d_out_i, &c->cap_i, (iv + 5) / 6))) return rc;
-	if ((rc = ensure_arena(c, &c->d_out_t, &c->cap_t, (tv + 5) / 6))) return rc;
+	for (uint32_t k = 0; k < c->ring_slots; k++) {  // every slot of the ring: a batch may land in any of them
+		mm_slot *sl = &c->ring[k];
+		if ((rc = ensure_chunk_capacity(c, sl, max_chunks))) return rc;
+		if ((rc = ensure_arena(c, &sl->d_out_i, &sl->cap_i, (iv + 5) / 6))) return rc;
+		if ((rc = ensure_arena(c, &sl->d_out_t, &sl->cap_t, (tv + 5) / 6))) return rc;
+	}
 	return MM_OK;
 }
 
-int mm_mesh_batch_async(mm_ctx *c, const uint8_t *d_chunks, const int64_t *d_offs, uint32_t n) {
-	return mm_mesh_batch_halo_async(c, d_chunks, d_offs, nullptr, n);
+int mm_ring_configure(mm_ctx *c, uint32_t slots) {
+	if (!c || slots < 1 || slots > kMaxRingSlots) return MM_ERR_INVALID;
+	if (use_device(c)) return MM_ERR_CUDA;
+	MM_CUDA(c, cudaStreamSynchronize(c->stream));
+	int rc;
+	for (uint32_t k = slots; k < kMaxRingSlots; k++) free_slot(&c->ring[k]);
+	for (uint32_t k = 0; k < slots; k++) {
+		mm_slot *sl = &c->ring[k];
+		if ((rc = ensure_slot_totals(c, sl))) return rc;
+		sl->ticket = 0;  // outstanding tickets do not survive a reconfiguration
+		sl->pending = sl->finished = false;
+	}
+	c->ring_slots = slots;
+	c->cur = &c->ring[0];
+	return MM_OK;
 }
 
-int mm_mesh_batch_halo_async(mm_ctx *c, const uint8_t *d_chunks, const int64_t *d_offs, const uint8_t *d_halo, uint32_t n) {
+// One batch into the next slot of the ring; returns its ticket.
+static int submit(mm_ctx *c, const uint8_t *d_chunks, const int64_t *d_offs, const uint8_t *d_halo, uint32_t n, uint64_t *ticket) {
 	if (!c || (n && (!d_chunks || !d_offs))) return MM_ERR_INVALID;
 	// the chunks are fetched by bulk async copies, the halo rows as 16-byte loads
 	if (n && ((uintptr_t)d_chunks & 15u)) return fail(c, MM_ERR_INVALID, "chunks must be 16-byte aligned");
@@ -442,58 +523,140 @@ int mm_mesh_batch_halo_async(mm_ctx *c, const uint8_t *d_chunks, const int64_t *
 	if (d_halo && ((uintptr_t)d_halo & 15u)) return fail(c, MM_ERR_INVALID, "halo must be 16-byte aligned");
 	if (!c->have_table) return fail(c, MM_ERR_NO_TABLE, "mm_set_block_table has not been called");
 	if (use_device(c)) return MM_ERR_CUDA;
-	c->finished = false;
-	c->pending = false;
-	c->last_chunks = d_chunks;
-	c->last_offs = (const long long *)d_offs;
-	c->last_halo = d_halo;
-	c->last_n = n;
-	c->last_launches = 0;
-	c->tot_i = c->tot_t = 0;
-	if (n == 0) { c->pending = true; return MM_OK; }
+	const uint64_t t = c->next_ticket;
+	mm_slot *sl = &c->ring[t % c->ring_slots];
 	int rc;
-	if ((rc = ensure_chunk_capacity(c, n))) return rc;
-	if ((rc = launch(c, d_chunks, c->last_offs, d_halo, n, c->time_next, device_targets(c)))) return rc;
+	if ((rc = ensure_slot_totals(c, sl))) return rc;
+	if (n && (rc = ensure_chunk_capacity(c, sl, n))) return rc;
+	sl->finished = false;
+	sl->pending = false;
+	sl->last_chunks = d_chunks;
+	sl->last_offs = (const long long *)d_offs;
+	sl->last_halo = d_halo;
+	sl->last_n = n;
+	sl->last_launches = 0;
+	sl->tot_i = sl->tot_t = 0;
+	sl->last_timed = c->time_next;
+	sl->wait_ticket = c->last_signal_ticket;  // an empty batch is complete when everything before it is
+	if (n) {
+		const uint64_t seq = c->no_signal ? 0 : c->last_signal_ticket + 1;  // completion signals count on their own: a re-run takes one too
+		if ((rc = launch(c, d_chunks, sl->last_offs, d_halo, n, c->time_next, slot_targets(sl), nullptr, seq, &sl->last_launches))) return rc;
+		if (seq) sl->wait_ticket = c->last_signal_ticket = seq;
+	}
 	c->time_next = false;
-	c->pending = true;
+	sl->ticket = t;
+	sl->pending = true;
+	c->cur = sl;
+	c->next_ticket = t + 1;
+	if (ticket) *ticket = t;
+	return MM_OK;
+}
+
+int mm_mesh_batch_async(mm_ctx *c, const uint8_t *d_chunks, const int64_t *d_offs, uint32_t n) {
+	return submit(c, d_chunks, d_offs, nullptr, n, nullptr);
+}
+
+int mm_mesh_batch_halo_async(mm_ctx *c, const uint8_t *d_chunks, const int64_t *d_offs, const uint8_t *d_halo, uint32_t n) {
+	return submit(c, d_chunks, d_offs, d_halo, n, nullptr);
+}
+
+int mm_mesh_batch_submit(mm_ctx *c, const uint8_t *d_chunks, const int64_t *d_offs, const uint8_t *d_halo, uint32_t n,
+                         uint64_t *ticket) {
+	if (!ticket) return MM_ERR_INVALID;
+	return submit(c, d_chunks, d_offs, d_halo, n, ticket);
+}
+
+int mm_mesh_batches_submit(mm_ctx *c, const uint8_t *const *d_chunks, const int64_t *const *d_offs, const uint32_t *n,
+                           uint32_t k, uint32_t repeat, uint64_t *first_ticket) {
+	if (!c || !d_chunks || !d_offs || !n || !k) return MM_ERR_INVALID;
+	uint64_t first = 0;
+	for (uint32_t r = 0; r < std::max<uint32_t>(repeat, 1u); r++)
+		for (uint32_t i = 0; i < k; i++) {
+			uint64_t t = 0;
+			const int rc = submit(c, d_chunks[i], d_offs[i], nullptr, n[i], &t);
+			if (rc) return rc;
+			if (!first) first = t;
+		}
+	if (first_ticket) *first_ticket = first;
+	return MM_OK;
+}
+
+static void fill_batch_out(const mm_ctx *, const mm_slot *sl, mm_batch_out *out) {
+	memset(out, 0, sizeof(*out));
+	out->d_intransparent = (const mm_vertex *)sl->d_out_i;
+	out->d_transparent = (const mm_vertex *)sl->d_out_t;
+	out->d_ranges_i = (const mm_range *)sl->d_ranges_i;
+	out->d_ranges_t = (const mm_range *)sl->d_ranges_t;
+	out->n_intransparent = sl->tot_i * 6;
+	out->n_transparent = sl->tot_t * 6;
+	out->n_chunks = sl->last_n;
+	out->launches = sl->last_launches;
+	out->kernel_ms = sl->last_ms;
+}
+
+// Completes the batch a slot holds: waits for its kernels, and if the slot's arenas were too small grows them
+// and runs the batch again (its inputs must still be resident).
+static int finish_slot(mm_ctx *c, mm_slot *sl) {
+	if (sl->last_n) {
+		for (int attempt = 0;; attempt++) {
+			int rc;
+			if ((rc = wait_signal(c, sl->wait_ticket))) return rc;
+			sl->tot_i = sl->h_totals[0];
+			sl->tot_t = sl->h_totals[1];
+			if (sl->tot_i <= sl->cap_i && sl->tot_t <= sl->cap_t) break;
+			if (attempt >= 1) return fail(c, MM_ERR_CUDA, "arena still too small after growth");
+			// grow to fit (+1/8 head room) and run again: the inputs are still resident
+			if ((rc = ensure_arena(c, &sl->d_out_i, &sl->cap_i, sl->tot_i + sl->tot_i / 8))) return rc;
+			if ((rc = ensure_arena(c, &sl->d_out_t, &sl->cap_t, sl->tot_t + sl->tot_t / 8))) return rc;
+			const uint64_t again = c->no_signal ? 0 : c->last_signal_ticket + 1;
+			if ((rc = launch(c, sl->last_chunks, sl->last_offs, sl->last_halo, sl->last_n, sl->last_timed, slot_targets(sl), nullptr,
+			                 again, &sl->last_launches)))
+				return rc;
+			if (again) sl->wait_ticket = c->last_signal_ticket = again;
+		}
+		sl->last_ms = 0.f;  // an untimed (mm_mesh_batch_async) batch enqueues kernels only
+		if (sl->last_timed) {
+			MM_CUDA(c, cudaEventSynchronize(c->ev1));
+			MM_CUDA(c, cudaEventElapsedTime(&sl->last_ms, c->ev0, c->ev1));
+		}
+	} else {
+		int rc;
+		if ((rc = wait_signal(c, sl->wait_ticket))) return rc;
+		sl->last_ms = 0.f;
+	}
+	sl->pending = false;
+	sl->finished = true;
 	return MM_OK;
 }
 
 int mm_batch_finish(mm_ctx *c, mm_batch_out *out) {
 	if (!c) return MM_ERR_INVALID;
-	if (!c->pending) return fail(c, MM_ERR_NO_BATCH, "no batch in flight");
+	mm_slot *sl = c->cur;
+	if (!sl->pending) return fail(c, MM_ERR_NO_BATCH, "no batch in flight");
 	if (use_device(c)) return MM_ERR_CUDA;
-	if (c->last_n) {
-		for (int attempt = 0;; attempt++) {
-			MM_CUDA(c, cudaStreamSynchronize(c->stream));
-			c->tot_i = c->h_totals[0];
-			c->tot_t = c->h_totals[1];
-			if (c->tot_i <= c->cap_i && c->tot_t <= c->cap_t) break;
-			if (attempt >= 1) return fail(c, MM_ERR_CUDA, "arena still too small after growth");
-			int rc;  // grow to fit (+1/8 head room) and run again: the inputs are still resident
-			if ((rc = ensure_arena(c, &c->d_out_i, &c->cap_i, c->tot_i + c->tot_i / 8))) return rc;
-			if ((rc = ensure_arena(c, &c->d_out_t, &c->cap_t, c->tot_t + c->tot_t / 8))) return rc;
-			if ((rc = launch(c, c->last_chunks, c->last_offs, c->last_halo, c->last_n, c->last_timed, device_targets(c)))) return rc;
-		}
-		c->last_ms = 0.f;  // an untimed (mm_mesh_batch_async) batch enqueues kernels only
-		if (c->last_timed) MM_CUDA(c, cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1));
-	} else {
-		c->last_ms = 0.f;
-	}
-	c->pending = false;
-	c->finished = true;
-	if (out) {
-		memset(out, 0, sizeof(*out));
-		out->d_intransparent = (const mm_vertex *)c->d_out_i;
-		out->d_transparent = (const mm_vertex *)c->d_out_t;
-		out->d_ranges_i = (const mm_range *)c->d_ranges_i;
-		out->d_ranges_t = (const mm_range *)c->d_ranges_t;
-		out->n_intransparent = c->tot_i * 6;
-		out->n_transparent = c->tot_t * 6;
-		out->n_chunks = c->last_n;
-		out->launches = c->last_launches;
-		out->kernel_ms = c->last_ms;
-	}
+	int rc;
+	if ((rc = finish_slot(c, sl))) return rc;
+	if (out) fill_batch_out(c, sl, out);
+	return MM_OK;
+}
+
+int mm_batch_wait(mm_ctx *c, uint64_t ticket, mm_batch_out *out) {
+	if (!c || !ticket) return MM_ERR_INVALID;
+	mm_slot *sl = &c->ring[ticket % c->ring_slots];
+	if (sl->ticket != ticket) return fail(c, MM_ERR_NO_BATCH, "ticket %llu is not in the ring (slot reused or never submitted)", (unsigned long long)ticket);
+	if (use_device(c)) return MM_ERR_CUDA;
+	int rc;
+	if (sl->pending && (rc = finish_slot(c, sl))) return rc;
+	if (out) fill_batch_out(c, sl, out);
+	return MM_OK;
+}
+
+int mm_batch_poll(mm_ctx *c, uint64_t ticket, int *done) {
+	if (!c || !ticket || !done) return MM_ERR_INVALID;
+	const mm_slot *sl = &c->ring[ticket % c->ring_slots];
+	if (sl->ticket != ticket) return fail(c, MM_ERR_NO_BATCH, "ticket %llu is not in the ring", (unsigned long long)ticket);
+	if (c->no_signal) *done = !sl->pending || cudaStreamQuery(c->stream) == cudaSuccess;
+	else *done = !sl->pending || *(volatile mm::u64 *)c->h_done >= sl->wait_ticket;
 	return MM_OK;
 }
 
@@ -530,20 +693,39 @@ int mm_mesh_batch(mm_ctx *c, const uint8_t *chunks, const int64_t *offs, const u
 	}
 	int rc;
 	c->time_next = true;  // the synchronous call brackets its kernels with events: mm_batch_out.kernel_ms
-	if ((rc = mm_mesh_batch_halo_async(c, dc, dof, dh, n))) return rc;
+	if ((rc = submit(c, dc, dof, dh, n, nullptr))) {
+		c->time_next = false;
+		return rc;
+	}
 	return mm_batch_finish(c, out);
+}
+
+// Copies the batch of slot `sl` to the host (any pointer may be NULL) on `stream` and waits for the copies.
+static int copy_slot(mm_ctx *c, const mm_slot *sl, cudaStream_t stream, mm_vertex *vi, mm_vertex *vt, mm_range *ri, mm_range *rt) {
+	if (vi && sl->tot_i) MM_CUDA(c, cudaMemcpyAsync(vi, sl->d_out_i, sl->tot_i * mm::kQuadBytes, cudaMemcpyDeviceToHost, stream));
+	if (vt && sl->tot_t) MM_CUDA(c, cudaMemcpyAsync(vt, sl->d_out_t, sl->tot_t * mm::kQuadBytes, cudaMemcpyDeviceToHost, stream));
+	if (ri && sl->last_n) MM_CUDA(c, cudaMemcpyAsync(ri, sl->d_ranges_i, (size_t)sl->last_n * 16, cudaMemcpyDeviceToHost, stream));
+	if (rt && sl->last_n) MM_CUDA(c, cudaMemcpyAsync(rt, sl->d_ranges_t, (size_t)sl->last_n * 16, cudaMemcpyDeviceToHost, stream));
+	MM_CUDA(c, cudaStreamSynchronize(stream));
+	return MM_OK;
 }
 
 int mm_copy_out(mm_ctx *c, mm_vertex *vi, mm_vertex *vt, mm_range *ri, mm_range *rt) {
 	if (!c) return MM_ERR_INVALID;
-	if (!c->finished) return fail(c, MM_ERR_NO_BATCH, "no finished batch");
+	if (!c->cur->finished) return fail(c, MM_ERR_NO_BATCH, "no finished batch");
 	if (use_device(c)) return MM_ERR_CUDA;
-	if (vi && c->tot_i) MM_CUDA(c, cudaMemcpyAsync(vi, c->d_out_i, c->tot_i * mm::kQuadBytes, cudaMemcpyDeviceToHost, c->stream));
-	if (vt && c->tot_t) MM_CUDA(c, cudaMemcpyAsync(vt, c->d_out_t, c->tot_t * mm::kQuadBytes, cudaMemcpyDeviceToHost, c->stream));
-	if (ri && c->last_n) MM_CUDA(c, cudaMemcpyAsync(ri, c->d_ranges_i, (size_t)c->last_n * 16, cudaMemcpyDeviceToHost, c->stream));
-	if (rt && c->last_n) MM_CUDA(c, cudaMemcpyAsync(rt, c->d_ranges_t, (size_t)c->last_n * 16, cudaMemcpyDeviceToHost, c->stream));
-	MM_CUDA(c, cudaStreamSynchronize(c->stream));
-	return MM_OK;
+	return copy_slot(c, c->cur, c->stream, vi, vt, ri, rt);
+}
+
+int mm_copy_out_ticket(mm_ctx *c, uint64_t ticket, mm_vertex *vi, mm_vertex *vt, mm_range *ri, mm_range *rt) {
+	if (!c || !ticket) return MM_ERR_INVALID;
+	mm_slot *sl = &c->ring[ticket % c->ring_slots];
+	if (sl->ticket != ticket) return fail(c, MM_ERR_NO_BATCH, "ticket %llu is not in the ring", (unsigned long long)ticket);
+	if (use_device(c)) return MM_ERR_CUDA;
+	int rc;
+	if (sl->pending && (rc = finish_slot(c, sl))) return rc;
+	// on the consumers' stream: the batches queued behind this one keep meshing meanwhile
+	return copy_slot(c, sl, c->s_draw, vi, vt, ri, rt);
 }
 
 // The mapped path.  Small batches (the reference's own call pattern is one chunk per call,
@@ -599,13 +781,14 @@ static int small_batch_host(mm_ctx *c, const uint8_t *chunks, const int64_t *off
 			d_chunks = c->d_small + L.chunks;
 			d_offs = (const long long *)(c->d_small + L.offs);
 		}
+		mm_slot *sl = c->cur;
 		Targets tg{c->d_small + L.out_i, c->d_small + L.out_t, c->mapped_qi, c->mapped_qt,
-		           (mm::Range *)(c->d_small + L.ranges_i), (mm::Range *)(c->d_small + L.ranges_t)};
-		c->pending = c->finished = false;  // the device arenas hold no batch of this call
-		c->last_launches = 0;
+		           (mm::Range *)(c->d_small + L.ranges_i), (mm::Range *)(c->d_small + L.ranges_t), sl->d_h_totals};
+		sl->pending = sl->finished = false;  // the device arenas hold no batch of this call
+		sl->ticket = 0;
 		if ((rc = launch(c, d_chunks, d_offs, nullptr, n, false, tg))) return rc;
 		MM_CUDA(c, cudaStreamSynchronize(c->stream));
-		const uint64_t ti = c->h_totals[0], tt = c->h_totals[1];
+		const uint64_t ti = sl->h_totals[0], tt = sl->h_totals[1];
 		if (ti > c->mapped_qi || tt > c->mapped_qt) {  // nothing was written: grow the mapped arenas and run again
 			if (attempt >= 1) return MM_OK;
 			const MappedLayout G(c->mapped_chunks, std::max(c->mapped_qi, ti + ti / 8), std::max(c->mapped_qt, tt + tt / 8));
@@ -622,7 +805,7 @@ static int small_batch_host(mm_ctx *c, const uint8_t *chunks, const int64_t *off
 		out->n_intransparent = ti * 6;
 		out->n_transparent = tt * 6;
 		out->n_chunks = n;
-		out->reserved = 0;
+		out->path = MM_PATH_MAPPED;
 		*done = true;
 		return MM_OK;
 	}
@@ -638,17 +821,18 @@ static int small_batch_host(mm_ctx *c, const uint8_t *chunks, const int64_t *off
 static int pipelined_batch_host(mm_ctx *c, const uint8_t *hc, const int64_t *ho, uint32_t n, mm_host_mesh *out, bool *done) {
 	*done = false;
 	if (!c->have_table) return fail(c, MM_ERR_NO_TABLE, "mm_set_block_table has not been called");
-	if (!c->cap_i && !c->cap_t) return MM_OK;
+	mm_slot *sl = c->cur;
+	if (!sl->cap_i && !sl->cap_t) return MM_OK;
 	if (c->host_qi_per_chunk < 0.0) return MM_OK;  // no earlier host batch to size the pinned result by
 	int rc;
 	if ((rc = ensure_in_capacity(c, n))) return rc;
-	if ((rc = ensure_chunk_capacity(c, n))) return rc;
+	if ((rc = ensure_chunk_capacity(c, sl, n))) return rc;
 	const auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
 	const size_t br = (size_t)n * 16;
 	// room in the pinned result: what the last host batch needed per chunk plus a quarter, never more than the
 	// device arenas hold (those may be far larger after a big device-resident batch)
-	const uint64_t room_i = std::min<uint64_t>(c->cap_i, (uint64_t)(c->host_qi_per_chunk * 1.25 * n) + 4096);
-	const uint64_t room_t = std::min<uint64_t>(c->cap_t, (uint64_t)(c->host_qt_per_chunk * 1.25 * n) + 4096);
+	const uint64_t room_i = std::min<uint64_t>(sl->cap_i, (uint64_t)(c->host_qi_per_chunk * 1.25 * n) + 4096);
+	const uint64_t room_t = std::min<uint64_t>(sl->cap_t, (uint64_t)(c->host_qt_per_chunk * 1.25 * n) + 4096);
 	const size_t oi = 0, ot = up(room_i * mm::kQuadBytes), ori = up(ot + room_t * mm::kQuadBytes), ort = ori + up(br);
 	if ((rc = ensure_pinned(c, &c->h_out, &c->h_out_bytes, ort + br + 256))) return rc;
 	if (!c->s_in) {
@@ -669,26 +853,29 @@ static int pipelined_batch_host(mm_ctx *c, const uint8_t *hc, const int64_t *ho,
 	};
 	for (uint32_t k = 0; k < std::min(pieces, ahead); k++)
 		if ((rc = send(k))) return rc;
-	c->pending = c->finished = false;
-	c->last_launches = 0;
+	sl->pending = sl->finished = false;
+	sl->ticket = 0;
+	sl->last_launches = 0;
 	const mm::u64 *carry = nullptr;
 	uint64_t pi = 0, pt = 0;  // quads already on their way back
 	bool fits = true;
 	for (uint32_t k = 0; k < pieces && fits; k++) {
 		const uint32_t first = k * piece, m = std::min(piece, n - first);
 		MM_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_in[k % ahead], 0));
-		const Targets tg{c->d_out_i, c->d_out_t, c->cap_i, c->cap_t, c->d_ranges_i + first, c->d_ranges_t + first};
-		if ((rc = launch(c, c->d_in_chunks + (size_t)first * 4096, c->d_in_offs + (size_t)first * 3, nullptr, m, false, tg, carry))) return rc;
+		const Targets tg{sl->d_out_i, sl->d_out_t, sl->cap_i, sl->cap_t, sl->d_ranges_i + first, sl->d_ranges_t + first, sl->d_h_totals};
+		if ((rc = launch(c, c->d_in_chunks + (size_t)first * 4096, c->d_in_offs + (size_t)first * 3, nullptr, m, false, tg, carry, 0,
+		                 &sl->last_launches)))
+			return rc;
 		carry = c->d_ticket + 2 + 2 * c->totals_slot;
 		MM_CUDA(c, cudaStreamSynchronize(c->stream));
 		if (k + ahead < pieces && (rc = send(k + ahead))) return rc;  // its event is free again
-		const uint64_t ti = c->h_totals[0], tt = c->h_totals[1];
+		const uint64_t ti = sl->h_totals[0], tt = sl->h_totals[1];
 		if (ti > room_i || tt > room_t) {
 			fits = false;
 			break;
 		}
-		if (ti > pi) MM_CUDA(c, cudaMemcpyAsync(c->h_out + oi + pi * mm::kQuadBytes, c->d_out_i + pi * mm::kQuadBytes, (ti - pi) * mm::kQuadBytes, cudaMemcpyDeviceToHost, c->s_out));
-		if (tt > pt) MM_CUDA(c, cudaMemcpyAsync(c->h_out + ot + pt * mm::kQuadBytes, c->d_out_t + pt * mm::kQuadBytes, (tt - pt) * mm::kQuadBytes, cudaMemcpyDeviceToHost, c->s_out));
+		if (ti > pi) MM_CUDA(c, cudaMemcpyAsync(c->h_out + oi + pi * mm::kQuadBytes, sl->d_out_i + pi * mm::kQuadBytes, (ti - pi) * mm::kQuadBytes, cudaMemcpyDeviceToHost, c->s_out));
+		if (tt > pt) MM_CUDA(c, cudaMemcpyAsync(c->h_out + ot + pt * mm::kQuadBytes, sl->d_out_t + pt * mm::kQuadBytes, (tt - pt) * mm::kQuadBytes, cudaMemcpyDeviceToHost, c->s_out));
 		pi = ti;
 		pt = tt;
 	}
@@ -697,18 +884,18 @@ static int pipelined_batch_host(mm_ctx *c, const uint8_t *hc, const int64_t *ho,
 		MM_CUDA(c, cudaStreamSynchronize(c->s_out));
 		return MM_OK;
 	}
-	MM_CUDA(c, cudaMemcpyAsync(c->h_out + ori, c->d_ranges_i, br, cudaMemcpyDeviceToHost, c->s_out));
-	MM_CUDA(c, cudaMemcpyAsync(c->h_out + ort, c->d_ranges_t, br, cudaMemcpyDeviceToHost, c->s_out));
+	MM_CUDA(c, cudaMemcpyAsync(c->h_out + ori, sl->d_ranges_i, br, cudaMemcpyDeviceToHost, c->s_out));
+	MM_CUDA(c, cudaMemcpyAsync(c->h_out + ort, sl->d_ranges_t, br, cudaMemcpyDeviceToHost, c->s_out));
 	MM_CUDA(c, cudaStreamSynchronize(c->s_out));
-	c->tot_i = pi;
-	c->tot_t = pt;
-	c->last_chunks = c->d_in_chunks;
-	c->last_offs = c->d_in_offs;
-	c->last_halo = nullptr;
-	c->last_n = n;
-	c->last_ms = 0.f;
-	c->last_timed = false;
-	c->finished = true;  // the device arenas hold this batch: mm_copy_out works
+	sl->tot_i = pi;
+	sl->tot_t = pt;
+	sl->last_chunks = c->d_in_chunks;
+	sl->last_offs = c->d_in_offs;
+	sl->last_halo = nullptr;
+	sl->last_n = n;
+	sl->last_ms = 0.f;
+	sl->last_timed = false;
+	sl->finished = true;  // the device arenas hold this batch: mm_copy_out works
 	c->host_qi_per_chunk = (double)pi / n;
 	c->host_qt_per_chunk = (double)pt / n;
 	out->intransparent = (const mm_vertex *)(c->h_out + oi);
@@ -718,7 +905,7 @@ static int pipelined_batch_host(mm_ctx *c, const uint8_t *hc, const int64_t *ho,
 	out->n_intransparent = pi * 6;
 	out->n_transparent = pt * 6;
 	out->n_chunks = n;
-	out->reserved = 0;
+	out->path = MM_PATH_PIPELINED;
 	*done = true;
 	return MM_OK;
 }
@@ -764,7 +951,7 @@ int mm_mesh_batch_host(mm_ctx *c, const uint8_t *chunks, const int64_t *offs, ui
 	out->n_intransparent = bo.n_intransparent;
 	out->n_transparent = bo.n_transparent;
 	out->n_chunks = n;
-	out->reserved = 0;
+	out->path = MM_PATH_PLAIN;
 	if (n) {
 		c->host_qi_per_chunk = (double)(bo.n_intransparent / 6) / n;
 		c->host_qt_per_chunk = (double)(bo.n_transparent / 6) / n;

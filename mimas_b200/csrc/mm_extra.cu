@@ -41,46 +41,9 @@ __global__ void push_blocks_kernel(const mm_cube *cubes, const uint32_t *base, u
 }
 
 // ---- terrain generator ---------------------------------------------------------------------
-struct Region {
-	uint64_t seed;
-	long long cx0, cy0, cz0;
-	uint32_t nx, ny, nz;
-};
-
-// leaves (into air only), then trunk / cactus: shared by the host loop and the device kernel
-TG_HD void tree_leaves(uint8_t *chunk, int x, int y, int base, const tg::Column &ci) {
-	if (ci.tree != 1) return;
-	for (int dz = 3; dz <= 5; dz++) {
-		const int r = dz < 5 ? 1 : 0;
-		for (int dx = -r; dx <= r; dx++)
-			for (int dy = -r; dy <= r; dy++) {
-				uint8_t *p = &chunk[(x + dx) * 256 + (y + dy) * 16 + base + dz];
-				if (*p == tg::AIR) *p = tg::LEAVES;
-			}
-	}
-}
-TG_HD void tree_trunk(uint8_t *chunk, int x, int y, int base, const tg::Column &ci) {
-	const int h = ci.tree == 1 ? 4 : 3;
-	for (int dz = 0; dz < h; dz++) chunk[x * 256 + y * 16 + base + dz] = ci.tree == 1 ? tg::TREE : tg::CACTUS;
-}
-
-void gen_chunk_host(const Region &rg, uint32_t i, uint8_t *chunk, long long *offs) {
-	const long long cx = rg.cx0 + (long long)(i % rg.nx), cy = rg.cy0 + (long long)((i / rg.nx) % rg.ny),
-	                cz = rg.cz0 + (long long)(i / (rg.nx * rg.ny));
-	const long long ox = cx * 16, oy = cy * 16, oz = cz * 16;
-	offs[0] = ox; offs[1] = oy; offs[2] = oz;
-	tg::Column cols[256];
-	for (int x = 0; x < 16; x++)
-		for (int y = 0; y < 16; y++) {
-			cols[x * 16 + y] = tg::column_info(rg.seed, ox + x, oy + y);
-			tg::gen_column(rg.seed, ox, oy, oz, x, y, cols[x * 16 + y], chunk + x * 256 + y * 16);
-		}
-	int base;
-	for (int k = 0; k < 256; k++)
-		if (tg::tree_fits(oz, k >> 4, k & 15, cols[k], &base)) tree_leaves(chunk, k >> 4, k & 15, base, cols[k]);
-	for (int k = 0; k < 256; k++)
-		if (tg::tree_fits(oz, k >> 4, k & 15, cols[k], &base)) tree_trunk(chunk, k >> 4, k & 15, base, cols[k]);
-}
+using tg::Region;
+using tg::tree_leaves;
+using tg::tree_trunk;
 
 // one CTA of 256 threads per chunk, one thread per column
 __global__ void __launch_bounds__(256) gen_terrain_kernel(Region rg, uint32_t n, uint8_t *chunks, long long *offs) {
@@ -179,10 +142,7 @@ int mm_push_blocks(mm_ctx *c, const mm_cube *cubes, uint32_t n, mm_vertex *out, 
 int mm_gen_terrain_host(uint64_t seed, int64_t cx0, int64_t cy0, int64_t cz0, uint32_t nx, uint32_t ny, uint32_t nz,
                         uint8_t *chunks, int64_t *offs) {
 	if (!chunks || !offs || !nx || !ny || !nz) return MM_ERR_INVALID;
-	const Region rg = {seed, cx0, cy0, cz0, nx, ny, nz};
-	const uint64_t n = (uint64_t)nx * ny * nz;
-	for (uint64_t i = 0; i < n; i++) gen_chunk_host(rg, (uint32_t)i, chunks + i * 4096, (long long *)offs + 3 * i);
-	return MM_OK;
+	return tg::gen_region_host(seed, cx0, cy0, cz0, nx, ny, nz, chunks, (long long *)offs) ? MM_OK : MM_ERR_INVALID;
 }
 
 int mm_gen_terrain_device(mm_ctx *c, uint64_t seed, int64_t cx0, int64_t cy0, int64_t cz0, uint32_t nx, uint32_t ny,

@@ -8,6 +8,30 @@
 #include "../../include/mimas_meshgen_cuda.h"
 #include "mesh_core.cuh"
 
+// One output slot of the ring: the arenas a batch's packed vertex streams and range records go to, where its
+// totals reach the host, and what is needed to run it again should the arenas turn out too small.
+struct mm_slot {
+	unsigned char *d_out_i = nullptr, *d_out_t = nullptr;  // arenas (capacities in quads of 216 B)
+	uint64_t cap_i = 0, cap_t = 0;
+	uint32_t cap_chunks = 0;                               // per-chunk arrays
+	mm::Range *d_ranges_i = nullptr, *d_ranges_t = nullptr;
+	mm::u64 *h_totals = nullptr;    // pinned + mapped, 2 words: the expand kernel writes the totals straight to the host
+	mm::u64 *d_h_totals = nullptr;  // the same words as the device sees them
+	// the batch the slot holds
+	uint64_t ticket = 0;            // 0 = none yet
+	uint64_t wait_ticket = 0;       // the batch is complete once the device has signalled this ticket (h_done)
+	bool pending = false, finished = false;
+	const unsigned char *last_chunks = nullptr;
+	const unsigned char *last_halo = nullptr;
+	const long long *last_offs = nullptr;
+	uint32_t last_n = 0;
+	uint32_t last_launches = 0;
+	bool last_timed = false;
+	uint64_t tot_i = 0, tot_t = 0;  // quads
+	float last_ms = 0.f;
+};
+constexpr uint32_t kMaxRingSlots = 8;
+
 struct mm_ctx {
 	int device = 0;
 	int sm_count = 0;
@@ -19,12 +43,17 @@ struct mm_ctx {
 	bool have_table = false;
 	mm::TabEntry *d_table = nullptr;
 
-	// arenas (capacities in quads of 216 B)
-	unsigned char *d_out_i = nullptr, *d_out_t = nullptr;
-	uint64_t cap_i = 0, cap_t = 0;
-	// per-chunk arrays
-	uint32_t cap_chunks = 0;
-	mm::Range *d_ranges_i = nullptr, *d_ranges_t = nullptr;
+	// output ring (mm_ring_configure; one slot unless asked otherwise): batch with ticket t goes to slot t % ring_slots
+	mm_slot ring[kMaxRingSlots];
+	uint32_t ring_slots = 1;
+	mm_slot *cur = &ring[0];          // slot of the most recent batch: what finish / copy_out / draw_batch refer to
+	uint64_t next_ticket = 1;         // tickets start at 1
+	uint64_t last_signal_ticket = 0;  // completion signal of the most recent batch that launched kernels (counts on its own)
+	bool no_signal = false;           // MM_NO_SIGNAL: batches do not signal, waits synchronise the stream
+	mm::u64 *h_done = nullptr;        // pinned + mapped: ticket of the last batch whose kernels have completed
+	mm::u64 *d_h_done = nullptr;
+	uint32_t *d_done_count = nullptr; // expand CTAs that have finished the current launch (last one signals)
+	cudaStream_t s_draw = nullptr;    // consumers of finished ring slots run here, beside the mesher's stream
 	// analysis -> expansion hand-over (mesh_kernel.cuh): per-chunk descriptor slots and counts
 	// -- two of each: consecutive launch pairs alternate, so that the analysis of one batch can run
 	// beside the expansion of the previous one (programmatic dependent launch)
@@ -39,9 +68,7 @@ struct mm_ctx {
 	int totals_slot = 0;              // slot the last launch wrote
 	mm::u64 ticket_base = 0;
 	unsigned char *d_flags = nullptr; // 256 flag bytes derived from the block table
-	mm::u64 *h_totals = nullptr;    // pinned + mapped, 2 words: the expand kernel writes the totals straight to the host
-	mm::u64 *d_h_totals = nullptr;  // the same words as the device sees them
-	bool time_next = false, last_timed = false;
+	bool time_next = false;
 	// mm_debug_trace: device timeline of the last trace_pairs launch pairs (8 words per pair, ring)
 	mm::u64 *d_trace = nullptr;
 	uint32_t trace_pairs = 0;
@@ -71,16 +98,8 @@ struct mm_ctx {
 	uint32_t pipe_min_chunks = 1024;  // 0: off (MM_PIPE_MIN_CHUNKS)
 	double host_qi_per_chunk = -1.0, host_qt_per_chunk = -1.0;  // quads per chunk of the last large host batch
 
-	// last batch
-	bool pending = false, finished = false;
-	const unsigned char *last_chunks = nullptr;
-	const unsigned char *last_halo = nullptr;
-	const long long *last_offs = nullptr;
-	uint32_t last_n = 0;
-	uint32_t last_launches = 0;
 	uint64_t total_launches = 0;
-	uint64_t tot_i = 0, tot_t = 0;  // quads
-	float last_ms = 0.f;
+	uint32_t host_path = 0;  // MM_PATH_* of the last mm_mesh_batch_host call
 
 	// headless draw (mm_render.cu): scratch of mm_cull_chunks / mm_draw_batch
 	unsigned char *d_cull = nullptr;   // flags, draw list, per-visible-chunk output offsets, block sums

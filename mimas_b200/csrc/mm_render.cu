@@ -273,6 +273,7 @@ int setup_cull(mm_ctx *c, uint32_t n, CullParams &p) {
 	             total = align256(o_bt + 8 * (size_t)nb) + 256;
 	if (total > c->cull_bytes) {
 		MM_CUDA(c, cudaStreamSynchronize(c->stream));
+		if (c->s_draw) MM_CUDA(c, cudaStreamSynchronize(c->s_draw));
 		cudaFree(c->d_cull);
 		c->d_cull = nullptr;
 		c->cull_bytes = 0;
@@ -289,11 +290,12 @@ int setup_cull(mm_ctx *c, uint32_t n, CullParams &p) {
 	return MM_OK;
 }
 
-int enqueue_cull(mm_ctx *c, const CullParams &p) {
+int enqueue_cull(mm_ctx *c, const CullParams &p, cudaStream_t stream = nullptr) {
+	if (!stream) stream = c->stream;
 	const uint32_t nb = (p.n + kCullThreads - 1) / kCullThreads;
-	cull_flags_kernel<<<nb, kCullThreads, 0, c->stream>>>(p);
-	scan_blocks_kernel<<<1, kCullThreads, 0, c->stream>>>(p, nb);
-	cull_write_kernel<<<nb, kCullThreads, 0, c->stream>>>(p);
+	cull_flags_kernel<<<nb, kCullThreads, 0, stream>>>(p);
+	scan_blocks_kernel<<<1, kCullThreads, 0, stream>>>(p, nb);
+	cull_write_kernel<<<nb, kCullThreads, 0, stream>>>(p);
 	MM_CUDA(c, cudaGetLastError());
 	return MM_OK;
 }
@@ -373,38 +375,36 @@ int mm_cull_chunks(mm_ctx *c, const int64_t *offs, uint32_t n, const mm_camera *
 	return rc;
 }
 
-int mm_draw_batch(mm_ctx *c, const mm_camera *cam, mm_draw_out *out) {
-	if (!c || !cam || !out) return MM_ERR_INVALID;
-	if (!c->finished) return fail(c, MM_ERR_NO_BATCH, "no finished device batch to draw");
-	MM_CUDA(c, cudaSetDevice(c->device));
+// One frame over the batch a ring slot holds, on `stream`.
+static int draw_slot(mm_ctx *c, const mm_slot *sl, cudaStream_t stream, const mm_camera *cam, mm_draw_out *out) {
 	memset(out, 0, sizeof(*out));
-	out->n_chunks = c->last_n;
-	if (c->last_n == 0) return MM_OK;
+	out->n_chunks = sl->last_n;
+	if (sl->last_n == 0) return MM_OK;
 	int rc;
 	if ((rc = ensure_draw_totals(c))) return rc;
 	CullParams p;
 	memset(&p, 0, sizeof(p));
 	Mats mt;
 	fill_camera(*cam, p, mt);
-	if ((rc = setup_cull(c, c->last_n, p))) return rc;
-	p.offs = c->last_offs;
-	p.n = c->last_n;
-	p.ranges_i = c->d_ranges_i;
-	p.ranges_t = c->d_ranges_t;
+	if ((rc = setup_cull(c, sl->last_n, p))) return rc;
+	p.offs = sl->last_offs;
+	p.n = sl->last_n;
+	p.ranges_i = sl->d_ranges_i;
+	p.ranges_t = sl->d_ranges_t;
 	p.totals = c->d_h_draw_totals;
 	for (int attempt = 0;; attempt++) {
 		DrawParams d;
 		d.draw = p.draw; d.first_i = p.first_i; d.first_t = p.first_t; d.totals = c->d_h_draw_totals;
-		d.ranges_i = c->d_ranges_i; d.ranges_t = c->d_ranges_t;
-		d.vi = (const mm_vertex *)c->d_out_i; d.vt = (const mm_vertex *)c->d_out_t;
+		d.ranges_i = sl->d_ranges_i; d.ranges_t = sl->d_ranges_t;
+		d.vi = (const mm_vertex *)sl->d_out_i; d.vt = (const mm_vertex *)sl->d_out_t;
 		d.out = (mm_shaded_vertex *)c->d_shaded;
 		d.cap = c->shaded_bytes / sizeof(mm_shaded_vertex);
-		MM_CUDA(c, cudaEventRecord(c->ev2, c->stream));
-		if ((rc = enqueue_cull(c, p))) return rc;
-		draw_kernel<<<c->sm_count * 8, kShadeThreads, 0, c->stream>>>(d, mt);
+		MM_CUDA(c, cudaEventRecord(c->ev2, stream));
+		if ((rc = enqueue_cull(c, p, stream))) return rc;
+		draw_kernel<<<c->sm_count * 8, kShadeThreads, 0, stream>>>(d, mt);
 		MM_CUDA(c, cudaGetLastError());
-		MM_CUDA(c, cudaEventRecord(c->ev3, c->stream));
-		MM_CUDA(c, cudaStreamSynchronize(c->stream));
+		MM_CUDA(c, cudaEventRecord(c->ev3, stream));
+		MM_CUDA(c, cudaStreamSynchronize(stream));
 		const unsigned long long need = c->h_draw_totals[1] + c->h_draw_totals[2];
 		if (need <= d.cap) break;
 		if (attempt >= 1) return fail(c, MM_ERR_CUDA, "shaded vertex buffer still too small after growth");
@@ -422,6 +422,21 @@ int mm_draw_batch(mm_ctx *c, const mm_camera *cam, mm_draw_out *out) {
 	out->n_shaded_i = c->h_draw_totals[1];
 	out->n_shaded_t = c->h_draw_totals[2];
 	return MM_OK;
+}
+
+int mm_draw_batch(mm_ctx *c, const mm_camera *cam, mm_draw_out *out) {
+	if (!c || !cam || !out) return MM_ERR_INVALID;
+	if (!c->cur->finished) return fail(c, MM_ERR_NO_BATCH, "no finished device batch to draw");
+	MM_CUDA(c, cudaSetDevice(c->device));
+	return draw_slot(c, c->cur, c->stream, cam, out);
+}
+
+int mm_draw_ticket(mm_ctx *c, uint64_t ticket, const mm_camera *cam, mm_draw_out *out) {
+	if (!c || !cam || !out || !ticket) return MM_ERR_INVALID;
+	MM_CUDA(c, cudaSetDevice(c->device));
+	int rc;
+	if ((rc = mm_batch_wait(c, ticket, nullptr))) return rc;  // polls the batch's completion word: no stream synchronisation
+	return draw_slot(c, &c->ring[ticket % c->ring_slots], c->s_draw, cam, out);
 }
 
 }  // extern "C"

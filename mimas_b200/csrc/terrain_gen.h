@@ -157,4 +157,56 @@ TG_HD bool tree_fits(int64_t oz, int x, int y, const Column &ci, int *base_z) {
 	return true;
 }
 
+struct Region {
+	uint64_t seed;
+	long long cx0, cy0, cz0;
+	uint32_t nx, ny, nz;
+};
+
+// leaves (into air only), then trunk / cactus: shared by the host loop and the device kernel
+TG_HD void tree_leaves(uint8_t *chunk, int x, int y, int base, const Column &ci) {
+	if (ci.tree != 1) return;
+	for (int dz = 3; dz <= 5; dz++) {
+		const int r = dz < 5 ? 1 : 0;
+		for (int dx = -r; dx <= r; dx++)
+			for (int dy = -r; dy <= r; dy++) {
+				uint8_t *p = &chunk[(x + dx) * 256 + (y + dy) * 16 + base + dz];
+				if (*p == AIR) *p = LEAVES;
+			}
+	}
+}
+TG_HD void tree_trunk(uint8_t *chunk, int x, int y, int base, const Column &ci) {
+	const int h = ci.tree == 1 ? 4 : 3;
+	for (int dz = 0; dz < h; dz++) chunk[x * 256 + y * 16 + base + dz] = ci.tree == 1 ? TREE : CACTUS;
+}
+
+// Chunk i of a region on the host (the device kernel in mm_extra.cu visits the same columns with one thread each).
+static inline void gen_chunk_host(const Region &rg, uint32_t i, uint8_t *chunk, long long *offs) {
+	const long long cx = rg.cx0 + (long long)(i % rg.nx), cy = rg.cy0 + (long long)((i / rg.nx) % rg.ny),
+	                cz = rg.cz0 + (long long)(i / (rg.nx * rg.ny));
+	const long long ox = cx * 16, oy = cy * 16, oz = cz * 16;
+	offs[0] = ox; offs[1] = oy; offs[2] = oz;
+	Column cols[256];
+	for (int x = 0; x < 16; x++)
+		for (int y = 0; y < 16; y++) {
+			cols[x * 16 + y] = column_info(rg.seed, ox + x, oy + y);
+			gen_column(rg.seed, ox, oy, oz, x, y, cols[x * 16 + y], chunk + x * 256 + y * 16);
+		}
+	int base;
+	for (int k = 0; k < 256; k++)
+		if (tree_fits(oz, k >> 4, k & 15, cols[k], &base)) tree_leaves(chunk, k >> 4, k & 15, base, cols[k]);
+	for (int k = 0; k < 256; k++)
+		if (tree_fits(oz, k >> 4, k & 15, cols[k], &base)) tree_trunk(chunk, k >> 4, k & 15, base, cols[k]);
+}
+
+// The whole region on the host (mm_gen_terrain_host of both libraries).  false: bad arguments.
+static inline bool gen_region_host(uint64_t seed, long long cx0, long long cy0, long long cz0, uint32_t nx, uint32_t ny,
+                                   uint32_t nz, uint8_t *chunks, long long *offs) {
+	if (!chunks || !offs || !nx || !ny || !nz) return false;
+	const Region rg = {seed, cx0, cy0, cz0, nx, ny, nz};
+	const uint64_t n = (uint64_t)nx * ny * nz;
+	for (uint64_t i = 0; i < n; i++) gen_chunk_host(rg, (uint32_t)i, chunks + i * 4096, offs + 3 * i);
+	return true;
+}
+
 }  // namespace tg

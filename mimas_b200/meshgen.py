@@ -198,7 +198,10 @@ class _BatchOut(C.Structure):
 class _HostMesh(C.Structure):
     _fields_ = [("intransparent", C.c_void_p), ("transparent", C.c_void_p), ("ranges_i", C.c_void_p),
                 ("ranges_t", C.c_void_p), ("n_intransparent", C.c_uint64), ("n_transparent", C.c_uint64),
-                ("n_chunks", C.c_uint32), ("reserved", C.c_uint32)]
+                ("n_chunks", C.c_uint32), ("path", C.c_uint32)]
+
+
+HOST_PATH_NAMES = {1: "mapped", 2: "pipelined", 3: "plain"}  # MM_PATH_*
 
 
 def _copy_from(ptr: Optional[int], count: int, dtype: np.dtype) -> np.ndarray:
@@ -333,6 +336,56 @@ class Mesher:
         gen_terrain order; `outside_id` is what lies beyond the box."""
         self._ck(self._lib.mm_gather_halos(self._ctx, C.c_void_p(d_chunks), dims[0], dims[1], dims[2], outside_id,
                                            C.c_void_p(d_halo)))
+
+    # -- output ring: several batches retrievable while later ones are meshed (mm_ring_configure) ----------
+    def ring_configure(self, slots: int):
+        self._ck(self._lib.mm_ring_configure(self._ctx, slots))
+
+    def submit(self, d_chunks: int, d_offs: int, n: int, d_halo: Optional[int] = None) -> int:
+        """mm_mesh_batch_submit: enqueue one batch into the next ring slot; returns its ticket."""
+        t = C.c_uint64()
+        self._ck(self._lib.mm_mesh_batch_submit(self._ctx, C.c_void_p(d_chunks), C.c_void_p(d_offs),
+                                                C.c_void_p(d_halo) if d_halo else None, n, C.byref(t)))
+        return t.value
+
+    def submit_many(self, d_chunks: Sequence[int], d_offs: Sequence[int], n: Sequence[int], repeat: int = 1) -> int:
+        """mm_mesh_batches_submit: k batches (x repeat, round robin) enqueued by ONE foreign call; returns the
+        first ticket (the others follow consecutively)."""
+        k = len(n)
+        pc = (C.c_void_p * k)(*d_chunks)
+        po = (C.c_void_p * k)(*d_offs)
+        pn = (C.c_uint32 * k)(*n)
+        t = C.c_uint64()
+        self._ck(self._lib.mm_mesh_batches_submit(self._ctx, pc, po, pn, k, repeat, C.byref(t)))
+        return t.value
+
+    def batch_wait(self, ticket: int) -> _BatchOut:
+        out = _BatchOut()
+        self._ck(self._lib.mm_batch_wait(self._ctx, ticket, C.byref(out)))
+        return out
+
+    def batch_poll(self, ticket: int) -> bool:
+        d = C.c_int()
+        self._ck(self._lib.mm_batch_poll(self._ctx, ticket, C.byref(d)))
+        return bool(d.value)
+
+    def copy_out_ticket(self, ticket: int) -> BatchMesh:
+        out = self.batch_wait(ticket)
+        vi = np.zeros(out.n_intransparent, dtype=VERTEX_DTYPE)
+        vt = np.zeros(out.n_transparent, dtype=VERTEX_DTYPE)
+        ri = np.zeros(out.n_chunks, dtype=RANGE_DTYPE)
+        rt = np.zeros(out.n_chunks, dtype=RANGE_DTYPE)
+        self._ck(self._lib.mm_copy_out_ticket(self._ctx, ticket, vi.ctypes.data, vt.ctypes.data, ri.ctypes.data,
+                                              rt.ctypes.data))
+        return BatchMesh(vi, vt, ri, rt)
+
+    def draw_ticket(self, ticket: int, cam):
+        """One frame over the batch of `ticket` on the consumer stream (later batches keep meshing)."""
+        from .render import DrawOut
+        out = DrawOut()
+        cc = cam.to_c()
+        self._ck(self._lib.mm_draw_ticket(self._ctx, ticket, C.byref(cc), C.byref(out)))
+        return out
 
     def batch_finish(self) -> _BatchOut:
         out = _BatchOut()
@@ -481,11 +534,26 @@ def mesh_for_chunk(offs, chunk, cache: TextureIdCache) -> ChunkMesh:
     return _default.mesh_for_chunk(offs, chunk, cache)
 
 
+_host_lib = None
+
+
 def gen_terrain_host(seed: int, c0, dims) -> Tuple[np.ndarray, np.ndarray]:
-    """Synthetic mapgen look-alike on the host (same bytes as the device generator)."""
+    """Synthetic mapgen look-alike on the host (same bytes as the device generator).  Served by the host-only
+    libmimas_terrain_host.so, so that CPU-side callers (the bench's CPU arms) never map the CUDA library."""
+    global _host_lib
+    if _host_lib is None:
+        import os
+        path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libmimas_terrain_host.so")
+        if not os.path.exists(path):
+            raise ImportError(f"{path} is missing: build it with `make -C mimas_b200/csrc`")
+        h = C.CDLL(path)
+        h.mm_gen_terrain_host.argtypes = [C.c_uint64, C.c_int64, C.c_int64, C.c_int64, C.c_uint32, C.c_uint32,
+                                          C.c_uint32, C.c_void_p, C.c_void_p]
+        h.mm_gen_terrain_host.restype = C.c_int
+        _host_lib = h
     n = int(dims[0]) * int(dims[1]) * int(dims[2])
     chunks = np.zeros((n, 4096), dtype=np.uint8)
     offs = np.zeros((n, 3), dtype=np.int64)
-    check(lib().mm_gen_terrain_host(seed, c0[0], c0[1], c0[2], dims[0], dims[1], dims[2],
-                                    chunks.ctypes.data, offs.ctypes.data), None)
+    check(_host_lib.mm_gen_terrain_host(seed, c0[0], c0[1], c0[2], dims[0], dims[1], dims[2],
+                                        chunks.ctypes.data, offs.ctypes.data), None)
     return chunks, offs

@@ -377,30 +377,38 @@ void mo_count_batch_halo(const uint8_t *chunks, const int64_t *offs, uint64_t n,
  * produces, so a whole batch can be compared with one memcmp. */
 typedef struct {
 	const uint8_t *chunks; const int64_t *offs; const mo_cache *cache; const uint8_t *halo;
-	uint64_t begin, end;
+	uint64_t n;
+	uint64_t *next; /* shared work counter: the threads draw blocks of MO_GRAIN chunks until the batch is done */
 	mo_vertex *intr; mo_vertex *trans;
 	const uint64_t *first_intr; const uint64_t *first_trans;
 	uint64_t verts; /* out */
 } batch_job;
 
+#define MO_GRAIN 4u
 static void *batch_worker(void *arg) {
 	batch_job *j = (batch_job *)arg;
 	uint64_t verts = 0;
-	for (uint64_t i = j->begin; i < j->end; i++) {
-		/* fresh, empty vectors per chunk, as in the reference (lib.rs:233,412) */
-		mo_vec r = { 0, 0, 0 }, rt = { 0, 0, 0 };
-		mesh_for_chunk_h(j->offs + 3 * i, j->chunks + 4096 * i, j->halo ? j->halo + 1536 * i : 0, j->cache, &r, &rt);
-		if (j->intr && r.len) memcpy(j->intr + j->first_intr[i], r.data, r.len * sizeof(mo_vertex));
-		if (j->trans && rt.len) memcpy(j->trans + j->first_trans[i], rt.data, rt.len * sizeof(mo_vertex));
-		verts += r.len + rt.len;
-		free(r.data); free(rt.data);
+	for (;;) {
+		const uint64_t begin = __atomic_fetch_add(j->next, MO_GRAIN, __ATOMIC_RELAXED);
+		if (begin >= j->n) break;
+		const uint64_t end = begin + MO_GRAIN < j->n ? begin + MO_GRAIN : j->n;
+		for (uint64_t i = begin; i < end; i++) {
+			/* fresh, empty vectors per chunk, as in the reference (lib.rs:233,412) */
+			mo_vec r = { 0, 0, 0 }, rt = { 0, 0, 0 };
+			mesh_for_chunk_h(j->offs + 3 * i, j->chunks + 4096 * i, j->halo ? j->halo + 1536 * i : 0, j->cache, &r, &rt);
+			if (j->intr && r.len) memcpy(j->intr + j->first_intr[i], r.data, r.len * sizeof(mo_vertex));
+			if (j->trans && rt.len) memcpy(j->trans + j->first_trans[i], rt.data, rt.len * sizeof(mo_vertex));
+			verts += r.len + rt.len;
+			free(r.data); free(rt.data);
+		}
 	}
 	j->verts = verts;
 	return 0;
 }
 
-/* Runs the batch on `threads` OS threads over contiguous chunk ranges (chunks are
- * independent, lib.rs:277-280).  intr/trans may be NULL (mesh and discard: the CPU
+/* Runs the batch on `threads` OS threads (chunks are independent, lib.rs:277-280); the threads share one
+ * atomic work counter, so that a region whose chunks differ a lot in cost (a quarter of a terrain region
+ * is all air) keeps every core busy to the end.  intr/trans may be NULL (mesh and discard: the CPU
  * baseline's timing mode -- the meshes are still fully built in per-chunk vectors).
  * Returns total vertices produced; *seconds receives the wall time of the parallel
  * region (CLOCK_MONOTONIC). */
@@ -425,11 +433,12 @@ uint64_t mo_mesh_batch_halo(const uint8_t *chunks, const int64_t *offs, uint64_t
 	batch_job *jobs = (batch_job *)calloc(threads, sizeof(batch_job));
 	pthread_t *tids = (pthread_t *)calloc(threads, sizeof(pthread_t));
 	struct timespec t0, t1;
+	uint64_t next = 0;
 	clock_gettime(CLOCK_MONOTONIC, &t0);
 	for (uint32_t t = 0; t < threads; t++) {
 		batch_job *j = &jobs[t];
 		j->chunks = chunks; j->offs = offs; j->cache = cache; j->halo = halo;
-		j->begin = n * t / threads; j->end = n * (t + 1) / threads;
+		j->n = n; j->next = &next;
 		j->intr = intr; j->trans = trans; j->first_intr = first_intr; j->first_trans = first_trans;
 		if (threads == 1) batch_worker(j);
 		else pthread_create(&tids[t], 0, batch_worker, j);

@@ -1,0 +1,21 @@
+#!/bin/bash
+# On the GPU box: every BASELINE.json config as a bench.py line (tag_bench_<workload>.json under gpurun_out/),
+# then the CPU reference arm of the default workload.  Usage: scripts/gpu_bench_all.sh [tag] [workloads...]
+tag=${1:-r02}; shift
+wls=${@:-terrain single checkerboard16384 radius8 radius16 radius32 edits million}
+mkdir -p gpurun_out
+for w in $wls; do
+  timeout 900 python bench.py --workload $w > gpurun_out/${tag}_bench_$w.json 2> gpurun_out/${tag}_bench_$w.err
+  echo "$w exit $?"; tail -c 600 gpurun_out/${tag}_bench_$w.err
+  python - <<P
+import json
+try:
+    d = json.loads(open("gpurun_out/${tag}_bench_$w.json").read().strip().splitlines()[-1])
+    r = d["roofline"]
+    print("  %-18s %10.3f ms/step %12.0f chunks/s  frac %.3f  iso %.4f ms  e2e %.0f chunks/s (%s)  cpu %s" % (
+        "$w", d["ms_per_step"], d["value"], r["frac"], r["isolated_batch_ms"], d["e2e"]["value"], d["e2e"]["path"],
+        d.get("cpu_baseline", {}).get("value")))
+except Exception as e:
+    print("  $w: no line:", e)
+P
+done
