@@ -228,6 +228,38 @@ int mm_gen_terrain_host(uint64_t seed, int64_t cx0, int64_t cy0, int64_t cz0,
 int mm_gen_terrain_device(mm_ctx *ctx, uint64_t seed, int64_t cx0, int64_t cy0, int64_t cz0,
                           uint32_t nx, uint32_t ny, uint32_t nz, uint8_t *d_chunks, int64_t *d_offs);
 
+/* mimas-server mapgen PHASE ONE on the device (mimas-server/mapgen.rs:64-245 `gen_chunk_phase_one`): the
+ * chunks of a box, generated straight into the mesher's input layout (same chunk order as mm_gen_terrain_*), so
+ * that server-side mapgen chunks reach the mesher without a host copy.  Phase two (trees, mapgen.rs:357-434) is not
+ * part of it: d_tree_counts (NULL or nx*ny*nz words) receives the number of tree spawn points per chunk
+ * (mapgen.rs:228).  Ores and plants are the `[[mapgen.ore]]` / `[[mapgen.plant]]` tables of game-params.toml
+ * (mimas-common/game_params.rs:134-149, 648-718), the block ids the roles of game_params.rs:79-90.
+ * PARITY UNPINNED against the reference (its arithmetic lives in the crates noise 0.7.0, rand_pcg 0.3.1, rand,
+ * twox-hash 1.6.1, none of them under the reference checkout; no reference test pins mapgen output): bit-exact to
+ * oracle/mapgen_oracle.c, whose PCG and XXH64 parts are pinned by their published vectors.  Synchronous. */
+#define MM_MAPGEN_MAX_ORES 8u
+#define MM_MAPGEN_MAX_PLANTS 16u
+typedef struct mm_mapgen_ore {      /* game_params.rs:134-143 `Ore` */
+	uint8_t block;
+	uint8_t noise_seed[8];
+	uint8_t pcg_seed[8];
+	double freq, pcg_chance, limit_a, limit_b;
+	int64_t limit_boundary;
+} mm_mapgen_ore;
+typedef struct mm_mapgen_plant {    /* game_params.rs:145-149 `Plant` */
+	uint8_t block;
+	uint8_t pcg_seed[8];
+	double pcg_limit;
+} mm_mapgen_plant;
+typedef struct mm_mapgen_params {
+	uint8_t air, water, sand, ground, ground_top, stone;   /* BlockRoles, game_params.rs:79-90 */
+	uint32_t n_ores, n_plants;
+	mm_mapgen_ore ores[MM_MAPGEN_MAX_ORES];
+	mm_mapgen_plant plants[MM_MAPGEN_MAX_PLANTS];
+} mm_mapgen_params;
+int mm_gen_mapgen_device(mm_ctx *ctx, uint64_t seed, const mm_mapgen_params *params, int64_t cx0, int64_t cy0, int64_t cz0,
+                         uint32_t nx, uint32_t ny, uint32_t nz, uint8_t *d_chunks, int64_t *d_offs, uint32_t *d_tree_counts);
+
 /* Plain device memory helpers so that non-CUDA host code (ctypes, Rust) can keep
  * inputs resident without linking the CUDA runtime itself. */
 int mm_dev_alloc(mm_ctx *ctx, size_t bytes, void **d_ptr);

@@ -47,6 +47,9 @@ constexpr int kThreads = kWarpsPerCta * 32;
 #ifndef MM_EXPAND_PREFETCH
 #define MM_EXPAND_PREFETCH 0
 #endif
+#ifndef MM_EXPAND_WARP_SEARCH
+#define MM_EXPAND_WARP_SEARCH 1
+#endif
 constexpr int kAnalyseCtasPerSm = MM_ANALYSE_CTAS;   // register budget of the analysis: 65536 / (128 * this)
 static_assert(kThreads == 128, "phase C hands one of 32 + 96 jobs to every thread");
 constexpr int kExpandWarps = MM_EXPAND_WARPS;    // expand_kernel
@@ -54,7 +57,7 @@ constexpr int kExpandThreads = kExpandWarps * 32;
 constexpr uint32_t kMaxLaunchChunks = 4096;      // the prefix of one launch lives in shared memory
 // expand: table | prefix_i[4096+4] | prefix_t[4096+4] | warp totals | stage tiles
 constexpr size_t kExpandPrefixWords = kMaxLaunchChunks + 4;
-constexpr size_t kExpandSmemBytes = 2048 + 2 * 4 * kExpandPrefixWords + 256 + kExpandWarps * (size_t)(kStageBytes + 16);
+constexpr size_t kExpandSmemBytes = 2048 + 2 * 4 * kExpandPrefixWords + 512 + kExpandWarps * (size_t)(kStageBytes + 16);
 
 struct ExpandParams {
 	const long long *offs;        // n * 3
@@ -195,7 +198,12 @@ __device__ __forceinline__ void store_tile(unsigned char *g, const unsigned char
 }
 
 // ---- kernel 1: analysis ------------------------------------------------------------------
-// One CTA of kThreads threads per chunk in flight; CTAs are persistent and draw chunk tickets.
+// One CTA of kThreads threads per chunk being analysed; CTAs are persistent and draw chunk tickets.  A CTA keeps
+// two chunks in flight: while chunk k goes through phases B-D, chunk k+1 lands in the other raw buffer (TMA,
+// issued a whole chunk ahead) and every warp takes it through phase A as soon as the warp itself is done with
+// k -- so no warp waits at a barrier for the slowest one to finish a chunk, and the load latency is never seen.
+// Barriers per chunk: (a) phase A complete / everyone done with the previous chunk, (b) run starts complete,
+// (c) transposes and counts complete; an empty chunk (no cube, no plant: a quarter of a terrain region) stops at (a).
 // HALO = the optional mode in which the touching layers of the six neighbour chunks occlude faces (an
 // extension; false = the reference's semantics, lib.rs:277-280, and the instantiation every number in
 // DESIGN.md is measured on).
@@ -215,129 +223,153 @@ __global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(co
 	if (tid == 0) trace_mark(p.trace, 0);
 	if (tid < 16) reinterpret_cast<uint4 *>(flags)[tid] = __ldg(reinterpret_cast<const uint4 *>(p.flags) + tid);
 	if (warp == 1) init_warp_smem(s, lane);
+	// FUSED: one CTA, one chunk -- no ticket is drawn, so a following launch may draw its own at once
+	uint32_t fused_drawn = 0;
+	auto draw = [&]() -> uint32_t {
+		if (FUSED) return fused_drawn++ == 0 ? 0u : 0xffffffffu;
+		return (uint32_t)min(atomicAdd(p.ticket, 1ull) - p.ticket_base, (u64)0xffffffffu);
+	};
 	if (tid == 0) {
-		mbar_init(&s.mbar);
-		fence_proxy_async_smem();  // the barrier is visible to the bulk-copy engine
-		// FUSED: one CTA, one chunk -- no ticket is drawn, so a following launch may draw its own at once
-		s.ticket[0] = FUSED ? 0u : (uint32_t)min(atomicAdd(p.ticket, 1ull) - p.ticket_base, (u64)0xffffffffu);
-		s.amb[0] = 0;
-	}
-	unsigned char *raw = smem_raw(s);
-	const TabEntry *tab = p.table;  // only read for chunks with ambiguous ids (fix_equal)
-	uint32_t par = 0;
-	for (;; par ^= 1u) {
-		__syncthreads();  // the previous chunk is done with shared memory; this round's ticket is visible
-		const uint32_t c = s.ticket[par];
-		if (c >= p.n) break;
-		if (tid == 0) {
-			bulk_load_g2s(raw, p.chunks + (size_t)c * 4096u, 4096u, &s.mbar);  // TMA: 4 KiB chunk -> shared memory
-			// the next ticket travels while this chunk is analysed
-			const uint32_t nxt = FUSED ? 0xffffffffu : (uint32_t)min(atomicAdd(p.ticket, 1ull) - p.ticket_base, (u64)0xffffffffu);
-			s.ticket[par ^ 1u] = nxt;
-			s.amb[par ^ 1u] = 0;
+		mbar_init(&s.mbar[0]);
+		mbar_init(&s.mbar[1]);
+		fence_proxy_async_smem();  // the barriers are visible to the bulk-copy engine
+		const uint32_t t0 = draw();
+		s.ticket[0] = t0;
+		if (t0 < p.n) bulk_load_g2s(s.raw[0], p.chunks + (size_t)t0 * 4096u, 4096u, &s.mbar[0]);  // TMA: 4 KiB chunk -> shared memory
+		const uint32_t t1 = draw();
+		s.ticket[1] = t1;
 #if MM_ANALYSE_PREFETCH
-			if (nxt < p.n) bulk_prefetch_l2(p.chunks + (size_t)nxt * 4096u, 4096u);  // and its chunk comes as far as L2
+		if (t1 < p.n) bulk_prefetch_l2(p.chunks + (size_t)t1 * 4096u, 4096u);
 #endif
-		}
+	}
+	const TabEntry *tab = p.table;  // only read for chunks with ambiguous ids (fix_equal)
+
+	// Phase A of chunk `c` in buffer `b`: thread <-> columns col = tid, tid + 128 (col = x*16 + y): blocky mask over z
+	// per column into Bzp[b]; what the warp's columns hold (flag bytes ORed, plants per range of 32 columns) into
+	// ambw[b] / pcnt[b].  Returns the crossed masks over z of the thread's two columns (low / high half).
+	auto phase_a = [&](int b, uint32_t c, uint32_t parity) -> uint32_t {
 		Col hrow;
 		if (HALO && tid < 96) {  // one 16-byte row of the halo slabs per thread, in flight beside the chunk
 			const uint4 v = __ldg(reinterpret_cast<const uint4 *>(p.halo + (size_t)c * 1536u) + tid);
 			hrow.w[0] = v.x; hrow.w[1] = v.y; hrow.w[2] = v.z; hrow.w[3] = v.w;
 		}
-		mbar_wait(&s.mbar, par);
-
-		// A. thread <-> columns col = tid, tid + 128 (col = x*16 + y): blocky mask over z per column
-		uint32_t crossed_cols = 0, amb = 0;
-		Col own[256 / kThreads];
-		bool uniform = true;
-#pragma unroll
-		for (int j = 0; j < 256 / kThreads; j++) {
-			own[j] = load_col(raw + (kThreads * j + tid) * 16);
-			const uint32_t w0 = own[j].w[0];
-			uniform = uniform && w0 == own[j].w[1] && w0 == own[j].w[2] && w0 == own[j].w[3] &&
-			          w0 == __byte_perm(w0, 0, 0) && w0 == *reinterpret_cast<const uint32_t *>(raw);
-		}
-		// a chunk of one undrawn id (all air: a quarter of a terrain region) is done here
-		if (MM_ANALYSE_UNIFORM_EXIT && __syncthreads_and(uniform) && (flags[raw[0]] & (kFlagBlocky | kFlagCrossed)) == 0) {
-			if (tid == 0) {
-				p.cnt_i[c] = 0;
-				p.cnt_t[c] = 0;
-			}
-			continue;
-		}
-		if (HALO && tid < 96) halo_row(s, flags, hrow, tid);
+		mbar_wait(&s.mbar[b], parity);
+		const unsigned char *raw = s.raw[b];
+		uint32_t amb = 0, czp = 0;
 #pragma unroll
 		for (int j = 0; j < 256 / kThreads; j++) {
 			const int col = kThreads * j + tid;
+			const Col own = load_col(raw + col * 16);
 			uint32_t orf;
-			const uint32_t bz = col_flags(flags, own[j], orf);
-			smem_Bzp(s)[((col >> 4) + 1) * kBzStride + (col & 15) + 1] = (uint16_t)bz;
-			crossed_cols |= ((orf >> 1) & 1u) << j;
+			const uint32_t bz = col_flags_any(flags, own, orf);
+			smem_Bzp(s, b)[((col >> 4) + 1) * kBzStride + (col & 15) + 1] = (uint16_t)bz;
+			if (orf & kFlagCrossed) czp |= col_crossed(flags, own) << (16 * j);
 			amb |= orf;
 		}
+		if (HALO && tid < 96) halo_row(s, b, flags, hrow, tid);
 		amb = __reduce_or_sync(full, amb);
-		if (lane == 0 && amb) atomicOr(&s.amb[par], amb);
-		__syncthreads();
-		amb = s.amb[par];
+		uint32_t n0 = 0, n1 = 0;
+		if (amb & kFlagCrossed) {
+			n0 = __reduce_add_sync(full, (uint32_t)__popc(czp & 0xffffu));
+			n1 = __reduce_add_sync(full, (uint32_t)__popc(czp >> 16));
+		}
+		if (lane == 0) {
+			s.ambw[b][warp] = amb;
+			s.pcnt[b][warp] = n0;
+			s.pcnt[b][4 + warp] = n1;
+		}
+		return czp;
+	};
+
+	__syncthreads();  // tickets, flag table, zero borders
+	uint32_t cz = 0;
+	if (s.ticket[0] < p.n) cz = phase_a(0, s.ticket[0], 0u);
+	uint32_t i0 = 0, i1 = 1, i2 = 2;  // ticket slots of this round, the next, the one after
+#pragma unroll 1
+	for (uint32_t k = 0;; k++) {
+		const int b = (int)(k & 1u);
+		const uint32_t c = s.ticket[i0];
+		if (c >= p.n) break;
+		__syncthreads();  // (a) phase A of this chunk is complete; everyone is done with the previous chunk
+		const uint32_t nxt = s.ticket[i1];
+		if (tid == 0) {
+			// the next chunk lands in the other buffer while this one is analysed; the ticket after it travels meanwhile
+			if (nxt < p.n) bulk_load_g2s(s.raw[b ^ 1], p.chunks + (size_t)nxt * 4096u, 4096u, &s.mbar[b ^ 1]);
+			const uint32_t t2 = draw();
+			s.ticket[i2] = t2;
+#if MM_ANALYSE_PREFETCH
+			if (t2 < p.n) bulk_prefetch_l2(p.chunks + (size_t)t2 * 4096u, 4096u);  // and its chunk comes as far as L2
+#endif
+		}
+		const uint4 aw = *reinterpret_cast<const uint4 *>(s.ambw[b]);
+		const uint32_t amb = aw.x | aw.y | aw.z | aw.w;
 		if (amb & kFlagBlocky) {  // else: no cube in the chunk (e.g. all air)
 			uint32_t *di = p.desc_i + (size_t)c * kDescStrideI;
 			// B. run starts over z for the six passes
 #pragma unroll 1
 			for (int j = 0; j < 256 / kThreads; j++) {
 				const int col = kThreads * j + tid;
-				col_starts<HALO>(s, tab, raw, col >> 4, col & 15, amb);
+				col_starts<HALO>(s, b, tab, col >> 4, col & 15, amb);
 			}
-			__syncthreads();
+			__syncthreads();  // (b)
 			// C. masks over the merge axes: 32 blocky jobs + 96 groups = one job per thread
-			if (tid < 32) transpose_blocky(s, tid);
+			if (tid < 32) transpose_blocky(s, b, tid);
 			else s.gcnt[tid - 32] = transpose_group(s, tid - 32);
-			if (HALO && tid >= 124) transpose_halo(s, tid - 124);  // Bzp's border is read-only here
-			__syncthreads();
+			if (HALO && tid >= 124) transpose_halo(s, b, tid - 124);  // Bzp's border is read-only here
+			__syncthreads();  // (c)
 			// exclusive scan of quads (low half) and non-empty words (high half) over the 96 groups, by every warp
-			// for itself (no hand-over through shared memory, one barrier less): the thread of group
-			// m = tid - 32 = (warp - 1) * 32 + lane finds its own prefix in round warp - 1
-			uint32_t run = 0, mine = 0;
+			// for itself (no hand-over through shared memory)
+			uint32_t run = 0, ex[3];
 #pragma unroll
-			for (int k = 0; k < 3; k++) {
-				const uint32_t v = s.gcnt[lane + 32 * k];
+			for (int r = 0; r < 3; r++) {
+				const uint32_t v = s.gcnt[lane + 32 * r];
 				const uint32_t inc = warp_incl_scan(v, lane);
-				if (k == warp - 1) mine = run + inc - v;
+				ex[r] = run + inc - v;
 				run += __shfl_sync(full, inc, 31);
 			}
-			if (tid >= 32) list_group_words(s, tid - 32, mine);
-			__syncthreads();
-			// D. descriptors: thread <-> non-empty word (two rows)
-			const uint32_t nwords = run >> 16;
+			// D. descriptors.  Warp w owns the groups m = w (mod 4) -- a quarter of the rows of every pass --: lane <-> group
+			// lists the group's non-empty words (two rows each) in the warp's own list, then lane <-> word writes one 32-bit
+			// descriptor per run start.  Nothing here crosses warps.
+			const int m = 4 * lane + warp;
+			const uint32_t e0 = __shfl_sync(full, ex[0], m & 31), e1 = __shfl_sync(full, ex[1], m & 31), e2 = __shfl_sync(full, ex[2], m & 31);
+			const uint32_t pre = (m >> 5) == 0 ? e0 : (m >> 5) == 1 ? e1 : e2;
+			const uint32_t mine = lane < kGroups / 4 ? s.gcnt[m] : 0u;
+			const uint32_t winc = warp_incl_scan(mine >> 16, lane);
+			const uint32_t nw = __shfl_sync(full, winc, 31);
+			uint32_t *wl = s.wl[warp];
+			if (mine) list_group_words(s, wl, m, pre & 0xffffu, winc - (mine >> 16));
+			__syncwarp();
 #pragma unroll 1
-			for (uint32_t i = (uint32_t)tid; i < nwords; i += kThreads) {
-				const uint32_t e = smem_wl(s)[i];
+			for (uint32_t i = (uint32_t)lane; i < nw; i += 32u) {
+				const uint32_t e = wl[i];
 				const uint32_t widx = e & 1023u;
-				emit_word_descs<HALO>(s, widx, reinterpret_cast<const uint32_t *>(s.S)[widx], di + (e >> 10));
+				emit_word_descs<HALO>(s, b, widx, reinterpret_cast<const uint32_t *>(s.S)[widx], di + (e >> 10));
 			}
 			if (tid == 0) p.cnt_i[c] = run & 0xffffu;
 		} else if (tid == 0) {
 			p.cnt_i[c] = 0;
 		}
 		if (amb & kFlagCrossed) {
-			__syncthreads();  // wl is dead: Cz takes its place
-			uint16_t *Cz = smem_Cz(s);
+			// plants (lib.rs:412-440) in column order: the ranges of 32 columns before this warp's, then the lanes before this one
+			const uint4 pa = *reinterpret_cast<const uint4 *>(s.pcnt[b]), pb = *reinterpret_cast<const uint4 *>(s.pcnt[b] + 4);
+			const uint32_t lo = warp == 0 ? 0u : warp == 1 ? pa.x : warp == 2 ? pa.x + pa.y : pa.x + pa.y + pa.z;
+			const uint32_t half = pa.x + pa.y + pa.z + pa.w;
+			const uint32_t hi = half + (warp == 0 ? 0u : warp == 1 ? pb.x : warp == 2 ? pb.x + pb.y : pb.x + pb.y + pb.z);
+			uint32_t *dt = p.desc_t + (size_t)c * kDescStrideT;
 #pragma unroll
 			for (int j = 0; j < 256 / kThreads; j++) {
-				const int col = kThreads * j + tid;
-				uint32_t cz = 0;
-				if ((crossed_cols >> j) & 1u) cz = col_crossed(flags, lds_col(raw + col * 16));
-				Cz[col] = (uint16_t)cz;
+				const uint32_t m16 = (cz >> (16 * j)) & 0xffffu;
+				const uint32_t cnt = (uint32_t)__popc(m16);
+				const uint32_t inc = warp_incl_scan(cnt, lane);
+				if (cnt) emit_column_plants(s.raw[b], kThreads * j + tid, m16, dt + (j ? hi : lo) + inc - cnt);
 			}
-			__syncthreads();
-			if (warp == 0) {
-				const uint32_t mine = count_plants8(s, lane);
-				const uint32_t inc = warp_incl_scan(mine, lane);
-				if (mine) emit_plant_descs(s, lane, p.desc_t + (size_t)c * kDescStrideT + (inc - mine));
-				if (lane == 31) p.cnt_t[c] = inc * (uint32_t)kPlantQuads;
-			}
+			if (tid == 0) p.cnt_t[c] = (half + pb.x + pb.y + pb.z + pb.w) * (uint32_t)kPlantQuads;
 		} else if (tid == 0) {
 			p.cnt_t[c] = 0;
 		}
+		// phase A of the next chunk, by every warp as soon as it gets here
+		cz = nxt < p.n ? phase_a(b ^ 1, nxt, ((k + 1u) >> 1) & 1u) : 0u;
+		const uint32_t t = i0; i0 = i1; i1 = i2; i2 = t;
 	}
 	// Programmatic dependent launch: this grid runs beside the expansion of the previous batch; it must
 	// not complete (and so release the expansion of this batch onto the arenas) before that one has.
@@ -477,6 +509,19 @@ __device__ __forceinline__ uint32_t find_chunk(const uint32_t *pre, uint32_t q) 
 	return lo;
 }
 
+// The chunk of the first quad of a tile, found by the whole warp: three rounds of 32 / 32 / 4 probes (128-, 4-, 1-entry
+// strides over the 4096 prefixes) instead of twelve dependent steps per lane.  Same for all lanes.
+// `top` = every 128th prefix, packed (the strided probes themselves would all hit one bank).
+__device__ __forceinline__ uint32_t find_chunk_warp(const uint32_t *pre, const uint32_t *top, uint32_t q0, int lane) {
+	static_assert(kMaxLaunchChunks == 4096, "32 x 32 x 4 probes");
+	const unsigned full = 0xffffffffu;
+	const uint32_t b1 = (uint32_t)__popc(__ballot_sync(full, top[lane] <= q0)) - 1u;     // pre[0] = 0 <= q0: at least one
+	const uint32_t b2 = (uint32_t)__popc(__ballot_sync(full, pre[b1 * 128u + lane * 4] <= q0)) - 1u;
+	const uint32_t base = b1 * 128u + b2 * 4u;
+	const uint32_t b3 = (uint32_t)__popc(__ballot_sync(full, lane < 4 && pre[base + (lane & 3)] <= q0)) - 1u;
+	return base + b3;
+}
+
 __global__ void __launch_bounds__(kExpandThreads, MM_EXPAND_MINBLOCKS) expand_kernel(const ExpandParams p) {
 	extern __shared__ __align__(128) unsigned char smem_raw_bytes[];
 	TabEntry *tab = reinterpret_cast<TabEntry *>(smem_raw_bytes);
@@ -484,7 +529,8 @@ __global__ void __launch_bounds__(kExpandThreads, MM_EXPAND_MINBLOCKS) expand_ke
 	uint32_t *pre_t = pre_i + kExpandPrefixWords;
 	uint32_t *warp_tot = pre_t + kExpandPrefixWords;
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-	unsigned char *stage = smem_raw_bytes + 2048 + 2 * 4 * kExpandPrefixWords + 256 + (size_t)warp * (kStageBytes + 16);
+	uint32_t *top_i = warp_tot + 64, *top_t = top_i + 32;  // every 128th prefix, for the first round of find_chunk_warp
+	unsigned char *stage = smem_raw_bytes + 2048 + 2 * 4 * kExpandPrefixWords + 512 + (size_t)warp * (kStageBytes + 16);
 
 	if (tid < 128) reinterpret_cast<uint4 *>(tab)[tid] = __ldg(reinterpret_cast<const uint4 *>(p.table) + tid);
 	const uint32_t lim = kMaxLaunchChunks;  // find_chunk() may touch every entry below that
@@ -498,6 +544,8 @@ __global__ void __launch_bounds__(kExpandThreads, MM_EXPAND_MINBLOCKS) expand_ke
 	if (tid == 0) trace_mark(p.trace, 1);
 	uint32_t tot_i, tot_t;
 	block_scan_counts(p.cnt_i, p.cnt_t, p.n, lim, pre_i, pre_t, warp_tot, tid, tot_i, tot_t);
+	if (tid < 64) (tid < 32 ? top_i : top_t - 32)[tid] = (tid < 32 ? pre_i : pre_t)[(tid & 31) * 128];
+	__syncthreads();
 	u64 carry_i = 0, carry_t = 0;
 	if (p.carry_in) {
 		carry_i = p.carry_in[0];
@@ -533,11 +581,16 @@ __global__ void __launch_bounds__(kExpandThreads, MM_EXPAND_MINBLOCKS) expand_ke
 	};
 	auto fetch = [&](uint32_t t, Fetched &f) {
 		const bool face = t < tiles_i;
-		const uint32_t q = (face ? t : t - tiles_i) * kTileQuads + (uint32_t)lane;
+		const uint32_t q0 = (face ? t : t - tiles_i) * kTileQuads;
+		const uint32_t q = q0 + (uint32_t)lane;
+		const uint32_t *pre = face ? pre_i : pre_t;
+		// most tiles lie inside one chunk: one search by the warp; only a tile that crosses into the next chunk
+		// (pre[c0 + 1] inside it) sends its lanes searching on their own
+		const uint32_t c0 = MM_EXPAND_WARP_SEARCH ? find_chunk_warp(pre, face ? top_i : top_t, q0, lane) : 0u;
+		const bool one = MM_EXPAND_WARP_SEARCH && pre[c0 + 1] >= q0 + (uint32_t)kTileQuads;
 		f.d = 0; f.ox = 0; f.oy = 0; f.oz = 0;
 		if (q < (face ? tot_i : tot_t)) {
-			const uint32_t *pre = face ? pre_i : pre_t;
-			const uint32_t c = find_chunk(pre, q);
+			const uint32_t c = one ? c0 : find_chunk(pre, q);
 			const uint32_t r = q - pre[c];
 			f.d = face ? __ldg(p.desc_i + (size_t)c * kDescStrideI + r) : __ldg(p.desc_t + (size_t)c * kDescStrideT + (r >> 2));
 			f.ox = __ldg(p.offs + 3 * (size_t)c);

@@ -155,8 +155,13 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, co
 	uint32_t launched = 0;
 	if (timed) MM_CUDA(c, cudaEventRecord(c->ev0, c->stream));
 	const mm::u64 *carry = carry0;  // totals of an earlier piece of the same batch, or NULL
-	for (uint32_t first = 0; first < n; first += mm::kMaxLaunchChunks) {
-		const uint32_t m = std::min<uint32_t>(n - first, mm::kMaxLaunchChunks);
+	// A batch that is waited for right away (mm_mesh_batch) has nothing queued behind it to overlap with, so it is cut
+	// into pieces that overlap with each other: the analysis of piece k+1 runs beside the expansion of piece k.
+	uint32_t step = mm::kMaxLaunchChunks;
+	if (timed && c->sync_pieces > 1 && n > 2 * c->sync_piece_min)
+		step = std::min<uint32_t>(mm::kMaxLaunchChunks, std::max<uint32_t>(c->sync_piece_min, ((n + c->sync_pieces - 1) / c->sync_pieces + 127u) & ~127u));
+	for (uint32_t first = 0; first < n; first += step) {
+		const uint32_t m = std::min<uint32_t>(n - first, step);
 		c->totals_slot ^= 1;
 		mm::AnalyseParams a;
 		a.chunks = d_chunks + (size_t)first * 4096u;
@@ -218,7 +223,7 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, co
 			if (d_halo) MM_CUDA(c, cudaLaunchKernelEx(&cfg, mm::analyse_kernel<true>, a));
 			else MM_CUDA(c, cudaLaunchKernelEx(&cfg, mm::analyse_kernel<false>, a));
 		}
-		c->ticket_base += (mm::u64)m + (mm::u64)grid;  // every CTA draws exactly one ticket >= m
+		c->ticket_base += (mm::u64)m + 2ull * (mm::u64)grid;  // every CTA draws exactly two tickets >= m (it looks two chunks ahead)
 
 		mm::ExpandParams e;
 		e.offs = d_offs + (size_t)first * 3u;
@@ -338,6 +343,8 @@ int mm_ctx_create(int device, mm_ctx **out) {
 		if (const char *e = getenv("MM_PIPE_MIN_CHUNKS")) c->pipe_min_chunks = (uint32_t)std::max(0, atoi(e));
 		c->no_small = getenv("MM_NO_SMALL_PATH") != nullptr;
 		c->no_signal = getenv("MM_NO_SIGNAL") != nullptr;
+		if (const char *e = getenv("MM_SYNC_PIECES")) c->sync_pieces = (uint32_t)std::max(1, atoi(e));
+		if (const char *e = getenv("MM_SYNC_PIECE_MIN")) c->sync_piece_min = (uint32_t)std::max(128, atoi(e));
 		if (const char *e = getenv("MM_MAPPED_MAX_CHUNKS")) c->mapped_max_chunks = (uint32_t)strtoul(e, nullptr, 10);
 		MM_CUDA(c, cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
 		c->stream = c->own_stream;

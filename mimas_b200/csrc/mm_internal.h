@@ -49,6 +49,7 @@ struct mm_ctx {
 	mm_slot *cur = &ring[0];          // slot of the most recent batch: what finish / copy_out / draw_batch refer to
 	uint64_t next_ticket = 1;         // tickets start at 1
 	uint64_t last_signal_ticket = 0;  // completion signal of the most recent batch that launched kernels (counts on its own)
+	uint32_t sync_pieces = 1, sync_piece_min = 512;  // MM_SYNC_PIECES / MM_SYNC_PIECE_MIN: a synchronous batch is cut into that many overlapping pieces
 	bool no_signal = false;           // MM_NO_SIGNAL: batches do not signal, waits synchronise the stream
 	mm::u64 *h_done = nullptr;        // pinned + mapped: ticket of the last batch whose kernels have completed
 	mm::u64 *d_h_done = nullptr;

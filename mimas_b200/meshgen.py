@@ -404,6 +404,15 @@ class Mesher:
         self._ck(self._lib.mm_gen_terrain_device(self._ctx, seed, c0[0], c0[1], c0[2], dims[0], dims[1], dims[2],
                                                  C.c_void_p(d_chunks), C.c_void_p(d_offs)))
 
+    def gen_mapgen_device(self, seed: int, c0, dims, d_chunks: int, d_offs: int, params=None, d_tree_counts: int = 0):
+        """mimas-server mapgen phase one (mapgen.rs:64-245) for a box of chunks, on the device (mm_gen_mapgen_device).
+        `params`: mimas_b200.mapgen.MapgenParams (default: the default game's ores and plants)."""
+        from . import mapgen as mg
+        cp = mg.to_c(params if params is not None else mg.default_mapgen_params())
+        self._ck(self._lib.mm_gen_mapgen_device(self._ctx, seed, C.byref(cp), c0[0], c0[1], c0[2], dims[0], dims[1], dims[2],
+                                                C.c_void_p(d_chunks), C.c_void_p(d_offs) if d_offs else None,
+                                                C.c_void_p(d_tree_counts) if d_tree_counts else None))
+
     def dev_alloc(self, nbytes: int) -> int:
         p = C.c_void_p()
         self._ck(self._lib.mm_dev_alloc(self._ctx, nbytes, C.byref(p)))
