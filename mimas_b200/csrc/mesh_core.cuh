@@ -14,16 +14,13 @@
 // re-formulated as two kernels.
 // ANALYSE (one 128-thread CTA per chunk; "lane" below = the thread's job index in a phase):
 //   A. lane <-> column (x, y): 16 block ids along z (one 16-byte load) -> 16-bit "blocky"
-//      mask over z (and the crossed mask, where the column holds plants)
-//   B. visibility and run-start masks of all six passes as bit operations on z-masks, with SWAR
-//      id-equality masks against the (x, y-1) and (x-1, y) columns where two visible faces meet
-//   C. 16x16 bit-matrix transposes (in registers) turn the z-masks into masks over the
+//      mask over z, plus SWAR id-equality masks against the (x, y-1) and (x-1, y) columns
+//   B. visibility and run-start masks of all six passes as bit operations on z-masks
+//   C. popc of the start masks -> quads per (pass, c1) group, warp scan -> group offsets
+//   D. 16x16 bit-matrix transposes (in registers) turn the z-masks into masks over the
 //      merge axis, one 16-bit word per row (pass, c1, c2) in the reference's emission order;
-//      popc of the start masks -> quads per (pass, c1) group, warp scan -> group offsets
-//   D. every run start becomes one 32-bit quad descriptor (block id, start, row, pass, length)
+//      every run start becomes one 32-bit quad descriptor (block id, start, row, pass, length)
 //      in the chunk's descriptor slot; crossed plants become plant descriptors
-//   Two chunks are in flight per CTA: while chunk k is in phases B-D, chunk k+1 lands in the other
-//   raw buffer and goes through phase A (`b` below = which of the double-buffered pieces a call works on).
 // EXPAND (one warp per tile of 32 quads of the packed stream):
 //   E. exclusive scan of the per-chunk counts (shared memory, redundantly per CTA), quad ->
 //      chunk by binary search, descriptor -> 216 bytes into a staging tile that a bulk async
@@ -83,38 +80,40 @@ struct Col {
 	uint32_t w[4];
 };
 
-// Shared memory of one analysing CTA.  Plain struct so that host emulation can allocate it.
-// Double-buffered (index b): what phase A of the next chunk writes while the current chunk is still being read.
-constexpr int kWlPerWarp = 192;            // a warp lists the non-empty words of its 24 groups (8 words each)
+// Shared memory of one analysing CTA (= one chunk in flight).  Plain struct so that host
+// emulation can allocate it.
 struct alignas(128) ChunkSmem {
-	// the chunks themselves, each filled by one bulk async copy (TMA)
-	alignas(128) unsigned char raw[2][4096];
-	// phase D: per warp, the list of non-empty 32-bit words of S (two rows each) with their quad offsets
-	alignas(16) uint32_t wl[4][kWlPerWarp];
+	// the chunk itself, filled by one bulk async copy (TMA)
+	alignas(128) unsigned char raw[4096];
+	// phase D: wl, the list of non-empty 32-bit words of S (two rows each) with their quad offsets;
+	// plants: Cz, the crossed mask over z per column
+	alignas(16) uint32_t u[768];
 	// run-start masks over z per column: passes 1,3,4,6 (p = 0,2,3,5) at [p][x*16 + y],
 	// passes 2,5 (p = 1,4) at [p][y*16 + x]; every 16-entry block [p][c1*16 ..] is one
 	// (pass, c1) group whose 16 x 16 bit transpose gives the masks over the merge axis
 	alignas(16) uint16_t S[kPasses * 256];
 	alignas(16) uint16_t By[256];              // blocky mask over y for row (x, z): [x*16 + z]
 	alignas(16) uint16_t Bx[256];              // blocky mask over x for row (y, z): [y*16 + z]
-	alignas(16) uint16_t Bzp[2][kBzStride * kBzStride + 4];  // blocky mask over z per column, zero border
-	alignas(16) uint32_t gcnt[kGroups];        // per group: quads | non-empty words << 16
+	alignas(16) uint16_t Bzp[kBzStride * kBzStride + 4];  // blocky mask over z per column, zero border
+	alignas(16) uint32_t gcnt[kGroups];        // per group: quads | non-empty words << 16; then the exclusive prefix of that
 	// halo mode only (an extension, see halo_row): blocky masks of the touching layers of the z-, z+ neighbour
 	// chunks over y per x (Hz[x], Hz[16 + x]) and of the x-, x+, y-, y+ neighbours over the merge axis per z
 	// (Hm[0..15] x- over y, Hm[16..31] x+ over y, Hm[32..47] y- over x, Hm[48..63] y+ over x)
-	alignas(16) uint16_t Hz[2][32];
+	alignas(16) uint16_t Hz[32];
 	alignas(16) uint16_t Hm[64];
-	uint32_t ambw[2][4];                       // per warp: OR of the flag bytes of the cells of its columns
-	uint32_t pcnt[2][8];                       // plants per range of 32 columns (range = column >> 5)
-	uint32_t ticket[3];                        // chunk indices of this and the next two rounds
-	alignas(8) unsigned long long mbar[2];     // mbarriers of the chunk loads (device only)
+	uint32_t amb[2];                           // OR of the flag bytes of the chunk's cells (double buffered)
+	uint32_t ticket[2];                        // chunk index of this / the next round (double buffered)
+	alignas(8) unsigned long long mbar;        // mbarrier of the chunk load (device only)
 };
 
-MM_HD unsigned char *smem_raw(ChunkSmem &s, int b) { return s.raw[b]; }
-MM_HD const unsigned char *smem_raw(const ChunkSmem &s, int b) { return s.raw[b]; }
-MM_HD uint16_t *smem_Bzp(ChunkSmem &s, int b) { return s.Bzp[b]; }
-MM_HD const uint16_t *smem_Bzp(const ChunkSmem &s, int b) { return s.Bzp[b]; }
+MM_HD unsigned char *smem_raw(ChunkSmem &s) { return s.raw; }
+MM_HD uint16_t *smem_Bzp(ChunkSmem &s) { return s.Bzp; }
+MM_HD const uint16_t *smem_Bzp(const ChunkSmem &s) { return s.Bzp; }
+MM_HD uint16_t *smem_Cz(ChunkSmem &s) { return reinterpret_cast<uint16_t *>(s.u); }   // crossed mask over z per column
+MM_HD const uint16_t *smem_Cz(const ChunkSmem &s) { return reinterpret_cast<const uint16_t *>(s.u); }
 // wl entry: index of a non-empty word of S (m*8 + k, 10 bits) | quads of the chunk before it << 10
+MM_HD uint32_t *smem_wl(ChunkSmem &s) { return s.u; }
+MM_HD const uint32_t *smem_wl(const ChunkSmem &s) { return s.u; }
 
 MM_HD int popc32(uint32_t v) {
 #if defined(__CUDA_ARCH__)
@@ -202,16 +201,14 @@ static inline void build_flags(const TabEntry *tab, uint8_t *flags) {
 // Once per CTA (lane = 0..31 of one warp): the zero border of Bzp (a neighbour outside the chunk never blocks,
 // lib.rs:277-280); the interior is rewritten by phase A for every chunk.
 MM_HD void init_warp_smem(ChunkSmem &s, int lane) {
-	for (int b = 0; b < 2; b++) {
-		uint16_t *B = smem_Bzp(s, b);
-		if (lane < kBzStride) {
-			B[lane] = 0;
-			B[(kBzStride - 1) * kBzStride + lane] = 0;
-		}
-		if (lane < 16) {
-			B[(lane + 1) * kBzStride] = 0;
-			B[(lane + 1) * kBzStride + kBzStride - 1] = 0;
-		}
+	uint16_t *B = smem_Bzp(s);
+	if (lane < kBzStride) {
+		B[lane] = 0;
+		B[(kBzStride - 1) * kBzStride + lane] = 0;
+	}
+	if (lane < 16) {
+		B[(lane + 1) * kBzStride] = 0;
+		B[(lane + 1) * kBzStride + kBzStride - 1] = 0;
 	}
 }
 
@@ -245,16 +242,6 @@ MM_HD uint32_t col_flags(const uint8_t *flags, const Col &c, uint32_t &orf) {
 	}
 	orf = o;
 	return acc >> 16;
-}
-
-// The same, with a short cut for a column of one block id (air above the ground, stone below it, water).
-MM_HD uint32_t col_flags_any(const uint8_t *flags, const Col &c, uint32_t &orf) {
-	const uint32_t w0 = c.w[0];
-	if (w0 == c.w[1] && w0 == c.w[2] && w0 == c.w[3] && w0 == byte_perm(w0, 0, 0)) {
-		orf = flags[w0 & 0xffu];
-		return (orf & kFlagBlocky) ? 0xffffu : 0u;
-	}
-	return col_flags(flags, c, orf);
 }
 
 // Bit z set <=> the two columns hold the same block id at z (equal ids => equal textures
@@ -322,9 +309,8 @@ MM_HD uint32_t fix_equal(const TabEntry *tab, const uint8_t *chunk, uint32_t d, 
 // HALO: the border of Bzp and Hz hold the neighbour chunks' touching layers (halo_row); they occlude
 // faces like cells of the chunk do, but a run never continues from them (a row starts at 0, lib.rs:294-313).
 template <bool HALO>
-MM_HD void col_starts(ChunkSmem &s, int b_, const TabEntry *tab, int x, int y, uint32_t amb) {
-	const uint8_t *chunk = smem_raw(s, b_);
-	const uint16_t *B = smem_Bzp(s, b_) + (x + 1) * kBzStride + (y + 1);
+MM_HD void col_starts(ChunkSmem &s, const TabEntry *tab, const uint8_t *chunk, int x, int y, uint32_t amb) {
+	const uint16_t *B = smem_Bzp(s) + (x + 1) * kBzStride + (y + 1);
 	const uint32_t b = B[0];
 	const uint32_t bym = B[-1], byp = B[1], bxm = B[-kBzStride], bxp = B[kBzStride];
 	const uint32_t bmm = B[-kBzStride - 1], bpm = B[kBzStride - 1], bmp = B[-kBzStride + 1];
@@ -332,7 +318,7 @@ MM_HD void col_starts(ChunkSmem &s, int b_, const TabEntry *tab, int x, int y, u
 	// previous cell along the merge axis; cells below z = 0 / above z = 15 of this and of the previous column
 	uint32_t py = bym, px = bxm, zlo = 0, zhi = 0, pzlo = 0, pzhi = 0;
 	if (HALO) {
-		const uint32_t hm = s.Hz[b_][x], hp = s.Hz[b_][16 + x];
+		const uint32_t hm = s.Hz[x], hp = s.Hz[16 + x];
 		py = y > 0 ? bym : 0u;
 		px = x > 0 ? bxm : 0u;
 		zlo = (hm >> y) & 1u;
@@ -415,14 +401,14 @@ MM_HD void transpose16(uint32_t w[8]) {
 
 // Blocky masks over the merge axes, from the z-masks: job 0..15 -> By rows of x = job
 // (bits over y), job 16..31 -> Bx rows of y = job - 16 (bits over x).
-MM_HD void transpose_blocky(ChunkSmem &s, int b_, int job) {
+MM_HD void transpose_blocky(ChunkSmem &s, int job) {
 	uint32_t w[8];
 	const bool over_y = job < 16;
 	const int f = job & 15;
 #pragma unroll
 	for (int k = 0; k < 8; k++) {
 		const int r0 = 2 * k, r1 = 2 * k + 1;
-		const uint16_t *B = smem_Bzp(s, b_);
+		const uint16_t *B = smem_Bzp(s);
 		const uint32_t lo = over_y ? B[(f + 1) * kBzStride + r0 + 1] : B[(r0 + 1) * kBzStride + f + 1];
 		const uint32_t hi = over_y ? B[(f + 1) * kBzStride + r1 + 1] : B[(r1 + 1) * kBzStride + f + 1];
 		w[k] = lo | (hi << 16);
@@ -439,22 +425,22 @@ MM_HD void transpose_blocky(ChunkSmem &s, int b_, int job) {
 // layout as oracle/meshgen_oracle.c blocked()).  Job t = 0..95 takes the 16 ids of row t & 15 of slab
 // t >> 4 (`c`) to a blocky mask: the x / y slabs give masks over z for the border columns of Bzp, the
 // z slabs masks over y per x.
-MM_HD void halo_row(ChunkSmem &s, int b_, const uint8_t *flags, const Col &c, int t) {
+MM_HD void halo_row(ChunkSmem &s, const uint8_t *flags, const Col &c, int t) {
 	uint32_t orf;
 	const uint16_t m = (uint16_t)col_flags(flags, c, orf);
 	const int slab = t >> 4, r = t & 15;
-	uint16_t *B = smem_Bzp(s, b_);
+	uint16_t *B = smem_Bzp(s);
 	if (slab == 0) B[r + 1] = m;
 	else if (slab == 1) B[(kBzStride - 1) * kBzStride + r + 1] = m;
 	else if (slab == 2) B[(r + 1) * kBzStride] = m;
 	else if (slab == 3) B[(r + 1) * kBzStride + kBzStride - 1] = m;
-	else s.Hz[b_][(slab - 4) * 16 + r] = m;
+	else s.Hz[(slab - 4) * 16 + r] = m;
 }
 // Job 0..3: the border masks of the x-, x+, y-, y+ layer (over z per y resp. x) transposed to masks over
 // the merge axis per z, as phase D needs them.
-MM_HD void transpose_halo(ChunkSmem &s, int b_, int job) {
+MM_HD void transpose_halo(ChunkSmem &s, int job) {
 	uint32_t w[8];
-	const uint16_t *B = smem_Bzp(s, b_);
+	const uint16_t *B = smem_Bzp(s);
 #pragma unroll
 	for (int k = 0; k < 8; k++) {
 		uint32_t lo, hi;
@@ -498,14 +484,15 @@ MM_HD uint32_t transpose_group(ChunkSmem &s, int m) {
 	return r;
 }
 
-// Appends the non-empty words of group m to a list.
+// Appends the non-empty words of group m to wl.  `pre` = quads | words << 16 of the groups before m.
 struct alignas(16) Word4 {
 	uint32_t v[4];
 };
-// `wl` = the list (of the calling warp), `q` = quads of the chunk before group m, `o` = entries already in the list.
-MM_HD void list_group_words(const ChunkSmem &s, uint32_t *wl, int m, uint32_t q, uint32_t o) {
+MM_HD void list_group_words(ChunkSmem &s, int m, uint32_t pre) {
 	// the group's eight words as two 16-byte loads: word by word the lanes (32 bytes apart) collide eight-fold
 	const Word4 lo = *reinterpret_cast<const Word4 *>(s.S + m * 16), hi = *reinterpret_cast<const Word4 *>(s.S + m * 16 + 8);
+	uint32_t *wl = smem_wl(s);
+	uint32_t o = pre >> 16, q = pre & 0xffffu;
 #pragma unroll
 	for (int k = 0; k < 8; k++) {
 		const uint32_t w = k < 4 ? lo.v[k] : hi.v[k - 4];
@@ -525,7 +512,7 @@ MM_HD void list_group_words(const ChunkSmem &s, uint32_t *wl, int m, uint32_t q,
 // runs ascending, lib.rs:294-313) to dst[0..popc(word)).  A run (lib.rs:244-271) ends where
 // the next one starts, where the face stops being visible, or at the end of the row.
 template <bool HALO>
-MM_HD void emit_word_descs(const ChunkSmem &s, int b_, uint32_t widx, uint32_t word, uint32_t *dst) {
+MM_HD void emit_word_descs(const ChunkSmem &s, uint32_t widx, uint32_t word, uint32_t *dst) {
 	const int m = (int)(widx >> 3), c2lo = (int)(widx & 7u) * 2;
 	const int p = m >> 4, c1 = m & 15;
 	const bool xin = (p == 1 || p == 4);
@@ -537,8 +524,8 @@ MM_HD void emit_word_descs(const ChunkSmem &s, int b_, uint32_t widx, uint32_t w
 	// beyond the chunk: nothing (lib.rs:277-280), or the neighbour chunk's layer in halo mode
 	uint32_t out = 0;
 	if (HALO) {
-		if (p == 0) out = s.Hz[b_][c1];
-		else if (p == 3) out = (uint32_t)s.Hz[b_][16 + c1] << 16;
+		if (p == 0) out = s.Hz[c1];
+		else if (p == 3) out = (uint32_t)s.Hz[16 + c1] << 16;
 		else out = *reinterpret_cast<const uint32_t *>(s.Hm + (p == 2 ? 0 : p == 5 ? 16 : p == 1 ? 32 : 48) + c2lo);
 	}
 	if (p == 0) nb = (b << 16) | (c2lo > 0 ? (uint32_t)Bm[-1] : out);                  // [0,0,-1]: row c2-1
@@ -554,20 +541,32 @@ MM_HD void emit_word_descs(const ChunkSmem &s, int b_, uint32_t widx, uint32_t w
 		const int bit = ffs32(rest) - 1;  // = (c2 & 1) * 16 + st
 		rest &= rest - 1u;
 		const int len = ffs32((T >> bit) | (0x80000000u >> bit));  // .. | end of the high row
-		const uint32_t id = s.raw[b_][cell0 + ((bit & 15) << sh) + (bit >> 4)];
+		const uint32_t id = s.raw[cell0 + ((bit & 15) << sh) + (bit >> 4)];
 		*dst++ = base | ((uint32_t)bit << 8) | ((uint32_t)len << 23) | id;
 	} while (rest);
 }
 
-// Crossed plants (lib.rs:412-440), x outer, y, z inner = linear cell order = column order, z ascending.
-// Plant descriptor: bits 0-7 block id | 8-19 cell index.  Writes the plants of one column (`cz` = its crossed
-// mask over z) to dst[0..popc(cz)).
-MM_HD void emit_column_plants(const uint8_t *raw, int col, uint32_t cz, uint32_t *dst) {
-	while (cz) {
-		const int z = ffs32(cz) - 1;
-		cz &= cz - 1u;
-		const int cell = col * 16 + z;
-		*dst++ = (uint32_t)raw[cell] | ((uint32_t)cell << 8);
+// Crossed plants (lib.rs:412-440), x outer, y, z inner = linear cell order.  Cz[col] = crossed
+// mask over z of column col = x*16 + y; this lane covers columns lane*8 .. lane*8+7.
+MM_HD uint32_t count_plants8(const ChunkSmem &s, int lane) {
+	const uint32_t *p = reinterpret_cast<const uint32_t *>(smem_Cz(s) + lane * 8);
+	uint32_t c = 0;
+#pragma unroll
+	for (int k = 0; k < 4; k++) c += (uint32_t)popc32(p[k]);
+	return c;
+}
+// Plant descriptor: bits 0-7 block id | 8-19 cell index.
+MM_HD void emit_plant_descs(const ChunkSmem &s, int lane, uint32_t *dst) {
+#pragma unroll 1
+	for (int k = 0; k < 8; k++) {
+		const int col = lane * 8 + k;
+		uint32_t mask = smem_Cz(s)[col];
+		while (mask) {
+			const int z = ffs32(mask) - 1;
+			mask &= mask - 1u;
+			const int cell = col * 16 + z;
+			*dst++ = (uint32_t)s.raw[cell] | ((uint32_t)cell << 8);
+		}
 	}
 }
 

@@ -72,25 +72,7 @@ struct ExpandParams {
 	u64 *totals;                  // [0] quads in out_i, [1] quad slots in out_t after this launch
 	u64 *host_totals;             // the same two words in mapped pinned host memory
 	u64 *trace;                   // NULL, or 4 words of this launch: first CTA start, first CTA past the wait, -, last CTA end (ns)
-	uint32_t *done_count;         // CTAs of this launch that have finished (the last one signals and resets it)
-	u64 *h_done;                  // NULL, or mapped pinned host word that receives done_ticket once every vertex has landed
-	u64 done_ticket;
 };
-
-// Called by every thread of a CTA after its last store has completed: the last CTA of the grid to get here tells
-// the host (mm_batch_wait polls the word), so that a batch can be handed to a consumer while later ones still run.
-__device__ __forceinline__ void signal_batch_done(uint32_t *done_count, u64 *h_done, u64 ticket, uint32_t ctas) {
-	if (h_done == nullptr) return;
-	__syncthreads();
-	if (threadIdx.x == 0) {
-		__threadfence();
-		if (ctas == 1u || atomicAdd(done_count, 1u) == ctas - 1u) {
-			if (ctas != 1u) *done_count = 0;
-			__threadfence_system();
-			*reinterpret_cast<volatile u64 *>(h_done) = ticket;  // posted write; nothing waits for it here
-		}
-	}
-}
 
 struct AnalyseParams {
 	const unsigned char *chunks;  // n * 4096
@@ -105,6 +87,11 @@ struct AnalyseParams {
 	u64 *ticket;                  // monotonically increasing across launches
 	u64 ticket_base;              // its value at launch
 	u64 *trace;                   // NULL, or 4 words of this launch: first CTA start, -, last CTA work done, last CTA end (ns)
+	// Completion signal of the batch BEFORE this launch: once this kernel is past its dependency wait, everything
+	// launched earlier on the stream has completed, and one thread says so to the host (mm_batch_wait polls the
+	// word) -- a batch can be handed to a consumer while later ones still run, at no cost to the batch itself.
+	u64 *h_done;                  // NULL, or mapped pinned host word
+	u64 prev_done;                // what to write there
 	ExpandParams x;               // FUSED instantiation only: where the one chunk's vertices go
 };
 
@@ -198,12 +185,7 @@ __device__ __forceinline__ void store_tile(unsigned char *g, const unsigned char
 }
 
 // ---- kernel 1: analysis ------------------------------------------------------------------
-// One CTA of kThreads threads per chunk being analysed; CTAs are persistent and draw chunk tickets.  A CTA keeps
-// two chunks in flight: while chunk k goes through phases B-D, chunk k+1 lands in the other raw buffer (TMA,
-// issued a whole chunk ahead) and every warp takes it through phase A as soon as the warp itself is done with
-// k -- so no warp waits at a barrier for the slowest one to finish a chunk, and the load latency is never seen.
-// Barriers per chunk: (a) phase A complete / everyone done with the previous chunk, (b) run starts complete,
-// (c) transposes and counts complete; an empty chunk (no cube, no plant: a quarter of a terrain region) stops at (a).
+// One CTA of kThreads threads per chunk in flight; CTAs are persistent and draw chunk tickets.
 // HALO = the optional mode in which the touching layers of the six neighbour chunks occlude faces (an
 // extension; false = the reference's semantics, lib.rs:277-280, and the instantiation every number in
 // DESIGN.md is measured on).
@@ -223,159 +205,136 @@ __global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(co
 	if (tid == 0) trace_mark(p.trace, 0);
 	if (tid < 16) reinterpret_cast<uint4 *>(flags)[tid] = __ldg(reinterpret_cast<const uint4 *>(p.flags) + tid);
 	if (warp == 1) init_warp_smem(s, lane);
-	// FUSED: one CTA, one chunk -- no ticket is drawn, so a following launch may draw its own at once
-	uint32_t fused_drawn = 0;
-	auto draw = [&]() -> uint32_t {
-		if (FUSED) return fused_drawn++ == 0 ? 0u : 0xffffffffu;
-		return (uint32_t)min(atomicAdd(p.ticket, 1ull) - p.ticket_base, (u64)0xffffffffu);
-	};
 	if (tid == 0) {
-		mbar_init(&s.mbar[0]);
-		mbar_init(&s.mbar[1]);
-		fence_proxy_async_smem();  // the barriers are visible to the bulk-copy engine
-		const uint32_t t0 = draw();
-		s.ticket[0] = t0;
-		if (t0 < p.n) bulk_load_g2s(s.raw[0], p.chunks + (size_t)t0 * 4096u, 4096u, &s.mbar[0]);  // TMA: 4 KiB chunk -> shared memory
-		const uint32_t t1 = draw();
-		s.ticket[1] = t1;
-#if MM_ANALYSE_PREFETCH
-		if (t1 < p.n) bulk_prefetch_l2(p.chunks + (size_t)t1 * 4096u, 4096u);
-#endif
+		mbar_init(&s.mbar);
+		fence_proxy_async_smem();  // the barrier is visible to the bulk-copy engine
+		// FUSED: one CTA, one chunk -- no ticket is drawn, so a following launch may draw its own at once
+		s.ticket[0] = FUSED ? 0u : (uint32_t)min(atomicAdd(p.ticket, 1ull) - p.ticket_base, (u64)0xffffffffu);
+		s.amb[0] = 0;
 	}
+	unsigned char *raw = smem_raw(s);
 	const TabEntry *tab = p.table;  // only read for chunks with ambiguous ids (fix_equal)
-
-	// Phase A of chunk `c` in buffer `b`: thread <-> columns col = tid, tid + 128 (col = x*16 + y): blocky mask over z
-	// per column into Bzp[b]; what the warp's columns hold (flag bytes ORed, plants per range of 32 columns) into
-	// ambw[b] / pcnt[b].  Returns the crossed masks over z of the thread's two columns (low / high half).
-	auto phase_a = [&](int b, uint32_t c, uint32_t parity) -> uint32_t {
+	uint32_t par = 0;
+	for (;; par ^= 1u) {
+		__syncthreads();  // the previous chunk is done with shared memory; this round's ticket is visible
+		const uint32_t c = s.ticket[par];
+		if (c >= p.n) break;
+		if (tid == 0) {
+			bulk_load_g2s(raw, p.chunks + (size_t)c * 4096u, 4096u, &s.mbar);  // TMA: 4 KiB chunk -> shared memory
+			// the next ticket travels while this chunk is analysed
+			const uint32_t nxt = FUSED ? 0xffffffffu : (uint32_t)min(atomicAdd(p.ticket, 1ull) - p.ticket_base, (u64)0xffffffffu);
+			s.ticket[par ^ 1u] = nxt;
+			s.amb[par ^ 1u] = 0;
+#if MM_ANALYSE_PREFETCH
+			if (nxt < p.n) bulk_prefetch_l2(p.chunks + (size_t)nxt * 4096u, 4096u);  // and its chunk comes as far as L2
+#endif
+		}
 		Col hrow;
 		if (HALO && tid < 96) {  // one 16-byte row of the halo slabs per thread, in flight beside the chunk
 			const uint4 v = __ldg(reinterpret_cast<const uint4 *>(p.halo + (size_t)c * 1536u) + tid);
 			hrow.w[0] = v.x; hrow.w[1] = v.y; hrow.w[2] = v.z; hrow.w[3] = v.w;
 		}
-		mbar_wait(&s.mbar[b], parity);
-		const unsigned char *raw = s.raw[b];
-		uint32_t amb = 0, czp = 0;
+		mbar_wait(&s.mbar, par);
+
+		// A. thread <-> columns col = tid, tid + 128 (col = x*16 + y): blocky mask over z per column
+		uint32_t crossed_cols = 0, amb = 0;
+		Col own[256 / kThreads];
+		bool uniform = true;
+#pragma unroll
+		for (int j = 0; j < 256 / kThreads; j++) {
+			own[j] = load_col(raw + (kThreads * j + tid) * 16);
+			const uint32_t w0 = own[j].w[0];
+			uniform = uniform && w0 == own[j].w[1] && w0 == own[j].w[2] && w0 == own[j].w[3] &&
+			          w0 == __byte_perm(w0, 0, 0) && w0 == *reinterpret_cast<const uint32_t *>(raw);
+		}
+		// a chunk of one undrawn id (all air: a quarter of a terrain region) is done here
+		if (MM_ANALYSE_UNIFORM_EXIT && __syncthreads_and(uniform) && (flags[raw[0]] & (kFlagBlocky | kFlagCrossed)) == 0) {
+			if (tid == 0) {
+				p.cnt_i[c] = 0;
+				p.cnt_t[c] = 0;
+			}
+			continue;
+		}
+		if (HALO && tid < 96) halo_row(s, flags, hrow, tid);
 #pragma unroll
 		for (int j = 0; j < 256 / kThreads; j++) {
 			const int col = kThreads * j + tid;
-			const Col own = load_col(raw + col * 16);
 			uint32_t orf;
-			const uint32_t bz = col_flags_any(flags, own, orf);
-			smem_Bzp(s, b)[((col >> 4) + 1) * kBzStride + (col & 15) + 1] = (uint16_t)bz;
-			if (orf & kFlagCrossed) czp |= col_crossed(flags, own) << (16 * j);
+			const uint32_t bz = col_flags(flags, own[j], orf);
+			smem_Bzp(s)[((col >> 4) + 1) * kBzStride + (col & 15) + 1] = (uint16_t)bz;
+			crossed_cols |= ((orf >> 1) & 1u) << j;
 			amb |= orf;
 		}
-		if (HALO && tid < 96) halo_row(s, b, flags, hrow, tid);
 		amb = __reduce_or_sync(full, amb);
-		uint32_t n0 = 0, n1 = 0;
-		if (amb & kFlagCrossed) {
-			n0 = __reduce_add_sync(full, (uint32_t)__popc(czp & 0xffffu));
-			n1 = __reduce_add_sync(full, (uint32_t)__popc(czp >> 16));
-		}
-		if (lane == 0) {
-			s.ambw[b][warp] = amb;
-			s.pcnt[b][warp] = n0;
-			s.pcnt[b][4 + warp] = n1;
-		}
-		return czp;
-	};
-
-	__syncthreads();  // tickets, flag table, zero borders
-	uint32_t cz = 0;
-	if (s.ticket[0] < p.n) cz = phase_a(0, s.ticket[0], 0u);
-	uint32_t i0 = 0, i1 = 1, i2 = 2;  // ticket slots of this round, the next, the one after
-#pragma unroll 1
-	for (uint32_t k = 0;; k++) {
-		const int b = (int)(k & 1u);
-		const uint32_t c = s.ticket[i0];
-		if (c >= p.n) break;
-		__syncthreads();  // (a) phase A of this chunk is complete; everyone is done with the previous chunk
-		const uint32_t nxt = s.ticket[i1];
-		if (tid == 0) {
-			// the next chunk lands in the other buffer while this one is analysed; the ticket after it travels meanwhile
-			if (nxt < p.n) bulk_load_g2s(s.raw[b ^ 1], p.chunks + (size_t)nxt * 4096u, 4096u, &s.mbar[b ^ 1]);
-			const uint32_t t2 = draw();
-			s.ticket[i2] = t2;
-#if MM_ANALYSE_PREFETCH
-			if (t2 < p.n) bulk_prefetch_l2(p.chunks + (size_t)t2 * 4096u, 4096u);  // and its chunk comes as far as L2
-#endif
-		}
-		const uint4 aw = *reinterpret_cast<const uint4 *>(s.ambw[b]);
-		const uint32_t amb = aw.x | aw.y | aw.z | aw.w;
+		if (lane == 0 && amb) atomicOr(&s.amb[par], amb);
+		__syncthreads();
+		amb = s.amb[par];
 		if (amb & kFlagBlocky) {  // else: no cube in the chunk (e.g. all air)
 			uint32_t *di = p.desc_i + (size_t)c * kDescStrideI;
 			// B. run starts over z for the six passes
 #pragma unroll 1
 			for (int j = 0; j < 256 / kThreads; j++) {
 				const int col = kThreads * j + tid;
-				col_starts<HALO>(s, b, tab, col >> 4, col & 15, amb);
+				col_starts<HALO>(s, tab, raw, col >> 4, col & 15, amb);
 			}
-			__syncthreads();  // (b)
+			__syncthreads();
 			// C. masks over the merge axes: 32 blocky jobs + 96 groups = one job per thread
-			if (tid < 32) transpose_blocky(s, b, tid);
+			if (tid < 32) transpose_blocky(s, tid);
 			else s.gcnt[tid - 32] = transpose_group(s, tid - 32);
-			if (HALO && tid >= 124) transpose_halo(s, b, tid - 124);  // Bzp's border is read-only here
-			__syncthreads();  // (c)
+			if (HALO && tid >= 124) transpose_halo(s, tid - 124);  // Bzp's border is read-only here
+			__syncthreads();
 			// exclusive scan of quads (low half) and non-empty words (high half) over the 96 groups, by every warp
-			// for itself (no hand-over through shared memory)
-			uint32_t run = 0, ex[3];
+			// for itself (no hand-over through shared memory, one barrier less): the thread of group
+			// m = tid - 32 = (warp - 1) * 32 + lane finds its own prefix in round warp - 1
+			uint32_t run = 0, mine = 0;
 #pragma unroll
-			for (int r = 0; r < 3; r++) {
-				const uint32_t v = s.gcnt[lane + 32 * r];
+			for (int k = 0; k < 3; k++) {
+				const uint32_t v = s.gcnt[lane + 32 * k];
 				const uint32_t inc = warp_incl_scan(v, lane);
-				ex[r] = run + inc - v;
+				if (k == warp - 1) mine = run + inc - v;
 				run += __shfl_sync(full, inc, 31);
 			}
-			// D. descriptors.  Warp w owns the groups m = w (mod 4) -- a quarter of the rows of every pass --: lane <-> group
-			// lists the group's non-empty words (two rows each) in the warp's own list, then lane <-> word writes one 32-bit
-			// descriptor per run start.  Nothing here crosses warps.
-			const int m = 4 * lane + warp;
-			const uint32_t e0 = __shfl_sync(full, ex[0], m & 31), e1 = __shfl_sync(full, ex[1], m & 31), e2 = __shfl_sync(full, ex[2], m & 31);
-			const uint32_t pre = (m >> 5) == 0 ? e0 : (m >> 5) == 1 ? e1 : e2;
-			const uint32_t mine = lane < kGroups / 4 ? s.gcnt[m] : 0u;
-			const uint32_t winc = warp_incl_scan(mine >> 16, lane);
-			const uint32_t nw = __shfl_sync(full, winc, 31);
-			uint32_t *wl = s.wl[warp];
-			if (mine) list_group_words(s, wl, m, pre & 0xffffu, winc - (mine >> 16));
-			__syncwarp();
+			if (tid >= 32) list_group_words(s, tid - 32, mine);
+			__syncthreads();
+			// D. descriptors: thread <-> non-empty word (two rows)
+			const uint32_t nwords = run >> 16;
 #pragma unroll 1
-			for (uint32_t i = (uint32_t)lane; i < nw; i += 32u) {
-				const uint32_t e = wl[i];
+			for (uint32_t i = (uint32_t)tid; i < nwords; i += kThreads) {
+				const uint32_t e = smem_wl(s)[i];
 				const uint32_t widx = e & 1023u;
-				emit_word_descs<HALO>(s, b, widx, reinterpret_cast<const uint32_t *>(s.S)[widx], di + (e >> 10));
+				emit_word_descs<HALO>(s, widx, reinterpret_cast<const uint32_t *>(s.S)[widx], di + (e >> 10));
 			}
 			if (tid == 0) p.cnt_i[c] = run & 0xffffu;
 		} else if (tid == 0) {
 			p.cnt_i[c] = 0;
 		}
 		if (amb & kFlagCrossed) {
-			// plants (lib.rs:412-440) in column order: the ranges of 32 columns before this warp's, then the lanes before this one
-			const uint4 pa = *reinterpret_cast<const uint4 *>(s.pcnt[b]), pb = *reinterpret_cast<const uint4 *>(s.pcnt[b] + 4);
-			const uint32_t lo = warp == 0 ? 0u : warp == 1 ? pa.x : warp == 2 ? pa.x + pa.y : pa.x + pa.y + pa.z;
-			const uint32_t half = pa.x + pa.y + pa.z + pa.w;
-			const uint32_t hi = half + (warp == 0 ? 0u : warp == 1 ? pb.x : warp == 2 ? pb.x + pb.y : pb.x + pb.y + pb.z);
-			uint32_t *dt = p.desc_t + (size_t)c * kDescStrideT;
+			__syncthreads();  // wl is dead: Cz takes its place
+			uint16_t *Cz = smem_Cz(s);
 #pragma unroll
 			for (int j = 0; j < 256 / kThreads; j++) {
-				const uint32_t m16 = (cz >> (16 * j)) & 0xffffu;
-				const uint32_t cnt = (uint32_t)__popc(m16);
-				const uint32_t inc = warp_incl_scan(cnt, lane);
-				if (cnt) emit_column_plants(s.raw[b], kThreads * j + tid, m16, dt + (j ? hi : lo) + inc - cnt);
+				const int col = kThreads * j + tid;
+				uint32_t cz = 0;
+				if ((crossed_cols >> j) & 1u) cz = col_crossed(flags, lds_col(raw + col * 16));
+				Cz[col] = (uint16_t)cz;
 			}
-			if (tid == 0) p.cnt_t[c] = (half + pb.x + pb.y + pb.z + pb.w) * (uint32_t)kPlantQuads;
+			__syncthreads();
+			if (warp == 0) {
+				const uint32_t mine = count_plants8(s, lane);
+				const uint32_t inc = warp_incl_scan(mine, lane);
+				if (mine) emit_plant_descs(s, lane, p.desc_t + (size_t)c * kDescStrideT + (inc - mine));
+				if (lane == 31) p.cnt_t[c] = inc * (uint32_t)kPlantQuads;
+			}
 		} else if (tid == 0) {
 			p.cnt_t[c] = 0;
 		}
-		// phase A of the next chunk, by every warp as soon as it gets here
-		cz = nxt < p.n ? phase_a(b ^ 1, nxt, ((k + 1u) >> 1) & 1u) : 0u;
-		const uint32_t t = i0; i0 = i1; i1 = i2; i2 = t;
 	}
 	// Programmatic dependent launch: this grid runs beside the expansion of the previous batch; it must
 	// not complete (and so release the expansion of this batch onto the arenas) before that one has.
 	if (tid == 0) trace_mark(p.trace, 2);
 	pdl_wait();
 	if (tid == 0) trace_mark(p.trace, 3);
+	if (p.h_done != nullptr && blockIdx.x == 0 && tid == 0) *reinterpret_cast<volatile u64 *>(p.h_done) = p.prev_done;
 	if (FUSED) pdl_launch_dependents();
 	if (FUSED) {  // p.n == 1, one CTA: the chunk's descriptors and counts are this CTA's own writes
 		__shared__ __align__(16) unsigned char stage_all[kWarpsPerCta * (kStageBytes + 16)];
@@ -415,7 +374,6 @@ __global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(co
 			if (lane == 0) store_tile(g, sp, tn * kQuadBytes);
 		}
 		if (lane == 0) bulk_wait_all();
-		signal_batch_done(x.done_count, x.h_done, x.done_ticket, 1u);
 	}
 }
 
@@ -622,7 +580,6 @@ __global__ void __launch_bounds__(kExpandThreads, MM_EXPAND_MINBLOCKS) expand_ke
 		if (MM_EXPAND_PREFETCH) cur = nxt;
 	}
 	if (lane == 0) bulk_wait_all();  // all bulk stores of this warp have landed before it exits
-	signal_batch_done(p.done_count, p.h_done, p.done_ticket, gridDim.x);
 	if (tid == 0) trace_mark(p.trace, 3);
 }
 

@@ -147,21 +147,18 @@ Targets slot_targets(const mm_slot *sl) {
 	return Targets{sl->d_out_i, sl->d_out_t, sl->cap_i, sl->cap_t, sl->d_ranges_i, sl->d_ranges_t, sl->d_h_totals};
 }
 
-// `signal` != 0: the last kernel of the batch writes it to c->h_done once every vertex has landed (mm_batch_wait).
+// The first kernel of the call carries the completion signal of the newest batch launched before it (see
+// AnalyseParams::h_done): once it is past its dependency wait, that batch has landed.
 int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, const unsigned char *d_halo, uint32_t n,
-           bool timed, const Targets &tg, const mm::u64 *carry0 = nullptr, uint64_t signal = 0, uint32_t *launches = nullptr) {
+           bool timed, const Targets &tg, const mm::u64 *carry0 = nullptr, uint32_t *launches = nullptr) {
 	int rc;
 	if ((rc = ensure_desc_capacity(c, n))) return rc;
 	uint32_t launched = 0;
+	uint64_t prev_done = c->last_signal_ticket > c->signalled_upto ? c->last_signal_ticket : 0;
 	if (timed) MM_CUDA(c, cudaEventRecord(c->ev0, c->stream));
 	const mm::u64 *carry = carry0;  // totals of an earlier piece of the same batch, or NULL
-	// A batch that is waited for right away (mm_mesh_batch) has nothing queued behind it to overlap with, so it is cut
-	// into pieces that overlap with each other: the analysis of piece k+1 runs beside the expansion of piece k.
-	uint32_t step = mm::kMaxLaunchChunks;
-	if (timed && c->sync_pieces > 1 && n > 2 * c->sync_piece_min)
-		step = std::min<uint32_t>(mm::kMaxLaunchChunks, std::max<uint32_t>(c->sync_piece_min, ((n + c->sync_pieces - 1) / c->sync_pieces + 127u) & ~127u));
-	for (uint32_t first = 0; first < n; first += step) {
-		const uint32_t m = std::min<uint32_t>(n - first, step);
+	for (uint32_t first = 0; first < n; first += mm::kMaxLaunchChunks) {
+		const uint32_t m = std::min<uint32_t>(n - first, mm::kMaxLaunchChunks);
 		c->totals_slot ^= 1;
 		mm::AnalyseParams a;
 		a.chunks = d_chunks + (size_t)first * 4096u;
@@ -179,6 +176,10 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, co
 		a.ticket_base = c->ticket_base;
 		mm::u64 *tr = c->d_trace ? c->d_trace + 8 * (c->trace_next++ % c->trace_pairs) : nullptr;
 		a.trace = tr;
+		a.h_done = prev_done ? c->d_h_done : nullptr;
+		a.prev_done = prev_done;
+		if (prev_done) c->signalled_upto = prev_done;
+		prev_done = 0;
 		cudaLaunchAttribute attr[1];
 		attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
 		attr[0].val.programmaticStreamSerializationAllowed = c->use_pdl ? 1 : 0;
@@ -197,9 +198,6 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, co
 			e.totals = c->d_ticket + 2 + 2 * c->totals_slot;
 			e.host_totals = tg.host_totals;
 			e.trace = nullptr;
-			e.done_count = c->d_done_count;
-			e.h_done = signal ? c->d_h_done : nullptr;
-			e.done_ticket = signal;
 			cudaLaunchConfig_t cfg = {};
 			cfg.gridDim = dim3(1);
 			cfg.blockDim = dim3(mm::kThreads);
@@ -223,7 +221,7 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, co
 			if (d_halo) MM_CUDA(c, cudaLaunchKernelEx(&cfg, mm::analyse_kernel<true>, a));
 			else MM_CUDA(c, cudaLaunchKernelEx(&cfg, mm::analyse_kernel<false>, a));
 		}
-		c->ticket_base += (mm::u64)m + 2ull * (mm::u64)grid;  // every CTA draws exactly two tickets >= m (it looks two chunks ahead)
+		c->ticket_base += (mm::u64)m + (mm::u64)grid;  // every CTA draws exactly one ticket >= m
 
 		mm::ExpandParams e;
 		e.offs = d_offs + (size_t)first * 3u;
@@ -243,10 +241,6 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, co
 		e.totals = c->d_ticket + 2 + 2 * c->totals_slot;
 		e.host_totals = tg.host_totals;
 		e.trace = tr ? tr + 4 : nullptr;
-		const bool last_pair = first + m >= n;
-		e.done_count = c->d_done_count;
-		e.h_done = signal && last_pair ? c->d_h_done : nullptr;
-		e.done_ticket = signal;
 		// programmatic dependent launch (see the kernels): analysis of batch k+1 beside expansion of batch k
 		cudaLaunchConfig_t cfg = {};
 		cfg.gridDim = dim3((unsigned)c->expand_grid);
@@ -265,29 +259,20 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, co
 	return MM_OK;
 }
 
-// Blocks until the device has signalled `seq` (written by the last kernel of a batch to mapped host memory).
-// The newest batch is simply waited for on the stream; an older one is polled for, so that the batches behind
-// it keep running.
+// Blocks until batch `seq` has landed.  A batch with a later launch behind it is signalled by that launch (mapped host
+// word, polled here -- the batches behind it keep running); the newest one is waited for on the stream.
 int wait_signal(mm_ctx *c, uint64_t seq) {
 	volatile mm::u64 *done = c->h_done;
-	if (c->no_signal) {  // MM_NO_SIGNAL: every wait is a stream synchronisation
-		MM_CUDA(c, cudaStreamSynchronize(c->stream));
-		return MM_OK;
-	}
 	if (*done >= seq) return MM_OK;
-	if (seq == c->last_signal_ticket) {
+	if (seq > c->signalled_upto) {  // nothing on the stream carries its signal
 		MM_CUDA(c, cudaStreamSynchronize(c->stream));
-		if (*done < seq) return fail(c, MM_ERR_CUDA, "batch %llu: stream idle but completion not signalled", (unsigned long long)seq);
 		return MM_OK;
 	}
 	for (uint32_t spin = 0;; spin++) {
 		if (*done >= seq) return MM_OK;
 		if ((spin & 1023u) == 1023u) {
 			const cudaError_t e = cudaStreamQuery(c->stream);
-			if (e == cudaSuccess) {
-				if (*done >= seq) return MM_OK;
-				return fail(c, MM_ERR_CUDA, "batch %llu: stream idle but completion not signalled", (unsigned long long)seq);
-			}
+			if (e == cudaSuccess) return MM_OK;  // the stream has drained: everything has landed
 			if (e != cudaErrorNotReady) return fail(c, MM_ERR_CUDA, "cudaStreamQuery: %s", cudaGetErrorString(e));
 		}
 		std::this_thread::yield();
@@ -342,9 +327,6 @@ int mm_ctx_create(int device, mm_ctx **out) {
 		c->fuse_single = getenv("MM_NO_FUSED_SINGLE") == nullptr;
 		if (const char *e = getenv("MM_PIPE_MIN_CHUNKS")) c->pipe_min_chunks = (uint32_t)std::max(0, atoi(e));
 		c->no_small = getenv("MM_NO_SMALL_PATH") != nullptr;
-		c->no_signal = getenv("MM_NO_SIGNAL") != nullptr;
-		if (const char *e = getenv("MM_SYNC_PIECES")) c->sync_pieces = (uint32_t)std::max(1, atoi(e));
-		if (const char *e = getenv("MM_SYNC_PIECE_MIN")) c->sync_piece_min = (uint32_t)std::max(128, atoi(e));
 		if (const char *e = getenv("MM_MAPPED_MAX_CHUNKS")) c->mapped_max_chunks = (uint32_t)strtoul(e, nullptr, 10);
 		MM_CUDA(c, cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
 		c->stream = c->own_stream;
@@ -363,8 +345,6 @@ int mm_ctx_create(int device, mm_ctx **out) {
 		MM_CUDA(c, cudaHostAlloc(&c->h_done, sizeof(mm::u64), cudaHostAllocMapped));
 		MM_CUDA(c, cudaHostGetDevicePointer((void **)&c->d_h_done, c->h_done, 0));
 		*c->h_done = 0;
-		MM_CUDA(c, cudaMalloc(&c->d_done_count, sizeof(uint32_t)));
-		MM_CUDA(c, cudaMemset(c->d_done_count, 0, sizeof(uint32_t)));
 		MM_CUDA(c, cudaStreamCreateWithFlags(&c->s_draw, cudaStreamNonBlocking));
 		return MM_OK;
 	};
@@ -385,7 +365,6 @@ int mm_ctx_destroy(mm_ctx *c) {
 	if (c->s_draw) cudaStreamSynchronize(c->s_draw);
 	for (uint32_t k = 0; k < kMaxRingSlots; k++) free_slot(&c->ring[k]);
 	cudaFree(c->d_table); cudaFree(c->d_cnt); cudaFree(c->d_desc_i); cudaFree(c->d_desc_t); cudaFree(c->d_flags); cudaFree(c->d_ticket);
-	cudaFree(c->d_done_count);
 	if (c->h_done) cudaFreeHost(c->h_done);
 	if (c->s_draw) cudaStreamDestroy(c->s_draw);
 	cudaFree(c->d_in_chunks); cudaFree(c->d_in_offs); cudaFree(c->d_in_halo); cudaFree(c->d_trace);
@@ -546,9 +525,8 @@ static int submit(mm_ctx *c, const uint8_t *d_chunks, const int64_t *d_offs, con
 	sl->last_timed = c->time_next;
 	sl->wait_ticket = c->last_signal_ticket;  // an empty batch is complete when everything before it is
 	if (n) {
-		const uint64_t seq = c->no_signal ? 0 : c->last_signal_ticket + 1;  // completion signals count on their own: a re-run takes one too
-		if ((rc = launch(c, d_chunks, sl->last_offs, d_halo, n, c->time_next, slot_targets(sl), nullptr, seq, &sl->last_launches))) return rc;
-		if (seq) sl->wait_ticket = c->last_signal_ticket = seq;
+		if ((rc = launch(c, d_chunks, sl->last_offs, d_halo, n, c->time_next, slot_targets(sl), nullptr, &sl->last_launches))) return rc;
+		sl->wait_ticket = ++c->last_signal_ticket;  // completion signals count on their own: a re-run takes one too
 	}
 	c->time_next = false;
 	sl->ticket = t;
@@ -615,11 +593,10 @@ static int finish_slot(mm_ctx *c, mm_slot *sl) {
 			// grow to fit (+1/8 head room) and run again: the inputs are still resident
 			if ((rc = ensure_arena(c, &sl->d_out_i, &sl->cap_i, sl->tot_i + sl->tot_i / 8))) return rc;
 			if ((rc = ensure_arena(c, &sl->d_out_t, &sl->cap_t, sl->tot_t + sl->tot_t / 8))) return rc;
-			const uint64_t again = c->no_signal ? 0 : c->last_signal_ticket + 1;
 			if ((rc = launch(c, sl->last_chunks, sl->last_offs, sl->last_halo, sl->last_n, sl->last_timed, slot_targets(sl), nullptr,
-			                 again, &sl->last_launches)))
+			                 &sl->last_launches)))
 				return rc;
-			if (again) sl->wait_ticket = c->last_signal_ticket = again;
+			sl->wait_ticket = ++c->last_signal_ticket;
 		}
 		sl->last_ms = 0.f;  // an untimed (mm_mesh_batch_async) batch enqueues kernels only
 		if (sl->last_timed) {
@@ -662,8 +639,8 @@ int mm_batch_poll(mm_ctx *c, uint64_t ticket, int *done) {
 	if (!c || !ticket || !done) return MM_ERR_INVALID;
 	const mm_slot *sl = &c->ring[ticket % c->ring_slots];
 	if (sl->ticket != ticket) return fail(c, MM_ERR_NO_BATCH, "ticket %llu is not in the ring", (unsigned long long)ticket);
-	if (c->no_signal) *done = !sl->pending || cudaStreamQuery(c->stream) == cudaSuccess;
-	else *done = !sl->pending || *(volatile mm::u64 *)c->h_done >= sl->wait_ticket;
+	*done = !sl->pending || *(volatile mm::u64 *)c->h_done >= sl->wait_ticket ||
+	        (sl->wait_ticket > c->signalled_upto && cudaStreamQuery(c->stream) == cudaSuccess);
 	return MM_OK;
 }
 
@@ -870,7 +847,7 @@ static int pipelined_batch_host(mm_ctx *c, const uint8_t *hc, const int64_t *ho,
 		const uint32_t first = k * piece, m = std::min(piece, n - first);
 		MM_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_in[k % ahead], 0));
 		const Targets tg{sl->d_out_i, sl->d_out_t, sl->cap_i, sl->cap_t, sl->d_ranges_i + first, sl->d_ranges_t + first, sl->d_h_totals};
-		if ((rc = launch(c, c->d_in_chunks + (size_t)first * 4096, c->d_in_offs + (size_t)first * 3, nullptr, m, false, tg, carry, 0,
+		if ((rc = launch(c, c->d_in_chunks + (size_t)first * 4096, c->d_in_offs + (size_t)first * 3, nullptr, m, false, tg, carry,
 		                 &sl->last_launches)))
 			return rc;
 		carry = c->d_ticket + 2 + 2 * c->totals_slot;

@@ -49,11 +49,9 @@ struct mm_ctx {
 	mm_slot *cur = &ring[0];          // slot of the most recent batch: what finish / copy_out / draw_batch refer to
 	uint64_t next_ticket = 1;         // tickets start at 1
 	uint64_t last_signal_ticket = 0;  // completion signal of the most recent batch that launched kernels (counts on its own)
-	uint32_t sync_pieces = 1, sync_piece_min = 512;  // MM_SYNC_PIECES / MM_SYNC_PIECE_MIN: a synchronous batch is cut into that many overlapping pieces
-	bool no_signal = false;           // MM_NO_SIGNAL: batches do not signal, waits synchronise the stream
+	uint64_t signalled_upto = 0;      // newest signal some later launch carries (AnalyseParams::h_done)
 	mm::u64 *h_done = nullptr;        // pinned + mapped: ticket of the last batch whose kernels have completed
 	mm::u64 *d_h_done = nullptr;
-	uint32_t *d_done_count = nullptr; // expand CTAs that have finished the current launch (last one signals)
 	cudaStream_t s_draw = nullptr;    // consumers of finished ring slots run here, beside the mesher's stream
 	// analysis -> expansion hand-over (mesh_kernel.cuh): per-chunk descriptor slots and counts
 	// -- two of each: consecutive launch pairs alternate, so that the analysis of one batch can run

@@ -56,83 +56,68 @@ static int mesh_batch_t(const uint8_t *chunks, const int64_t *offs, uint32_t n, 
 	std::vector<uint32_t> desc_i((size_t)n * kDescStrideI, 0xDEADBEEFu), desc_t((size_t)n * kDescStrideT, 0xDEADBEEFu);
 	std::vector<uint32_t> cnt_i(n), cnt_t(n);
 	for (uint32_t c = 0; c < n; c++) {
-		const int b = (int)(c & 1u);  // the kernel alternates between its two buffers
 		const uint8_t *chunk = chunks + (size_t)c * 4096;
-		memcpy(smem_raw(s, b), chunk, 4096);  // the bulk async copy of the kernel
-		const uint8_t *raw = smem_raw(s, b);
-		// A: thread tid <-> columns tid, tid + 128; per warp the OR of the flags and the plants per range of 32 columns
-		uint32_t czp[128] = {0};
-		for (int w = 0; w < 4; w++) {
-			uint32_t amb = 0, n0 = 0, n1 = 0;
-			for (int lane = 0; lane < 32; lane++) {
-				const int tid = 32 * w + lane;
-				for (int j = 0; j < 2; j++) {
-					const int col = 128 * j + tid;
-					const Col own = load_col(raw + col * 16);
-					uint32_t orf;
-					const uint32_t bz = col_flags_any(flags, own, orf);
-					smem_Bzp(s, b)[((col >> 4) + 1) * kBzStride + (col & 15) + 1] = (uint16_t)bz;
-					if (orf & kFlagCrossed) czp[tid] |= col_crossed(flags, own) << (16 * j);
-					amb |= orf;
-				}
-				n0 += (uint32_t)popc32(czp[tid] & 0xffffu);
-				n1 += (uint32_t)popc32(czp[tid] >> 16);
-			}
-			s.ambw[b][w] = amb;
-			s.pcnt[b][w] = n0;
-			s.pcnt[b][4 + w] = n1;
+		memcpy(smem_raw(s), chunk, 4096);  // the bulk async copy of the kernel
+		const uint8_t *raw = smem_raw(s);
+		// A
+		uint32_t amb = 0;
+		uint32_t crossed_cols[kLanes * 4] = {0};
+		bool uniform = true;
+		for (int i = 1; i < 4096; i++) uniform = uniform && raw[i] == raw[0];
+		if (uniform && (flags[raw[0]] & (kFlagBlocky | kFlagCrossed)) == 0) {  // the kernel's all-air exit
+			cnt_i[c] = 0;
+			cnt_t[c] = 0;
+			continue;
 		}
 		if (HALO)
-			for (int tid = 0; tid < 96; tid++) halo_row(s, b, flags, load_col(halo + (size_t)c * 1536 + tid * 16), tid);
-		const uint32_t amb = s.ambw[b][0] | s.ambw[b][1] | s.ambw[b][2] | s.ambw[b][3];
+			for (int tid = 0; tid < 96; tid++) halo_row(s, flags, load_col(halo + (size_t)c * 1536 + tid * 16), tid);
+		for (int j = 0; j < 2; j++)
+			for (int tid = 0; tid < 128; tid++) {
+				const int col = 128 * j + tid;
+				uint32_t orf;
+				const uint32_t bz = col_flags(flags, load_col(raw + col * 16), orf);
+				smem_Bzp(s)[((col >> 4) + 1) * kBzStride + (col & 15) + 1] = (uint16_t)bz;
+				crossed_cols[tid] |= ((orf >> 1) & 1u) << j;
+				amb |= orf;
+			}
 		uint32_t nq = 0, npl = 0;
 		uint32_t *di = desc_i.data() + (size_t)c * kDescStrideI;
 		if (amb & kFlagBlocky) {
 			// B
-			for (int col = 0; col < 256; col++) col_starts<HALO>(s, b, tab, col >> 4, col & 15, amb);
+			for (int col = 0; col < 256; col++) col_starts<HALO>(s, tab, raw, col >> 4, col & 15, amb);
 			// C
-			for (int lane = 0; lane < kLanes; lane++) transpose_blocky(s, b, lane);
+			for (int lane = 0; lane < kLanes; lane++) transpose_blocky(s, lane);
 			if (HALO)
-				for (int job = 0; job < 4; job++) transpose_halo(s, b, job);
+				for (int job = 0; job < 4; job++) transpose_halo(s, job);
+			uint32_t run = 0;
 			for (int m = 0; m < kGroups; m++) s.gcnt[m] = transpose_group(s, m);
-			uint32_t pre[kGroups], run = 0;
 			for (int m = 0; m < kGroups; m++) {  // exclusive scan, quads (low half) and words (high half) at once
-				pre[m] = run;
-				run += s.gcnt[m];
+				const uint32_t v = s.gcnt[m];
+				s.gcnt[m] = run;
+				run += v;
 			}
 			nq = run & 0xffffu;
-			// D: warp w owns the groups m = w (mod 4), lists their non-empty words in its own list, then word by word
-			for (int w = 0; w < 4; w++) {
-				uint32_t nw = 0;
-				for (int lane = 0; lane < kGroups / 4; lane++) {
-					const int m = 4 * lane + w;
-					if (s.gcnt[m]) list_group_words(s, s.wl[w], m, pre[m] & 0xffffu, nw);
-					nw += s.gcnt[m] >> 16;
-				}
-				for (uint32_t i = 0; i < nw; i++) {
-					const uint32_t e = s.wl[w][i];
-					const uint32_t widx = e & 1023u;
-					emit_word_descs<HALO>(s, b, widx, reinterpret_cast<const uint32_t *>(s.S)[widx], di + (e >> 10));
-				}
+			const uint32_t nwords = run >> 16;
+			for (int m = 0; m < kGroups; m++) list_group_words(s, m, s.gcnt[m]);
+			// D
+			for (uint32_t i = 0; i < nwords; i++) {
+				const uint32_t e = smem_wl(s)[i];
+				const uint32_t widx = e & 1023u;
+				emit_word_descs<HALO>(s, widx, reinterpret_cast<const uint32_t *>(s.S)[widx], di + (e >> 10));
 			}
 		}
 		if (amb & kFlagCrossed) {
-			uint32_t base[8], tot = 0;
-			for (int r = 0; r < 8; r++) {
-				base[r] = tot;
-				tot += s.pcnt[b][r];
-			}
-			for (int w = 0; w < 4; w++)
-				for (int j = 0; j < 2; j++) {
-					uint32_t at = base[4 * j + w];
-					for (int lane = 0; lane < 32; lane++) {
-						const int tid = 32 * w + lane;
-						const uint32_t m16 = (czp[tid] >> (16 * j)) & 0xffffu;
-						if (m16) emit_column_plants(raw, 128 * j + tid, m16, desc_t.data() + (size_t)c * kDescStrideT + at);
-						at += (uint32_t)popc32(m16);
-					}
+			uint16_t *Cz = smem_Cz(s);
+			for (int j = 0; j < 2; j++)
+				for (int tid = 0; tid < 128; tid++) {
+					const int col = 128 * j + tid;
+					Cz[col] = (uint16_t)(((crossed_cols[tid] >> j) & 1u) ? col_crossed(flags, load_col(raw + col * 16)) : 0u);
 				}
-			npl = tot;
+			for (int lane = 0; lane < kLanes; lane++) {
+				const uint32_t mine = count_plants8(s, lane);
+				if (mine) emit_plant_descs(s, lane, desc_t.data() + (size_t)c * kDescStrideT + npl);
+				npl += mine;
+			}
 		}
 		cnt_i[c] = nq;
 		cnt_t[c] = npl * kPlantQuads;
