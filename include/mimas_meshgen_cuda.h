@@ -313,6 +313,11 @@ int mm_draw_batch(mm_ctx *ctx, const mm_camera *cam, mm_draw_out *out);
 /* the same over the batch of a ring ticket (waits for it), on the context's consumer stream: batches queued
  * behind it keep meshing while this one is drawn. */
 int mm_draw_ticket(mm_ctx *ctx, uint64_t ticket, const mm_camera *cam, mm_draw_out *out);
+/* In two halves, so that the host can queue more mesher batches while a frame is shaded: _async waits for the
+ * ticket and enqueues the frame on the consumer stream, mm_draw_collect waits for it and reports.  One frame in
+ * flight per context. */
+int mm_draw_ticket_async(mm_ctx *ctx, uint64_t ticket, const mm_camera *cam);
+int mm_draw_collect(mm_ctx *ctx, mm_draw_out *out);
 
 /* What GL does with the shaded vertices, headless: primitive assembly, clipping, back-face culling
  * (CullCounterClockwise), rasterisation, depth test IfLess and the fragment shader

@@ -24,7 +24,7 @@ SYMBOLS = (
     "mm_debug_trace", "mm_vertex_stage", "mm_cull_chunks", "mm_draw_batch", "mm_mesh_batch_halo_async",
     "mm_gather_halos", "mm_set_textures", "mm_raster_frame", "mm_ring_configure", "mm_mesh_batch_submit",
     "mm_mesh_batches_submit", "mm_batch_wait", "mm_batch_poll", "mm_copy_out_ticket", "mm_draw_ticket",
-    "mm_gen_mapgen_device",
+    "mm_gen_mapgen_device", "mm_draw_ticket_async", "mm_draw_collect",
 )
 
 
@@ -88,6 +88,8 @@ def lib() -> C.CDLL:
     l.mm_batch_poll.argtypes = [vp, u64, C.POINTER(C.c_int)]
     l.mm_copy_out_ticket.argtypes = [vp, u64, vp, vp, vp, vp]
     l.mm_draw_ticket.argtypes = [vp, u64, vp, vp]
+    l.mm_draw_ticket_async.argtypes = [vp, u64, vp]
+    l.mm_draw_collect.argtypes = [vp, vp]
     l.mm_gen_mapgen_device.argtypes = [vp, u64, vp, i64, i64, i64, u32, u32, u32, vp, vp, vp]
     l.mm_abi_version.argtypes = []
     for s in SYMBOLS:

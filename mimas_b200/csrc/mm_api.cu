@@ -345,7 +345,11 @@ int mm_ctx_create(int device, mm_ctx **out) {
 		MM_CUDA(c, cudaHostAlloc(&c->h_done, sizeof(mm::u64), cudaHostAllocMapped));
 		MM_CUDA(c, cudaHostGetDevicePointer((void **)&c->d_h_done, c->h_done, 0));
 		*c->h_done = 0;
-		MM_CUDA(c, cudaStreamCreateWithFlags(&c->s_draw, cudaStreamNonBlocking));
+		{  // consumers get the SMs first whenever the persistent mesher kernels hand some back
+			int lo = 0, hi = 0;
+			MM_CUDA(c, cudaDeviceGetStreamPriorityRange(&lo, &hi));
+			MM_CUDA(c, cudaStreamCreateWithPriority(&c->s_draw, cudaStreamNonBlocking, hi));
+		}
 		return MM_OK;
 	};
 	rc = body();

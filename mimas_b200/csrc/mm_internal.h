@@ -106,6 +106,10 @@ struct mm_ctx {
 	unsigned char *d_shaded = nullptr;
 	size_t shaded_bytes = 0;
 	cudaEvent_t ev2 = nullptr, ev3 = nullptr;
+	const mm_slot *draw_slot = nullptr;   // the frame in flight (mm_draw_ticket_async .. mm_draw_collect), or NULL
+	cudaStream_t draw_stream = nullptr;
+	mm_camera draw_cam;
+	const uint32_t *draw_list = nullptr;
 	// software rasteriser (mm_raster.cu): texture array, 64-bit key frame buffer, queue of large triangles
 	float *d_tex = nullptr;
 	uint32_t tex_layers = 0, tex_size = 0;

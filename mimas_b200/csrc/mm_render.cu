@@ -375,11 +375,15 @@ int mm_cull_chunks(mm_ctx *c, const int64_t *offs, uint32_t n, const mm_camera *
 	return rc;
 }
 
-// One frame over the batch a ring slot holds, on `stream`.
-static int draw_slot(mm_ctx *c, const mm_slot *sl, cudaStream_t stream, const mm_camera *cam, mm_draw_out *out) {
-	memset(out, 0, sizeof(*out));
-	out->n_chunks = sl->last_n;
-	if (sl->last_n == 0) return MM_OK;
+// One frame over the batch a ring slot holds, on `stream`: enqueue (cull + vertex shader), then collect (wait, grow the
+// shaded buffer and run again if it was too small, read the totals).  One frame in flight per context.
+static int draw_enqueue(mm_ctx *c, const mm_slot *sl, cudaStream_t stream, const mm_camera *cam) {
+	c->draw_slot = nullptr;
+	if (sl->last_n == 0) {
+		c->draw_slot = sl;
+		c->draw_stream = stream;
+		return MM_OK;
+	}
 	int rc;
 	if ((rc = ensure_draw_totals(c))) return rc;
 	CullParams p;
@@ -392,21 +396,35 @@ static int draw_slot(mm_ctx *c, const mm_slot *sl, cudaStream_t stream, const mm
 	p.ranges_i = sl->d_ranges_i;
 	p.ranges_t = sl->d_ranges_t;
 	p.totals = c->d_h_draw_totals;
+	DrawParams d;
+	d.draw = p.draw; d.first_i = p.first_i; d.first_t = p.first_t; d.totals = c->d_h_draw_totals;
+	d.ranges_i = sl->d_ranges_i; d.ranges_t = sl->d_ranges_t;
+	d.vi = (const mm_vertex *)sl->d_out_i; d.vt = (const mm_vertex *)sl->d_out_t;
+	d.out = (mm_shaded_vertex *)c->d_shaded;
+	d.cap = c->shaded_bytes / sizeof(mm_shaded_vertex);
+	MM_CUDA(c, cudaEventRecord(c->ev2, stream));
+	if ((rc = enqueue_cull(c, p, stream))) return rc;
+	draw_kernel<<<c->sm_count * 8, kShadeThreads, 0, stream>>>(d, mt);
+	MM_CUDA(c, cudaGetLastError());
+	MM_CUDA(c, cudaEventRecord(c->ev3, stream));
+	c->draw_slot = sl;
+	c->draw_stream = stream;
+	c->draw_cam = *cam;
+	c->draw_list = p.draw;
+	return MM_OK;
+}
+
+static int draw_collect(mm_ctx *c, mm_draw_out *out) {
+	const mm_slot *sl = c->draw_slot;
+	if (!sl) return fail(c, MM_ERR_NO_BATCH, "no frame in flight");
+	memset(out, 0, sizeof(*out));
+	out->n_chunks = sl->last_n;
+	c->draw_slot = nullptr;
+	if (sl->last_n == 0) return MM_OK;
 	for (int attempt = 0;; attempt++) {
-		DrawParams d;
-		d.draw = p.draw; d.first_i = p.first_i; d.first_t = p.first_t; d.totals = c->d_h_draw_totals;
-		d.ranges_i = sl->d_ranges_i; d.ranges_t = sl->d_ranges_t;
-		d.vi = (const mm_vertex *)sl->d_out_i; d.vt = (const mm_vertex *)sl->d_out_t;
-		d.out = (mm_shaded_vertex *)c->d_shaded;
-		d.cap = c->shaded_bytes / sizeof(mm_shaded_vertex);
-		MM_CUDA(c, cudaEventRecord(c->ev2, stream));
-		if ((rc = enqueue_cull(c, p, stream))) return rc;
-		draw_kernel<<<c->sm_count * 8, kShadeThreads, 0, stream>>>(d, mt);
-		MM_CUDA(c, cudaGetLastError());
-		MM_CUDA(c, cudaEventRecord(c->ev3, stream));
-		MM_CUDA(c, cudaStreamSynchronize(stream));
+		MM_CUDA(c, cudaStreamSynchronize(c->draw_stream));
 		const unsigned long long need = c->h_draw_totals[1] + c->h_draw_totals[2];
-		if (need <= d.cap) break;
+		if (need <= c->shaded_bytes / sizeof(mm_shaded_vertex)) break;
 		if (attempt >= 1) return fail(c, MM_ERR_CUDA, "shaded vertex buffer still too small after growth");
 		cudaFree(c->d_shaded);
 		c->d_shaded = nullptr;
@@ -414,10 +432,14 @@ static int draw_slot(mm_ctx *c, const mm_slot *sl, cudaStream_t stream, const mm
 		const size_t bytes = align256((size_t)(need + need / 8) * sizeof(mm_shaded_vertex));
 		MM_CUDA(c, cudaMalloc(&c->d_shaded, bytes));
 		c->shaded_bytes = bytes;
+		const mm_camera cam = c->draw_cam;
+		int rc;
+		if ((rc = draw_enqueue(c, sl, c->draw_stream, &cam))) return rc;
+		c->draw_slot = nullptr;
 	}
 	MM_CUDA(c, cudaEventElapsedTime(&out->kernel_ms, c->ev2, c->ev3));
 	out->d_shaded = (const mm_shaded_vertex *)c->d_shaded;
-	out->d_draw_list = p.draw;
+	out->d_draw_list = c->draw_list;
 	out->n_drawn = (uint32_t)c->h_draw_totals[0];
 	out->n_shaded_i = c->h_draw_totals[1];
 	out->n_shaded_t = c->h_draw_totals[2];
@@ -428,15 +450,30 @@ int mm_draw_batch(mm_ctx *c, const mm_camera *cam, mm_draw_out *out) {
 	if (!c || !cam || !out) return MM_ERR_INVALID;
 	if (!c->cur->finished) return fail(c, MM_ERR_NO_BATCH, "no finished device batch to draw");
 	MM_CUDA(c, cudaSetDevice(c->device));
-	return draw_slot(c, c->cur, c->stream, cam, out);
+	int rc;
+	if ((rc = draw_enqueue(c, c->cur, c->stream, cam))) return rc;
+	return draw_collect(c, out);
+}
+
+int mm_draw_ticket_async(mm_ctx *c, uint64_t ticket, const mm_camera *cam) {
+	if (!c || !cam || !ticket) return MM_ERR_INVALID;
+	MM_CUDA(c, cudaSetDevice(c->device));
+	if (c->draw_slot) return fail(c, MM_ERR_INVALID, "a frame is in flight: collect it first (mm_draw_collect)");
+	int rc;
+	if ((rc = mm_batch_wait(c, ticket, nullptr))) return rc;  // polls the batch's completion word: no stream synchronisation
+	return draw_enqueue(c, &c->ring[ticket % c->ring_slots], c->s_draw, cam);
+}
+
+int mm_draw_collect(mm_ctx *c, mm_draw_out *out) {
+	if (!c || !out) return MM_ERR_INVALID;
+	MM_CUDA(c, cudaSetDevice(c->device));
+	return draw_collect(c, out);
 }
 
 int mm_draw_ticket(mm_ctx *c, uint64_t ticket, const mm_camera *cam, mm_draw_out *out) {
-	if (!c || !cam || !out || !ticket) return MM_ERR_INVALID;
-	MM_CUDA(c, cudaSetDevice(c->device));
-	int rc;
-	if ((rc = mm_batch_wait(c, ticket, nullptr))) return rc;  // polls the batch's completion word: no stream synchronisation
-	return draw_slot(c, &c->ring[ticket % c->ring_slots], c->s_draw, cam, out);
+	if (!out) return MM_ERR_INVALID;
+	const int rc = mm_draw_ticket_async(c, ticket, cam);
+	return rc ? rc : mm_draw_collect(c, out);
 }
 
 }  // extern "C"

@@ -383,8 +383,18 @@ class Mesher:
         """One frame over the batch of `ticket` on the consumer stream (later batches keep meshing)."""
         from .render import DrawOut
         out = DrawOut()
-        cc = cam.to_c()
+        cc = cam.to_c() if hasattr(cam, "to_c") else cam   # a Camera, or the mm_camera it was turned into
         self._ck(self._lib.mm_draw_ticket(self._ctx, ticket, C.byref(cc), C.byref(out)))
+        return out
+
+    def draw_ticket_async(self, ticket: int, cam):
+        cc = cam.to_c() if hasattr(cam, "to_c") else cam   # a Camera, or the mm_camera it was turned into
+        self._ck(self._lib.mm_draw_ticket_async(self._ctx, ticket, C.byref(cc)))
+
+    def draw_collect(self):
+        from .render import DrawOut
+        out = DrawOut()
+        self._ck(self._lib.mm_draw_collect(self._ctx, C.byref(out)))
         return out
 
     def batch_finish(self) -> _BatchOut:
@@ -451,19 +461,19 @@ class Mesher:
         offs = np.ascontiguousarray(offs, dtype=np.int64).reshape(-1, 3)
         draw = np.zeros(max(len(offs), 1), dtype=np.uint32)
         n = C.c_uint32()
-        cc = cam.to_c()
+        cc = cam.to_c() if hasattr(cam, "to_c") else cam   # a Camera, or the mm_camera it was turned into
         self._ck(self._lib.mm_cull_chunks(self._ctx, offs.ctypes.data, len(offs), C.byref(cc), draw.ctypes.data, C.byref(n)))
         return draw[:n.value].copy()
 
     def vertex_stage(self, d_in: int, n: int, cam, d_out: int):
-        cc = cam.to_c()
+        cc = cam.to_c() if hasattr(cam, "to_c") else cam   # a Camera, or the mm_camera it was turned into
         self._ck(self._lib.mm_vertex_stage(self._ctx, C.c_void_p(d_in), C.c_uint64(n), C.byref(cc), C.c_void_p(d_out)))
 
     def draw_batch(self, cam):
         """One frame over the last finished device batch: returns render.DrawOut (device pointers)."""
         from .render import DrawOut
         out = DrawOut()
-        cc = cam.to_c()
+        cc = cam.to_c() if hasattr(cam, "to_c") else cam   # a Camera, or the mm_camera it was turned into
         self._ck(self._lib.mm_draw_batch(self._ctx, C.byref(cc), C.byref(out)))
         return out
 

@@ -109,6 +109,8 @@ class Camera:
         return np.ascontiguousarray(m.T)
 
     def to_c(self) -> CCamera:
+        """mm_camera of this view.  Pass the result itself to the draw calls of a hot loop: building the two
+        matrices in numpy costs far more than a frame's enqueue."""
         c = CCamera()
         c.vmatrix[:] = [float(v) for v in self.get_matrix().reshape(-1)]
         c.pmatrix[:] = [float(v) for v in self.get_perspective().reshape(-1)]

@@ -19,3 +19,9 @@ except Exception as e:
     print("  $w: no line:", e)
 P
 done
+timeout 600 python bench.py --workload terrain --consume > gpurun_out/${tag}_bench_terrain_consumed.json 2> gpurun_out/${tag}_bench_terrain_consumed.err; echo "consume exit $?"
+python -c "
+import json
+d=json.loads(open('gpurun_out/${tag}_bench_terrain_consumed.json').read().strip().splitlines()[-1])
+print('  consumed: %.4f ms/step %.0f chunks/s' % (d['ms_per_step'], d['value']), d.get('consumed'))"
+timeout 600 python bench.py --impl reference > gpurun_out/${tag}_bench_reference.json 2>&1; cat gpurun_out/${tag}_bench_reference.json | cut -c1-300
