@@ -14,6 +14,8 @@ Workloads (BASELINE.json `configs`, one JSON line each, same schema):
     edits              configs[3]: remesh after single-block edits (each edit remeshes exactly its chunk)
     million            configs[4]: 1,048,576 mapgen chunks (128x128x64 region) per step; under torchrun the region is
                        cut into N contiguous shards (STRONG scaling, no collective)
+    mapgen             like terrain, but the chunks come from the device restatement of mimas-server's mapgen phase one
+                       (mm_gen_mapgen_device; parity of that generator to the reference is unpinned) instead of the look-alike
 A step = one pass of the mesher over the workload's batch, inputs resident in HBM; `e2e` = the same through the
 host API (host chunks in, H2D, kernels, D2H, host vertex vectors out).  Every workload is first compared with
 the CPU oracle (parity gate) -- no number is printed for a mesh that differs.  torch.distributed carries only
@@ -41,7 +43,7 @@ N_CHUNKS = REGION[0] * REGION[1] * REGION[2]
 ROTATE = 12                    # distinct input batches cycled through: 12 x 16 MiB > 126 MB of L2
 RING = int(os.environ.get("MM_BENCH_RING", "3"))  # output slots of the streamed workload: three batches stay retrievable
 L2_BYTES = 126e6
-WORKLOADS = ["terrain", "single", "checkerboard16384", "radius8", "radius16", "radius32", "edits", "million", "checkerboard"]
+WORKLOADS = ["terrain", "single", "checkerboard16384", "radius8", "radius16", "radius32", "edits", "million", "checkerboard", "mapgen"]
 MILLION = (128, 128, 64)       # configs[4]: chunk region centred on the origin
 
 
@@ -186,6 +188,11 @@ def host_sample(workload, rank=0, world=1):
     import mimas_b200
     if workload == "terrain":
         return mimas_b200.gen_terrain_host(SEED, region_origin(rank, 0), REGION) + ("the whole 4096-chunk batch",)
+    if workload == "mapgen":   # the restated mapgen on the host (oracle side: CPU arms only)
+        from mimas_b200 import mapgen as pm
+        from oracle import mapgen as om
+        c, o, _ = om.gen_region(SEED, region_origin(rank, 0), REGION, pm.to_c(pm.default_mapgen_params()))
+        return c, o, "the whole 4096-chunk batch"
     if workload == "single":
         a = mimas_b200.gen_terrain_host(SEED, (3, 2, 1), (1, 1, 1))
         b = mimas_b200.gen_terrain_host(SEED, (3, 2, 0), (1, 1, 1))
@@ -221,6 +228,8 @@ def apply_edits(chunks, offs, k=256, seed=44):
 def workload_config(workload, n, world=1):
     base = {"terrain": f"batch of {n} synthetic mapgen terrain chunks (32x32x4 region, seed {SEED}), "
                        "no halo (reference semantics), default game block table",
+            "mapgen": f"batch of {n} chunks of the restated mimas-server mapgen phase one (32x32x4 region, seed {SEED}; "
+                      "generated on the device, parity of the generator unpinned), no halo, default game block table",
             "single": "single 16^3 chunk per call: synthetic mapgen chunk at offs (48,32,16) and (48,32,0), alternating",
             "checkerboard16384": "batch of 16384 worst-case solid/air checkerboard chunks (12288 quads each), one call",
             "checkerboard": f"batch of {n} worst-case solid/air checkerboard chunks (12288 quads each)",
@@ -230,7 +239,9 @@ def workload_config(workload, n, world=1):
     if workload.startswith("radius"):
         r = int(workload[6:])
         base[workload] = f"view radius {r} (z radius 2): full mesh of {n} synthetic mapgen chunks in one call"
-    l2 = {"terrain": f"{ROTATE} distinct input batches rotated ({ROTATE * n * 4096 / 1e6:.0f} MB > L2); "
+    l2 = {"mapgen": f"{ROTATE} distinct input batches rotated ({ROTATE * n * 4096 / 1e6:.0f} MB > L2); "
+                    f"each step also writes a fresh >126 MB vertex stream into a ring of {RING} arenas",
+          "terrain": f"{ROTATE} distinct input batches rotated ({ROTATE * n * 4096 / 1e6:.0f} MB > L2); "
                      f"each step also writes a fresh >126 MB vertex stream into a ring of {RING} arenas",
           "single": "latency workload: nothing to flush (one 4 KiB chunk per call)",
           "edits": "latency workload: L2 flushed (256 MB written) between timed steps",
@@ -321,7 +332,7 @@ def main():
                     help="terrain: every streamed batch is handed to the headless draw (cull + vertex shader) while the next ones mesh")
     args = ap.parse_args()
     wl = args.workload
-    defaults = {"terrain": (300, 20), "single": (400, 20), "checkerboard16384": (5, 3), "checkerboard": (40, 5),
+    defaults = {"mapgen": (300, 20), "terrain": (300, 20), "single": (400, 20), "checkerboard16384": (5, 3), "checkerboard": (40, 5),
                 "radius8": (40, 5), "radius16": (40, 5), "radius32": (30, 5), "edits": (40, 5), "million": (5, 3)}
     if wl == "terrain" and args.consume:
         defaults["terrain"] = (60, 6)
@@ -363,11 +374,11 @@ def main():
     mesher.set_stream(stream.cuda_stream)
     sm_count, ctas_per_sm, threads = mesher.device_info()
     cache = oracle_cache()
-    streamed = wl in ("terrain", "checkerboard")           # batches queued back to back through the ring
+    streamed = wl in ("terrain", "checkerboard", "mapgen")   # batches queued back to back through the ring
     strong = wl == "million"
 
     # ---- inputs, resident in HBM ---------------------------------------------------------------------------
-    if wl == "terrain":
+    if wl in ("terrain", "mapgen"):
         n, rot = N_CHUNKS, ROTATE
         boxes = [(region_origin(rank, r), REGION) for r in range(rot)]
     elif wl == "checkerboard":
@@ -386,7 +397,9 @@ def main():
     d_chunks = [torch.empty(n * 4096, dtype=torch.uint8, device="cuda") for _ in range(rot)]
     d_offs = [torch.empty(n * 3, dtype=torch.int64, device="cuda") for _ in range(rot)]
     for r in range(rot):
-        if boxes is not None:
+        if wl == "mapgen":
+            mesher.gen_mapgen_device(SEED, boxes[r][0], boxes[r][1], d_chunks[r].data_ptr(), d_offs[r].data_ptr())
+        elif boxes is not None:
             mesher.gen_terrain_device(SEED, boxes[r][0], boxes[r][1], d_chunks[r].data_ptr(), d_offs[r].data_ptr())
         else:
             c, o = checkerboard(n, parity0=r)
@@ -416,7 +429,7 @@ def main():
         verts.append(out.n_intransparent + out.n_transparent)
         iso_ms.append(out.kernel_ms)  # one batch alone on the GPU, events around its kernels
         launches_per_step = out.launches
-        if args.no_verify or not (r == 0 or (wl == "terrain" and rank == 0 and r < 3) or wl == "single"):
+        if args.no_verify or not (r == 0 or (wl in ("terrain", "mapgen") and rank == 0 and r < 3) or wl == "single"):
             continue
         if n <= 6000:
             ok = full_compare(mesher, out, d_chunks[r].cpu().numpy().reshape(n, 4096), d_offs[r].cpu().numpy().reshape(n, 3), cache)
@@ -574,7 +587,7 @@ def main():
 
     if rank == 0:
         peak, peak_src = peaks()
-        traffic, ncu_gbs = ncu_traffic() if wl == "terrain" else (None, None)
+        traffic, ncu_gbs = ncu_traffic() if wl == "terrain" and not args.consume else (None, None)
         if traffic:   # ncu-counted steady-state DRAM bytes per step over the step time measured here, un-profiled
             ncu_gbs = traffic / (ms_per_step * 1e-3) / 1e9
         latency = wl in ("single", "edits")

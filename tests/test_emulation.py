@@ -182,3 +182,15 @@ def test_emulated_halo_shared_textures(emul):
     i, t, _, _ = emul(chunks, offs, kernel_table(rows, fb), halo=halo)
     assert first_diff(i, want["intransparent"].tobytes()) is None
     assert first_diff(t, want["transparent"].tobytes()) is None
+
+
+def test_emulated_kernel_on_fuzz_cases_with_random_tables(emul):
+    """The per-lane kernel logic on the differential fuzz's cases (tests/fuzz_util.py): random tables in which
+    different block ids share textures, fallback ids, crossed ids, origins up to 2^62."""
+    from tests import fuzz_util
+    for seed in range(1000, 1096):
+        rows, fb, chunk, offs = fuzz_util.make_case(seed)
+        wi, wt = oracle.mesh_for_chunk(offs, chunk, oracle.cache_from_entries(rows, len(rows), fb))
+        i, t, _, _ = emul(chunk, offs, kernel_table(rows, fb))
+        assert first_diff(i, wi.tobytes()) is None, f"seed {seed}"
+        assert first_diff(t, wt.tobytes()) is None, f"seed {seed}"

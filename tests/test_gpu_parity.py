@@ -117,6 +117,26 @@ def test_shared_textures_merge_across_block_ids(ocache):
         assert_batch_equal(m.mesh_batch(offs, chunks), oracle.mesh_batch(chunks, offs, oc, threads=4))
 
 
+def test_fuzz_cases_with_random_tables_through_the_c_abi():
+    """The differential fuzz's generator (tests/fuzz_util.py) against the CUDA path: 160 random tables (different ids
+    sharing textures, fallback and crossed ids) x chunks x origins up to 2^62, eight chunks per table in one batch."""
+    import mimas_b200
+    from tests import fuzz_util
+    with mimas_b200.Mesher(0) as m:
+        for t in range(160):
+            rng = np.random.RandomState(5000 + t)
+            rows, fb = fuzz_util.random_table(rng)
+            chunks = np.stack([fuzz_util.random_chunk(rng, len(rows)) for _ in range(8)])
+            offs = np.array([[fuzz_util.OFFSETS[i] for i in rng.randint(0, len(fuzz_util.OFFSETS), size=3)] for _ in range(8)],
+                            dtype=np.int64)
+            m.set_cache(mimas_b200.TextureIdCache.from_table_rows(rows, fb))
+            want = oracle.mesh_batch(chunks, offs, oracle.cache_from_entries(rows, len(rows), fb), threads=4)
+            assert_batch_equal(m.mesh_batch(offs, chunks), want)
+            one = m.mesh_for_chunk(offs[3], chunks[3])          # and the fused single-chunk launch
+            a, n = int(want["first_i"][3]), int(want["count_i"][3])
+            assert one.intransparent.tobytes() == want["intransparent"][a:a + n].tobytes(), f"table {t}"
+
+
 def test_repeated_launches_with_changing_batch_sizes(mesher, ocache):
     """Exercises arena growth + re-run and the alternating hand-over buffers across launches of changing size."""
     import mimas_b200
