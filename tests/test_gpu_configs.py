@@ -220,3 +220,34 @@ def test_many_batches_by_one_call_and_draw_of_an_older_ticket(ocache):
         for _, _, dc, do in all_sets:
             m.dev_free(dc)
             m.dev_free(do)
+
+
+def test_ring_poll_empty_batches_and_halo_tickets(ocache):
+    """mm_batch_poll, zero-chunk batches between real ones, and a halo batch through the ring."""
+    import time
+    import mimas_b200
+    from tests.util import halos_for_box
+    with mimas_b200.Mesher(0, product_cache(G)) as m:
+        dims = (6, 5, 4)
+        n = dims[0] * dims[1] * dims[2]
+        chunks, offs = mimas_b200.gen_terrain_host(78, (-3, -2, -2), dims)
+        halo = halos_for_box(chunks, dims, outside=0)
+        dc, do, dh = m.dev_alloc(n * 4096), m.dev_alloc(n * 24), m.dev_alloc(n * 1536)
+        m.upload(dc, chunks); m.upload(do, offs); m.upload(dh, halo)
+        m.ring_configure(4)
+        t_plain = m.submit(dc, do, n)
+        t_empty = m.submit(dc, do, 0)
+        t_halo = m.submit(dc, do, n, d_halo=dh)
+        t_last = m.submit(dc, do, n)
+        deadline = time.time() + 30
+        while not m.batch_poll(t_last):                      # the newest batch: polled through the stream
+            assert time.time() < deadline
+        assert m.batch_poll(t_plain) and m.batch_poll(t_empty) and m.batch_poll(t_halo)
+        want = oracle.mesh_batch(chunks, offs, ocache, threads=8)
+        assert_batch_equal(m.copy_out_ticket(t_plain), want)
+        assert_batch_equal(m.copy_out_ticket(t_last), want)
+        assert_batch_equal(m.copy_out_ticket(t_halo), oracle.mesh_batch(chunks, offs, ocache, threads=8, halo=halo))
+        e = m.batch_wait(t_empty)
+        assert e.n_chunks == 0 and e.n_intransparent == 0 and e.n_transparent == 0
+        for p in (dc, do, dh):
+            m.dev_free(p)
