@@ -342,6 +342,9 @@ int mm_ctx_create(int device, mm_ctx **out) {
 			const int rs = ensure_slot_totals(c, &c->ring[0]);
 			if (rs) return rs;
 		}
+		// the host paths (mapped / pipelined) read their totals from words of their own: a ring batch still in flight keeps its slot's
+		MM_CUDA(c, cudaHostAlloc(&c->h_host_totals, sizeof(mm::u64) * 2, cudaHostAllocMapped));
+		MM_CUDA(c, cudaHostGetDevicePointer((void **)&c->d_h_host_totals, c->h_host_totals, 0));
 		MM_CUDA(c, cudaHostAlloc(&c->h_done, sizeof(mm::u64), cudaHostAllocMapped));
 		MM_CUDA(c, cudaHostGetDevicePointer((void **)&c->d_h_done, c->h_done, 0));
 		*c->h_done = 0;
@@ -370,6 +373,7 @@ int mm_ctx_destroy(mm_ctx *c) {
 	for (uint32_t k = 0; k < kMaxRingSlots; k++) free_slot(&c->ring[k]);
 	cudaFree(c->d_table); cudaFree(c->d_cnt); cudaFree(c->d_desc_i); cudaFree(c->d_desc_t); cudaFree(c->d_flags); cudaFree(c->d_ticket);
 	if (c->h_done) cudaFreeHost(c->h_done);
+	if (c->h_host_totals) cudaFreeHost(c->h_host_totals);
 	if (c->s_draw) cudaStreamDestroy(c->s_draw);
 	cudaFree(c->d_in_chunks); cudaFree(c->d_in_offs); cudaFree(c->d_in_halo); cudaFree(c->d_trace);
 	if (c->h_in) cudaFreeHost(c->h_in);
@@ -769,14 +773,12 @@ static int small_batch_host(mm_ctx *c, const uint8_t *chunks, const int64_t *off
 			d_chunks = c->d_small + L.chunks;
 			d_offs = (const long long *)(c->d_small + L.offs);
 		}
-		mm_slot *sl = c->cur;
+		// nothing of this call touches a ring slot: vertices, range records and totals all go to mapped host memory
 		Targets tg{c->d_small + L.out_i, c->d_small + L.out_t, c->mapped_qi, c->mapped_qt,
-		           (mm::Range *)(c->d_small + L.ranges_i), (mm::Range *)(c->d_small + L.ranges_t), sl->d_h_totals};
-		sl->pending = sl->finished = false;  // the device arenas hold no batch of this call
-		sl->ticket = 0;
+		           (mm::Range *)(c->d_small + L.ranges_i), (mm::Range *)(c->d_small + L.ranges_t), c->d_h_host_totals};
 		if ((rc = launch(c, d_chunks, d_offs, nullptr, n, false, tg))) return rc;
 		MM_CUDA(c, cudaStreamSynchronize(c->stream));
-		const uint64_t ti = sl->h_totals[0], tt = sl->h_totals[1];
+		const uint64_t ti = c->h_host_totals[0], tt = c->h_host_totals[1];
 		if (ti > c->mapped_qi || tt > c->mapped_qt) {  // nothing was written: grow the mapped arenas and run again
 			if (attempt >= 1) return MM_OK;
 			const MappedLayout G(c->mapped_chunks, std::max(c->mapped_qi, ti + ti / 8), std::max(c->mapped_qt, tt + tt / 8));
@@ -850,14 +852,14 @@ static int pipelined_batch_host(mm_ctx *c, const uint8_t *hc, const int64_t *ho,
 	for (uint32_t k = 0; k < pieces && fits; k++) {
 		const uint32_t first = k * piece, m = std::min(piece, n - first);
 		MM_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_in[k % ahead], 0));
-		const Targets tg{sl->d_out_i, sl->d_out_t, sl->cap_i, sl->cap_t, sl->d_ranges_i + first, sl->d_ranges_t + first, sl->d_h_totals};
+		const Targets tg{sl->d_out_i, sl->d_out_t, sl->cap_i, sl->cap_t, sl->d_ranges_i + first, sl->d_ranges_t + first, c->d_h_host_totals};
 		if ((rc = launch(c, c->d_in_chunks + (size_t)first * 4096, c->d_in_offs + (size_t)first * 3, nullptr, m, false, tg, carry,
 		                 &sl->last_launches)))
 			return rc;
 		carry = c->d_ticket + 2 + 2 * c->totals_slot;
 		MM_CUDA(c, cudaStreamSynchronize(c->stream));
 		if (k + ahead < pieces && (rc = send(k + ahead))) return rc;  // its event is free again
-		const uint64_t ti = sl->h_totals[0], tt = sl->h_totals[1];
+		const uint64_t ti = c->h_host_totals[0], tt = c->h_host_totals[1];
 		if (ti > room_i || tt > room_t) {
 			fits = false;
 			break;

@@ -251,3 +251,28 @@ def test_ring_poll_empty_batches_and_halo_tickets(ocache):
         assert e.n_chunks == 0 and e.n_intransparent == 0 and e.n_transparent == 0
         for p in (dc, do, dh):
             m.dev_free(p)
+
+
+def test_single_chunk_host_calls_between_ring_batches_leave_them_alone(ocache):
+    """The reference's call pattern (one chunk, host in / host out: the mapped path) while ring batches are in flight:
+    neither disturbs the other."""
+    import mimas_b200
+    with mimas_b200.Mesher(0, product_cache(G)) as m:
+        chunks, offs = mimas_b200.gen_terrain_host(78, (-4, -4, -2), (8, 8, 4))
+        n = len(chunks)
+        want = oracle.mesh_batch(chunks, offs, ocache, threads=8)
+        dc, do = m.dev_alloc(n * 4096), m.dev_alloc(n * 24)
+        m.upload(dc, chunks); m.upload(do, offs)
+        m.ring_configure(2)
+        t1 = m.submit(dc, do, n)
+        t2 = m.submit(dc, do, n)
+        for name in ("layered_terrain", "one_sapling", "checkerboard_odd", "all_air"):
+            c = G.cases[name]
+            got = m.mesh_for_chunk(c["offs"], c["chunk"])
+            assert first_diff(got.intransparent.tobytes(), c["intr"]) is None
+            assert first_diff(got.transparent.tobytes(), c["trans"]) is None
+        small = m.mesh_batch(offs[:40], chunks[:40])                    # 40 chunks: still the mapped path
+        assert_batch_equal(small, oracle.mesh_batch(chunks[:40], offs[:40], ocache, threads=4))
+        assert_batch_equal(m.copy_out_ticket(t1), want)
+        assert_batch_equal(m.copy_out_ticket(t2), want)
+        m.dev_free(dc); m.dev_free(do)
