@@ -72,6 +72,10 @@ struct ExpandParams {
 	u64 *totals;                  // [0] quads in out_i, [1] quad slots in out_t after this launch
 	u64 *host_totals;             // the same two words in mapped pinned host memory
 	u64 *trace;                   // NULL, or 4 words of this launch: first CTA start, first CTA past the wait, -, last CTA end (ns)
+	// FUSED single-chunk launch over mapped host memory only: a mapped host word that receives flag_value once the
+	// vertices have landed in host memory, so that the caller polls a cache line instead of synchronising the stream
+	u64 *h_flag;
+	u64 flag_value;
 };
 
 struct AnalyseParams {
@@ -374,6 +378,13 @@ __global__ void __launch_bounds__(kThreads, kAnalyseCtasPerSm) analyse_kernel(co
 			if (lane == 0) store_tile(g, sp, tn * kQuadBytes);
 		}
 		if (lane == 0) bulk_wait_all();
+		if (x.h_flag != nullptr) {
+			__syncthreads();
+			if (tid == 0) {
+				__threadfence_system();
+				*reinterpret_cast<volatile u64 *>(x.h_flag) = x.flag_value;
+			}
+		}
 	}
 }
 

@@ -11,6 +11,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <chrono>
 #include <new>
 #include <thread>
 #include <vector>
@@ -198,6 +199,9 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, co
 			e.totals = c->d_ticket + 2 + 2 * c->totals_slot;
 			e.host_totals = tg.host_totals;
 			e.trace = nullptr;
+			e.h_flag = c->flag_wanted ? c->d_h_flag : nullptr;  // mapped path: the caller polls instead of synchronising
+			e.flag_value = c->flag_wanted;
+			c->flag_armed = c->flag_wanted;
 			cudaLaunchConfig_t cfg = {};
 			cfg.gridDim = dim3(1);
 			cfg.blockDim = dim3(mm::kThreads);
@@ -241,6 +245,8 @@ int launch(mm_ctx *c, const unsigned char *d_chunks, const long long *d_offs, co
 		e.totals = c->d_ticket + 2 + 2 * c->totals_slot;
 		e.host_totals = tg.host_totals;
 		e.trace = tr ? tr + 4 : nullptr;
+		e.h_flag = nullptr;
+		e.flag_value = 0;
 		// programmatic dependent launch (see the kernels): analysis of batch k+1 beside expansion of batch k
 		cudaLaunchConfig_t cfg = {};
 		cfg.gridDim = dim3((unsigned)c->expand_grid);
@@ -345,6 +351,9 @@ int mm_ctx_create(int device, mm_ctx **out) {
 		// the host paths (mapped / pipelined) read their totals from words of their own: a ring batch still in flight keeps its slot's
 		MM_CUDA(c, cudaHostAlloc(&c->h_host_totals, sizeof(mm::u64) * 2, cudaHostAllocMapped));
 		MM_CUDA(c, cudaHostGetDevicePointer((void **)&c->d_h_host_totals, c->h_host_totals, 0));
+		MM_CUDA(c, cudaHostAlloc(&c->h_flag, sizeof(mm::u64), cudaHostAllocMapped));
+		MM_CUDA(c, cudaHostGetDevicePointer((void **)&c->d_h_flag, c->h_flag, 0));
+		*c->h_flag = 0;
 		MM_CUDA(c, cudaHostAlloc(&c->h_done, sizeof(mm::u64), cudaHostAllocMapped));
 		MM_CUDA(c, cudaHostGetDevicePointer((void **)&c->d_h_done, c->h_done, 0));
 		*c->h_done = 0;
@@ -374,6 +383,7 @@ int mm_ctx_destroy(mm_ctx *c) {
 	cudaFree(c->d_table); cudaFree(c->d_cnt); cudaFree(c->d_desc_i); cudaFree(c->d_desc_t); cudaFree(c->d_flags); cudaFree(c->d_ticket);
 	if (c->h_done) cudaFreeHost(c->h_done);
 	if (c->h_host_totals) cudaFreeHost(c->h_host_totals);
+	if (c->h_flag) cudaFreeHost(c->h_flag);
 	if (c->s_draw) cudaStreamDestroy(c->s_draw);
 	cudaFree(c->d_in_chunks); cudaFree(c->d_in_offs); cudaFree(c->d_in_halo); cudaFree(c->d_trace);
 	if (c->h_in) cudaFreeHost(c->h_in);
@@ -776,8 +786,25 @@ static int small_batch_host(mm_ctx *c, const uint8_t *chunks, const int64_t *off
 		// nothing of this call touches a ring slot: vertices, range records and totals all go to mapped host memory
 		Targets tg{c->d_small + L.out_i, c->d_small + L.out_t, c->mapped_qi, c->mapped_qt,
 		           (mm::Range *)(c->d_small + L.ranges_i), (mm::Range *)(c->d_small + L.ranges_t), c->d_h_host_totals};
-		if ((rc = launch(c, d_chunks, d_offs, nullptr, n, false, tg))) return rc;
-		MM_CUDA(c, cudaStreamSynchronize(c->stream));
+		// one chunk = one fused launch: it tells a mapped host word when its vertices have landed, and polling that
+		// word costs a few microseconds less than synchronising the stream
+		c->flag_wanted = ++c->flag_seq;
+		c->flag_armed = 0;
+		rc = launch(c, d_chunks, d_offs, nullptr, n, false, tg);
+		c->flag_wanted = 0;
+		if (rc) return rc;
+		bool landed = false;
+		if (c->flag_armed) {
+			const auto t0 = std::chrono::steady_clock::now();
+			for (uint32_t spin = 0;; spin++) {
+				if (*(volatile mm::u64 *)c->h_flag >= c->flag_armed) { landed = true; break; }
+				if ((spin & 255u) == 255u && std::chrono::steady_clock::now() - t0 > std::chrono::milliseconds(2)) break;
+#if defined(__x86_64__)
+				__builtin_ia32_pause();
+#endif
+			}
+		}
+		if (!landed) MM_CUDA(c, cudaStreamSynchronize(c->stream));
 		const uint64_t ti = c->h_host_totals[0], tt = c->h_host_totals[1];
 		if (ti > c->mapped_qi || tt > c->mapped_qt) {  // nothing was written: grow the mapped arenas and run again
 			if (attempt >= 1) return MM_OK;

@@ -51,6 +51,8 @@ struct mm_ctx {
 	uint64_t last_signal_ticket = 0;  // completion signal of the most recent batch that launched kernels (counts on its own)
 	uint64_t signalled_upto = 0;      // newest signal some later launch carries (AnalyseParams::h_done)
 	mm::u64 *h_host_totals = nullptr, *d_h_host_totals = nullptr;  // pinned + mapped, 2 words: totals of the host paths' launches
+	mm::u64 *h_flag = nullptr, *d_h_flag = nullptr;  // pinned + mapped: the fused single-chunk launch of the mapped path says "landed" here
+	mm::u64 flag_seq = 0, flag_wanted = 0, flag_armed = 0;
 	mm::u64 *h_done = nullptr;        // pinned + mapped: ticket of the last batch whose kernels have completed
 	mm::u64 *d_h_done = nullptr;
 	cudaStream_t s_draw = nullptr;    // consumers of finished ring slots run here, beside the mesher's stream

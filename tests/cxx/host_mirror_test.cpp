@@ -3,6 +3,10 @@
 //                                     without a CUDA device)
 //   host_mirror_test cases <file>     mesh_for_chunk / mesh_batch / push_block on a B200 against expected bytes
 //                                     written by tests/test_cxx_host.py (known-answer vectors + oracle output)
+//   host_mirror_test latency <file>   the reference's call pattern from a compiled host: one mesh_for_chunk call per
+//                                     chunk of the file (client.rs:259-267), microseconds per call incl. the Vec copies
+#include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <fstream>
@@ -121,10 +125,54 @@ static int cases(const char *path) {
 	return 0;
 }
 
+static int latency(const char *path) {
+	std::ifstream f(path, std::ios::binary);
+	CHECK(f.good());
+	CHECK(rd<uint32_t>(f) == 0x54434D4Du);
+	const uint32_t n_rows = rd<uint32_t>(f);
+	uint16_t fb[4];
+	f.read(reinterpret_cast<char *>(fb), 8);
+	std::vector<std::optional<MeshDrawStyle>> styles;
+	for (uint32_t i = 0; i < n_rows; i++) {
+		uint16_t r[5];
+		f.read(reinterpret_cast<char *>(r), 10);
+		if (r[0] == 1) styles.push_back(MeshDrawStyle::make_blocky(BlockTextureIds::make({r[1]}, {r[2]}, {r[3]})));
+		else if (r[0] == 2) styles.push_back(MeshDrawStyle::make_crossed({r[4]}));
+		else styles.push_back(std::nullopt);
+	}
+	const TextureIdCache cache(BlockTextureIds::make({fb[0]}, {fb[1]}, {fb[2]}), styles);
+	const uint32_t n = rd<uint32_t>(f);
+	std::vector<std::array<isize, 3>> offs(n);
+	std::vector<MapChunkData> chunks(n);
+	for (uint32_t i = 0; i < n; i++) {
+		f.read(reinterpret_cast<char *>(offs[i].data()), 24);
+		f.read(reinterpret_cast<char *>(chunks[i].ids.data()), 4096);
+		const uint64_t ni = rd<uint64_t>(f), nt = rd<uint64_t>(f);
+		f.seekg((std::streamoff)((ni + nt) * 36), std::ios::cur);
+	}
+	CHECK(f.good());
+	for (uint32_t i = 0; i < n; i++) {
+		for (int w = 0; w < 20; w++) (void)mesh_for_chunk(offs[i], chunks[i], cache);
+		std::vector<double> us(300);
+		size_t verts = 0;
+		for (double &u : us) {
+			const auto t0 = std::chrono::steady_clock::now();
+			const ChunkMesh m = mesh_for_chunk(offs[i], chunks[i], cache);
+			u = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count();
+			verts = m.intransparent.size() + m.transparent.size();
+		}
+		std::sort(us.begin(), us.end());
+		std::printf("{\"chunk\": %u, \"offs\": [%lld, %lld, %lld], \"vertices\": %zu, \"us_median\": %.2f, \"us_p10\": %.2f, \"us_p90\": %.2f}\n", i,
+		            (long long)offs[i][0], (long long)offs[i][1], (long long)offs[i][2], verts, us[150], us[30], us[270]);
+	}
+	return 0;
+}
+
 int main(int argc, char **argv) {
 	try {
 		if (argc >= 2 && std::string(argv[1]) == "selfcheck") return selfcheck();
 		if (argc >= 3 && std::string(argv[1]) == "cases") return cases(argv[2]);
+		if (argc >= 3 && std::string(argv[1]) == "latency") return latency(argv[2]);
 	} catch (const std::exception &e) {
 		std::fprintf(stderr, "exception: %s\n", e.what());
 		return 2;
