@@ -541,7 +541,12 @@ def main():
     vert_bytes = float(np.mean([36 * verts[i % rot] for i in range(args.steps)]))
 
     # ---- end to end through the C ABI with host buffers (H2D + kernel + D2H every step) ----------------------
-    hc, ho, e2e_what = host_sample(wl, rank, world)
+    if wl == "mapgen":   # the product's own generator made these chunks on the device: fetch them (the oracle's mapgen is for the CPU arms)
+        hc = d_chunks[0].cpu().numpy().reshape(n, 4096)
+        ho = d_offs[0].cpu().numpy().reshape(n, 3)
+        e2e_what = "the whole 4096-chunk batch"
+    else:
+        hc, ho, e2e_what = host_sample(wl, rank, world)
     ne = len(hc)
     e2e_steps = 1 if args.quick else (args.e2e_steps or {"terrain": min(args.steps, 20), "single": 200, "million": 3}.get(wl, 5))
     pin_c, pin_o = mesher.host_alloc(ne * 4096), mesher.host_alloc(ne * 24)
