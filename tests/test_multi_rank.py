@@ -79,3 +79,25 @@ def test_reference_arm_under_torchrun_prints_one_line_from_rank0():
     assert d["impl"] == "reference" and d["n_gpus"] == 2 and d["gpu_launches"] == 0
     assert d["metric"] == "chunks_meshed_per_sec" and d["value"] > 0 and d["cpu_baseline"]["kind"] == "port"
     assert d["e2e"]["value"] == d["value"] and d["e2e"]["h2d_bytes_per_step"] == 0
+
+
+def test_million_shards_partition_the_region_and_every_workload_has_a_config():
+    """configs[4] under N ranks: the 128x128x64 region is cut along y into N disjoint boxes that add up to 1,048,576
+    chunks (strong scaling); and every bench workload names its configuration."""
+    sys.path.insert(0, ROOT)
+    import bench
+    for world in (1, 2, 4, 8):
+        seen, total = set(), 0
+        for rank in range(world):
+            c0, dims = bench.million_shard(rank, world)
+            assert dims[0] == 128 and dims[2] == 64 and dims[1] == 128 // world and c0[0] == -64 and c0[2] == -32
+            ys = set(range(c0[1], c0[1] + dims[1]))
+            assert not (ys & seen)
+            seen |= ys
+            total += dims[0] * dims[1] * dims[2]
+        assert total == 1 << 20 and seen == set(range(-64, 64))
+    for wl in bench.WORKLOADS:
+        cfg = bench.workload_config(wl, 4096, 2)
+        assert cfg["workload"] and cfg["l2"]
+    c, o = bench.checkerboard(5, parity0=1)
+    assert c.shape == (5, 4096) and set(np.unique(c)) == {0, 5} and (c[0] != c[1]).all() and o.shape == (5, 3)
