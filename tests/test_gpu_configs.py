@@ -276,3 +276,40 @@ def test_single_chunk_host_calls_between_ring_batches_leave_them_alone(ocache):
         assert_batch_equal(m.copy_out_ticket(t1), want)
         assert_batch_equal(m.copy_out_ticket(t2), want)
         m.dev_free(dc); m.dev_free(do)
+
+
+def test_error_behaviour_of_the_c_abi():
+    """The reference's mesher is infallible (no Result, lib.rs:231-232); the C ABI answers every misuse with a status
+    code and a message, never with a crash or a silently wrong mesh: no table, bad arguments, no batch, bad ring size,
+    a table row of an unknown kind -- and the context keeps working afterwards."""
+    import ctypes as C
+    import mimas_b200
+    from mimas_b200._lib import MMError, lib
+    l = lib()
+    with mimas_b200.Mesher(0) as m:                       # no table yet
+        chunk = np.zeros(4096, np.uint8)
+        with pytest.raises(MMError) as e:
+            m.mesh_for_chunk((0, 0, 0), chunk)
+        assert e.value.code == 5                          # MM_ERR_NO_TABLE
+        assert b"mm_set_block_table" in l.mm_last_error_string(m._ctx)
+        with pytest.raises(MMError) as e:
+            m.batch_finish()
+        assert e.value.code == 6                          # MM_ERR_NO_BATCH
+        with pytest.raises(MMError) as e:
+            m.ring_configure(9)
+        assert e.value.code == 1                          # MM_ERR_INVALID
+        bad = np.zeros(256, dtype=mimas_b200.meshgen.BLOCK_ENTRY_DTYPE)
+        bad["kind"][7] = 3
+        with pytest.raises(MMError) as e:
+            m.set_table(bad)
+        assert e.value.code == 1
+        assert l.mm_mesh_batch(m._ctx, None, None, None, 5, None) == 1
+        assert l.mm_batch_wait(m._ctx, 0, None) == 1
+        assert l.mm_ctx_create(99, C.byref(C.c_void_p())) == 1   # no such device
+        m.set_cache(product_cache(G))                     # and now it works
+        c = G.cases["layered_terrain"]
+        got = m.mesh_for_chunk(c["offs"], c["chunk"])
+        assert first_diff(got.intransparent.tobytes(), c["intr"]) is None
+        with pytest.raises(MMError) as e:
+            m.batch_wait(12345)                           # a ticket that was never issued
+        assert e.value.code == 6
