@@ -4,8 +4,8 @@
     python scripts/ncu_summary.py gpurun_out/<tag>_prof.ncu-rep profiles/<name>
 
 Writes <name>_ncu_summary.json (key metrics per captured launch), <name>_ncu_hot.txt (the
-hottest SASS instructions with their dominant stall reason) and refreshes
-profiles/roofline_traffic.json (DRAM bytes per launch of the mesher kernel, read by bench.py).
+hottest SASS instructions with their dominant stall reason).  The steady-state DRAM traffic that bench.py reports
+(profiles/roofline_traffic.json) comes from scripts/ncu_steady.py, not from this cold, serialised capture.
 """
 import csv
 import io
@@ -71,10 +71,7 @@ def main():
                 pairs.append(a["dram_bytes_total"] + b["dram_bytes_total"])
     if pairs:
         traffic = pairs
-    if traffic:
-        json.dump({"source": os.path.basename(out) + "_ncu_summary.json", "kernel": "analyse_kernel + expand_kernel" if pairs else launches[0]["kernel"],
-                   "dram_bytes_per_launch": sum(traffic) / len(traffic), "per_launch": traffic},
-                  open(os.path.join(os.path.dirname(out) or ".", "roofline_traffic.json"), "w"), indent=1)
+    # (cold, serialised captures under-count DRAM traffic: profiles/roofline_traffic.json comes from scripts/ncu_steady.py)
 
     # hottest instructions of the first captured launch
     src = list(csv.reader(io.StringIO(ncu(rep, "--page", "source", "--csv", "--print-source", "sass"))))
