@@ -348,13 +348,17 @@ class Mesher:
                                                 C.c_void_p(d_halo) if d_halo else None, n, C.byref(t)))
         return t.value
 
-    def submit_many(self, d_chunks: Sequence[int], d_offs: Sequence[int], n: Sequence[int], repeat: int = 1) -> int:
-        """mm_mesh_batches_submit: k batches (x repeat, round robin) enqueued by ONE foreign call; returns the
-        first ticket (the others follow consecutively)."""
+    @staticmethod
+    def prepare_many(d_chunks: Sequence[int], d_offs: Sequence[int], n: Sequence[int]):
+        """The argument arrays of mm_mesh_batches_submit, built once (outside a timed region: marshalling a dozen
+        pointers in Python costs more than the call)."""
         k = len(n)
-        pc = (C.c_void_p * k)(*d_chunks)
-        po = (C.c_void_p * k)(*d_offs)
-        pn = (C.c_uint32 * k)(*n)
+        return ((C.c_void_p * k)(*d_chunks), (C.c_void_p * k)(*d_offs), (C.c_uint32 * k)(*n), k)
+
+    def submit_many(self, d_chunks=None, d_offs=None, n=None, repeat: int = 1, prepared=None) -> int:
+        """mm_mesh_batches_submit: k batches (x repeat, round robin) enqueued by ONE foreign call; returns the
+        first ticket (the others follow consecutively).  `prepared` = the result of prepare_many."""
+        pc, po, pn, k = prepared if prepared is not None else self.prepare_many(d_chunks, d_offs, n)
         t = C.c_uint64()
         self._ck(self._lib.mm_mesh_batches_submit(self._ctx, pc, po, pn, k, repeat, C.byref(t)))
         return t.value

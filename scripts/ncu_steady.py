@@ -40,15 +40,15 @@ def run():
         m.mesh_batch_device(dc[r].data_ptr(), do[r].data_ptr(), N)
         out = m.mesh_batch_device(dc[r].data_ptr(), do[r].data_ptr(), N)
         verts.append(out.n_intransparent + out.n_transparent)
-    pc, po = [t.data_ptr() for t in dc], [t.data_ptr() for t in do]
+    many = m.prepare_many([t.data_ptr() for t in dc], [t.data_ptr() for t in do], [N] * rot)
     with torch.cuda.stream(st):
-        m.submit_many(pc, po, [N] * rot, repeat=WARM // rot)
+        m.submit_many(prepared=many, repeat=WARM // rot)
         m.batch_finish()
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         torch.cuda.profiler.start()
         e0.record(st)
-        m.submit_many(pc, po, [N] * rot, repeat=STEPS // rot)
+        m.submit_many(prepared=many, repeat=STEPS // rot)
         e1.record(st)
         torch.cuda.synchronize()
         torch.cuda.profiler.stop()
