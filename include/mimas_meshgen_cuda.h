@@ -260,6 +260,25 @@ typedef struct mm_mapgen_params {
 int mm_gen_mapgen_device(mm_ctx *ctx, uint64_t seed, const mm_mapgen_params *params, int64_t cx0, int64_t cy0, int64_t cz0,
                          uint32_t nx, uint32_t ny, uint32_t nz, uint8_t *d_chunks, int64_t *d_offs, uint32_t *d_tree_counts);
 
+/* The mesher for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  No counterpart in the reference.
+ * Same result as mm_mesh_batch(halo = NULL) for n <= MM_NOALLOC_MAX_CHUNKS chunks, bit for bit, but the caller owns
+ * every output and the call allocates nothing (no cudaMalloc / cudaFree / cudaHostAlloc, in any call, first or
+ * later): the analysis -> expansion hand-over lives in a static device array of
+ * MM_NOALLOC_MAX_CHUNKS x 64 KiB + 2.25 KiB = 16.0 MiB that every GPU which loads the library holds until exit.
+ * All pointers are device pointers: chunks (n x 4096, 16-byte aligned), offs (n x 3), d_out_i / d_out_t vertex
+ * buffers of cap_*_vertices vertices (16-byte aligned; a capacity of 0 is allowed), d_ranges_i / d_ranges_t (n
+ * records each), d_totals (2 words: QUADS in each stream, x 6 = vertices).  The two kernels are enqueued on the
+ * context's stream and the call returns; mm_ctx_sync waits.  A stream whose total exceeds its capacity is not
+ * written at all (range records and totals still are): compare d_totals with the capacity.
+ * n > MM_NOALLOC_MAX_CHUNKS is MM_ERR_INVALID with a message.  The block table must be set (mm_set_block_table,
+ * at set-up; that call does allocate).  Every call on every context of a device shares the one scratch array:
+ * calls on one stream run in order and are safe; calls that overlap on the GPU (two contexts / streams) race. */
+#define MM_NOALLOC_MAX_CHUNKS 256u
+int mm_mesh_batch_noalloc(mm_ctx *ctx, const uint8_t *d_chunks, const int64_t *d_offs, uint32_t n, mm_vertex *d_out_i,
+                          uint64_t cap_i_vertices, mm_vertex *d_out_t, uint64_t cap_t_vertices, mm_range *d_ranges_i,
+                          mm_range *d_ranges_t, uint64_t *d_totals);
+
 /* Plain device memory helpers so that non-CUDA host code (ctypes, Rust) can keep
  * inputs resident without linking the CUDA runtime itself. */
 int mm_dev_alloc(mm_ctx *ctx, size_t bytes, void **d_ptr);

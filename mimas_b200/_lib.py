@@ -24,7 +24,7 @@ SYMBOLS = (
     "mm_debug_trace", "mm_vertex_stage", "mm_cull_chunks", "mm_draw_batch", "mm_mesh_batch_halo_async",
     "mm_gather_halos", "mm_set_textures", "mm_raster_frame", "mm_ring_configure", "mm_mesh_batch_submit",
     "mm_mesh_batches_submit", "mm_batch_wait", "mm_batch_poll", "mm_copy_out_ticket", "mm_draw_ticket",
-    "mm_gen_mapgen_device", "mm_draw_ticket_async", "mm_draw_collect",
+    "mm_gen_mapgen_device", "mm_draw_ticket_async", "mm_draw_collect", "mm_mesh_batch_noalloc",
 )
 
 
@@ -73,6 +73,7 @@ def lib() -> C.CDLL:
     l.mm_dev_upload.argtypes = [vp, vp, vp, C.c_size_t]
     l.mm_dev_download.argtypes = [vp, vp, vp, C.c_size_t]
     l.mm_ctx_sync.argtypes = [vp]
+    l.mm_mesh_batch_noalloc.argtypes = [vp, vp, vp, u32, vp, u64, vp, u64, vp, vp, vp]
     l.mm_host_alloc.argtypes = [vp, C.c_size_t, C.POINTER(vp)]
     l.mm_host_free.argtypes = [vp, vp]
     l.mm_launch_count.argtypes = [vp, C.POINTER(u64)]

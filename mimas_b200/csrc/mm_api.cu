@@ -12,6 +12,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <mutex>
 #include <new>
 #include <thread>
 #include <vector>
@@ -1035,6 +1036,125 @@ int mm_dev_download(mm_ctx *c, void *h_dst, const void *d_src, size_t bytes) {
 	if (use_device(c)) return MM_ERR_CUDA;
 	MM_CUDA(c, cudaMemcpyAsync(h_dst, d_src, bytes, cudaMemcpyDeviceToHost, c->stream));
 	MM_CUDA(c, cudaStreamSynchronize(c->stream));
+	return MM_OK;
+}
+
+}  // extern "C"
+
+// ---- mm_mesh_batch_noalloc: the mesher for callers that must not allocate ------------------------------------
+// No counterpart in the reference.  The analysis -> expansion
+// hand-over (descriptor slots, counts, ticket word) of up to MM_NOALLOC_MAX_CHUNKS chunks lives in a file-scope
+// device array instead of cudaMalloc'ed buffers: every GPU that loads the library holds it until exit.  All calls
+// share it (contents of the last call stay; the ticket word is cleared on the stream before every pair).
+namespace {
+constexpr size_t kNaHead = 256;                                                        // ticket word
+constexpr size_t kNaCnt = sizeof(uint32_t) * MM_NOALLOC_MAX_CHUNKS;                    // cnt_i, then cnt_t
+constexpr size_t kNaDescI = sizeof(uint32_t) * (size_t)MM_NOALLOC_MAX_CHUNKS * mm::kDescStrideI;
+constexpr size_t kNaDescT = sizeof(uint32_t) * (size_t)MM_NOALLOC_MAX_CHUNKS * mm::kDescStrideT;
+constexpr size_t kNaBytes = kNaHead + 2 * kNaCnt + kNaDescI + kNaDescT;
+static_assert(MM_NOALLOC_MAX_CHUNKS % 4 == 0 && MM_NOALLOC_MAX_CHUNKS <= mm::kMaxLaunchChunks, "counts are read four at a time; one launch pair");
+static_assert(kNaCnt % 256 == 0 && kNaDescI % 256 == 0, "every part stays 256-byte aligned");
+}  // namespace
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNaBytes];
+namespace {
+// In host code g_noalloc_scratch is a stand-in, not a device address: the address the kernels get comes from
+// cudaGetSymbolAddress, looked up once per device with that device current.
+std::mutex g_noalloc_mutex;
+unsigned char *g_noalloc_ptr[64] = {nullptr};
+int noalloc_scratch(mm_ctx *c, unsigned char **out) {
+	if (c->device < 0 || c->device >= 64) return fail(c, MM_ERR_UNSUPPORTED, "device index %d beyond the table of scratch addresses", c->device);
+	std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+	if (!g_noalloc_ptr[c->device]) {
+		void *p = nullptr;
+		const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);  // use_device(c) made c->device current
+		if (e != cudaSuccess || !p) return fail(c, MM_ERR_CUDA, "cudaGetSymbolAddress(g_noalloc_scratch): %s", cudaGetErrorString(e));
+		g_noalloc_ptr[c->device] = (unsigned char *)p;
+	}
+	*out = g_noalloc_ptr[c->device];
+	return MM_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int mm_mesh_batch_noalloc(mm_ctx *c, const uint8_t *d_chunks, const int64_t *d_offs, uint32_t n, mm_vertex *d_out_i,
+                          uint64_t cap_i_vertices, mm_vertex *d_out_t, uint64_t cap_t_vertices, mm_range *d_ranges_i,
+                          mm_range *d_ranges_t, uint64_t *d_totals) {
+	if (!c || !d_totals || (n && (!d_chunks || !d_offs || !d_ranges_i || !d_ranges_t))) return MM_ERR_INVALID;
+	if (n > MM_NOALLOC_MAX_CHUNKS)
+		return fail(c, MM_ERR_INVALID, "mm_mesh_batch_noalloc: %u chunks exceed the static scratch of %u chunks (MM_NOALLOC_MAX_CHUNKS); use mm_mesh_batch",
+		            n, (unsigned)MM_NOALLOC_MAX_CHUNKS);
+	if ((cap_i_vertices && !d_out_i) || (cap_t_vertices && !d_out_t)) return fail(c, MM_ERR_INVALID, "capacity without an output buffer");
+	if (n && ((uintptr_t)d_chunks & 15u)) return fail(c, MM_ERR_INVALID, "chunks must be 16-byte aligned");
+	if (((uintptr_t)d_offs | (uintptr_t)d_ranges_i | (uintptr_t)d_ranges_t | (uintptr_t)d_totals) & 7u)
+		return fail(c, MM_ERR_INVALID, "offs, range records and totals must be 8-byte aligned");
+	if (((uintptr_t)d_out_i | (uintptr_t)d_out_t) & 15u) return fail(c, MM_ERR_INVALID, "vertex buffers must be 16-byte aligned");
+	if (!c->have_table) return fail(c, MM_ERR_NO_TABLE, "mm_set_block_table has not been called");
+	if (use_device(c)) return MM_ERR_CUDA;
+	if (n == 0) {
+		MM_CUDA(c, cudaMemsetAsync(d_totals, 0, 2 * sizeof(uint64_t), c->stream));
+		return MM_OK;
+	}
+	unsigned char *scr = nullptr;
+	int rc;
+	if ((rc = noalloc_scratch(c, &scr))) return rc;
+	MM_CUDA(c, cudaMemsetAsync(scr, 0, kNaHead, c->stream));  // the ticket word starts every pair at zero
+
+	mm::AnalyseParams a;
+	memset(&a, 0, sizeof(a));
+	a.chunks = d_chunks;
+	a.halo = nullptr;
+	a.n = n;
+	a.table = c->d_table;
+	a.flags = c->d_flags;
+	a.cnt_i = reinterpret_cast<uint32_t *>(scr + kNaHead);
+	a.cnt_t = reinterpret_cast<uint32_t *>(scr + kNaHead + kNaCnt);
+	a.desc_i = reinterpret_cast<uint32_t *>(scr + kNaHead + 2 * kNaCnt);
+	a.desc_t = reinterpret_cast<uint32_t *>(scr + kNaHead + 2 * kNaCnt + kNaDescI);
+	a.ticket = reinterpret_cast<mm::u64 *>(scr);
+	a.ticket_base = 0;
+	a.trace = nullptr;
+	a.h_done = nullptr;
+	a.prev_done = 0;
+	// no programmatic dependent launch: the pair runs strictly after whatever is on the stream, and in order
+	cudaLaunchAttribute attr[1];
+	attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+	attr[0].val.programmaticStreamSerializationAllowed = 0;
+	{
+		cudaLaunchConfig_t cfg = {};
+		cfg.gridDim = dim3(std::min<uint32_t>(n, (uint32_t)(c->sm_count * c->analyse_ctas_per_sm)));
+		cfg.blockDim = dim3(mm::kThreads);
+		cfg.stream = c->stream;
+		cfg.attrs = attr;
+		cfg.numAttrs = 1;
+		MM_CUDA(c, cudaLaunchKernelEx(&cfg, mm::analyse_kernel<false>, a));
+	}
+	mm::ExpandParams e;
+	memset(&e, 0, sizeof(e));
+	e.offs = (const long long *)d_offs;
+	e.n = n;
+	e.table = c->d_table;
+	e.desc_i = a.desc_i; e.desc_t = a.desc_t; e.cnt_i = a.cnt_i; e.cnt_t = a.cnt_t;
+	e.out_i = (unsigned char *)d_out_i; e.out_t = (unsigned char *)d_out_t;
+	e.cap_i = cap_i_vertices / 6; e.cap_t = cap_t_vertices / 6;
+	e.ranges_i = (mm::Range *)d_ranges_i; e.ranges_t = (mm::Range *)d_ranges_t;
+	e.carry_in = nullptr;
+	e.totals = (mm::u64 *)d_totals;
+	e.host_totals = (mm::u64 *)d_totals;  // the kernel writes the two words twice; the caller's device words take both
+	e.trace = nullptr;
+	e.h_flag = nullptr;
+	e.flag_value = 0;
+	{
+		cudaLaunchConfig_t cfg = {};
+		cfg.gridDim = dim3((unsigned)c->expand_grid);
+		cfg.blockDim = dim3(mm::kExpandThreads);
+		cfg.dynamicSmemBytes = mm::kExpandSmemBytes;
+		cfg.stream = c->stream;
+		cfg.attrs = attr;
+		cfg.numAttrs = 1;
+		MM_CUDA(c, cudaLaunchKernelEx(&cfg, mm::expand_kernel, e));
+	}
+	c->total_launches += 2;
 	return MM_OK;
 }
 

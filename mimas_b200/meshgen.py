@@ -530,6 +530,13 @@ class Mesher:
     def sync(self):
         self._ck(self._lib.mm_ctx_sync(self._ctx))
 
+    def mesh_batch_noalloc(self, d_chunks: int, d_offs: int, n: int, d_out_i: int, cap_i_vertices: int, d_out_t: int,
+                           cap_t_vertices: int, d_ranges_i: int, d_ranges_t: int, d_totals: int):
+        """mm_mesh_batch_noalloc: every buffer is the caller's, nothing is allocated, n <= 256; asynchronous."""
+        self._ck(self._lib.mm_mesh_batch_noalloc(self._ctx, C.c_void_p(d_chunks), C.c_void_p(d_offs), n, C.c_void_p(d_out_i),
+                                                 cap_i_vertices, C.c_void_p(d_out_t), cap_t_vertices, C.c_void_p(d_ranges_i),
+                                                 C.c_void_p(d_ranges_t), C.c_void_p(d_totals)))
+
     def device_info(self) -> Tuple[int, int, int]:
         a, b, c = C.c_int(), C.c_int(), C.c_int()
         self._ck(self._lib.mm_device_info(self._ctx, C.byref(a), C.byref(b), C.byref(c)))
