@@ -62,6 +62,7 @@ struct CullParams {
 	uint32_t *draw;                        // n
 	unsigned long long *first_i, *first_t; // per drawn chunk: where its shaded vertices start
 	unsigned long long *totals;            // [0] drawn chunks, [1] vertices i, [2] vertices t (mapped host memory)
+	unsigned long long *totals_dev;        // the same three words in device memory, for the draw kernel
 };
 
 __device__ __forceinline__ bool chunk_visible(const CullParams &p, uint32_t i) {
@@ -164,6 +165,9 @@ __global__ void __launch_bounds__(kCullThreads) scan_blocks_kernel(const CullPar
 		__syncthreads();
 	}
 	if (threadIdx.x == 0) {
+		p.totals_dev[0] = carry[0];
+		p.totals_dev[1] = carry[1];
+		p.totals_dev[2] = carry[2];
 		p.totals[0] = carry[0];
 		p.totals[1] = carry[1];
 		p.totals[2] = carry[2];
@@ -287,6 +291,7 @@ int setup_cull(mm_ctx *c, uint32_t n, CullParams &p) {
 	p.bs_cnt = (uint32_t *)(c->d_cull + o_bc);
 	p.bs_vi = (unsigned long long *)(c->d_cull + o_bi);
 	p.bs_vt = (unsigned long long *)(c->d_cull + o_bt);
+	p.totals_dev = (unsigned long long *)(c->d_cull + total - 256);  // the spare 256 bytes at the end
 	return MM_OK;
 }
 
@@ -397,7 +402,7 @@ static int draw_enqueue(mm_ctx *c, const mm_slot *sl, cudaStream_t stream, const
 	p.ranges_t = sl->d_ranges_t;
 	p.totals = c->d_h_draw_totals;
 	DrawParams d;
-	d.draw = p.draw; d.first_i = p.first_i; d.first_t = p.first_t; d.totals = c->d_h_draw_totals;
+	d.draw = p.draw; d.first_i = p.first_i; d.first_t = p.first_t; d.totals = p.totals_dev;  // device copy: no PCIe read per CTA
 	d.ranges_i = sl->d_ranges_i; d.ranges_t = sl->d_ranges_t;
 	d.vi = (const mm_vertex *)sl->d_out_i; d.vt = (const mm_vertex *)sl->d_out_t;
 	d.out = (mm_shaded_vertex *)c->d_shaded;
