@@ -456,7 +456,7 @@ def main():
     alg_bytes = [n * (4096 + 24 + 16) + 36 * v + 2048 * pairs for v in verts]
 
     # ---- device-resident timed region ----------------------------------------------------------------------
-    sampler = ClockSampler(local_rank) if rank == 0 else None
+    sampler = ClockSampler(local_rank)   # every rank samples its own GPU; rank 0's goes into `clocks`, all of them into `ranks`
     windows = []
     consumed = None
     flush = None if streamed or wl in ("single", "million", "checkerboard16384") else torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
@@ -533,6 +533,7 @@ def main():
             barrier()
             windows.append((t_host0, time.time()))
     gpu_launches = mesher.launch_count() - launches0
+    own_ms_total = ms_total
     ms_total = max_over_ranks(ms_total)
     ms_per_step = ms_total / args.steps
     n_job = world * n   # strong scaling: the shards add up to the whole region; weak: every rank its own batch
@@ -578,6 +579,11 @@ def main():
     e2e_s = max_over_ranks(t1 - t0)
     e2e_value = world * ne * e2e_steps / e2e_s
     clocks = sampler.stop(windows) if sampler else None
+    per_rank = None
+    if world > 1:   # outside every timed region: which GPU was the slowest, and was it throttled (the value follows the slowest rank)
+        import torch.distributed as dist
+        per_rank = [None] * world
+        dist.all_gather_object(per_rank, {"rank": rank, "ms_per_step": own_ms_total / args.steps, "clocks": clocks})
 
     # ---- CPU baseline on this box's host cores (rank 0, N = 1 only): a bounded sample of the workload -----------
     cpu = None
@@ -624,6 +630,8 @@ def main():
         if latency:
             line["roofline"]["note"] = "latency-bound workload (launch + PCIe round trip), reported for completeness, not graded against the roofline"
             line["latency_us"] = {"device_resident_call": 1e3 * ms_per_step, "host_call": 1e6 * e2e_s / e2e_steps / calls}
+        if per_rank:
+            line["ranks"] = per_rank
         if consumed:
             line["consumed"] = consumed
         if cpu:
