@@ -130,38 +130,77 @@ __device__ __forceinline__ double powi4(double a) {
 __device__ __forceinline__ double clamp1(double v) { return v < -1.0 ? -1.0 : (v > 1.0 ? 1.0 : v); }
 __device__ __forceinline__ unsigned perm2(const uint8_t *t, long long x, long long y) { return t[t[x & 0xff] ^ (unsigned)(y & 0xff)]; }
 
-__device__ __forceinline__ double surflet2(const uint8_t *t, long long cx, long long cy, double dx, double dy) {
+__device__ __forceinline__ double surflet2(const uint8_t *t, const double (*g2)[2], long long cx, long long cy, double dx, double dy) {
 	const double attn = 1.0 - (dx * dx + dy * dy);
 	if (attn > 0.0) {
 		const unsigned g = perm2(t, cx, cy) & 7u;
-		return powi4(attn) * (dx * c_grad2[g][0] + dy * c_grad2[g][1]);
+		return powi4(attn) * (dx * g2[g][0] + dy * g2[g][1]);
 	}
 	return 0.0;
 }
-__device__ double perlin2(const uint8_t *t, double x, double y) {
+// g2 / g3: the gradient tables in SHARED memory (the index differs from lane to lane: from __constant__ memory
+// such a read is served one address after the other)
+__device__ double perlin2(const uint8_t *t, const double (*g2)[2], double x, double y) {
 	const double fx = floor(x), fy = floor(y);
 	const long long nx = (long long)fx, ny = (long long)fy;
 	const double dx = x - fx, dy = y - fy, ex = dx - 1.0, ey = dy - 1.0;
-	const double f00 = surflet2(t, nx, ny, dx, dy), f10 = surflet2(t, nx + 1, ny, ex, dy);
-	const double f01 = surflet2(t, nx, ny + 1, dx, ey), f11 = surflet2(t, nx + 1, ny + 1, ex, ey);
+	const double f00 = surflet2(t, g2, nx, ny, dx, dy), f10 = surflet2(t, g2, nx + 1, ny, ex, dy);
+	const double f01 = surflet2(t, g2, nx, ny + 1, dx, ey), f11 = surflet2(t, g2, nx + 1, ny + 1, ex, ey);
 	return clamp1((f00 + f10 + f01 + f11) * 3.1604938271604937);
 }
-__device__ __forceinline__ double surflet3(const uint8_t *t, long long cx, long long cy, long long cz, double dx, double dy, double dz) {
+__device__ __forceinline__ double surflet3(const uint8_t *t, const double (*g3)[3], long long cx, long long cy, long long cz, double dx, double dy, double dz) {
 	const double attn = 1.0 - (dx * dx + dy * dy + dz * dz);
 	if (attn > 0.0) {
 		const unsigned g = t[perm2(t, cx, cy) ^ (unsigned)(cz & 0xff)] & 31u;
-		return powi4(attn) * (dx * c_grad3[g][0] + dy * c_grad3[g][1] + dz * c_grad3[g][2]);
+		return powi4(attn) * (dx * g3[g][0] + dy * g3[g][1] + dz * g3[g][2]);
 	}
 	return 0.0;
 }
-__device__ double perlin3(const uint8_t *t, double x, double y, double z) {
+__device__ double perlin3(const uint8_t *t, const double (*g3)[3], double x, double y, double z) {
 	const double fx = floor(x), fy = floor(y), fz = floor(z);
 	const long long nx = (long long)fx, ny = (long long)fy, nz = (long long)fz;
 	const double dx = x - fx, dy = y - fy, dz = z - fz, ex = dx - 1.0, ey = dy - 1.0, ez = dz - 1.0;
-	const double f000 = surflet3(t, nx, ny, nz, dx, dy, dz), f100 = surflet3(t, nx + 1, ny, nz, ex, dy, dz);
-	const double f010 = surflet3(t, nx, ny + 1, nz, dx, ey, dz), f110 = surflet3(t, nx + 1, ny + 1, nz, ex, ey, dz);
-	const double f001 = surflet3(t, nx, ny, nz + 1, dx, dy, ez), f101 = surflet3(t, nx + 1, ny, nz + 1, ex, dy, ez);
-	const double f011 = surflet3(t, nx, ny + 1, nz + 1, dx, ey, ez), f111 = surflet3(t, nx + 1, ny + 1, nz + 1, ex, ey, ez);
+	const double f000 = surflet3(t, g3, nx, ny, nz, dx, dy, dz), f100 = surflet3(t, g3, nx + 1, ny, nz, ex, dy, dz);
+	const double f010 = surflet3(t, g3, nx, ny + 1, nz, dx, ey, dz), f110 = surflet3(t, g3, nx + 1, ny + 1, nz, ex, ey, dz);
+	const double f001 = surflet3(t, g3, nx, ny, nz + 1, dx, dy, ez), f101 = surflet3(t, g3, nx + 1, ny, nz + 1, ex, dy, ez);
+	const double f011 = surflet3(t, g3, nx, ny + 1, nz + 1, dx, ey, ez), f111 = surflet3(t, g3, nx + 1, ny + 1, nz + 1, ex, ey, ez);
+	return clamp1((f000 + f100 + f010 + f110 + f001 + f101 + f011 + f111) * 3.8898553255531074);
+}
+
+// perlin3 for the cells of ONE column: x and y are fixed, so the floors, the fractions, the four (x, y) corner hashes and
+// the partial sums dx*dx + dy*dy are worked out once per column and noise; every expression keeps the operand order of
+// surflet3 / perlin3 above, so the values are the same bit for bit.
+struct ColXY {
+	double dx, dy, ex, ey, s00, s10, s01, s11;
+	unsigned h00, h10, h01, h11;
+};
+__device__ __forceinline__ ColXY col_xy(const uint8_t *t, double x, double y) {
+	const double fx = floor(x), fy = floor(y);
+	const long long nx = (long long)fx, ny = (long long)fy;
+	ColXY c;
+	c.dx = x - fx; c.dy = y - fy; c.ex = c.dx - 1.0; c.ey = c.dy - 1.0;
+	c.s00 = c.dx * c.dx + c.dy * c.dy; c.s10 = c.ex * c.ex + c.dy * c.dy;
+	c.s01 = c.dx * c.dx + c.ey * c.ey; c.s11 = c.ex * c.ex + c.ey * c.ey;
+	c.h00 = perm2(t, nx, ny); c.h10 = perm2(t, nx + 1, ny); c.h01 = perm2(t, nx, ny + 1); c.h11 = perm2(t, nx + 1, ny + 1);
+	return c;
+}
+__device__ __forceinline__ double surflet3h(const uint8_t *t, const double (*g3)[3], unsigned h, long long cz, double dx, double dy,
+                                            double dz, double sxy) {
+	const double attn = 1.0 - (sxy + dz * dz);
+	if (attn > 0.0) {
+		const unsigned g = t[h ^ (unsigned)(cz & 0xff)] & 31u;
+		return powi4(attn) * (dx * g3[g][0] + dy * g3[g][1] + dz * g3[g][2]);
+	}
+	return 0.0;
+}
+__device__ __forceinline__ double perlin3_col(const uint8_t *t, const double (*g3)[3], const ColXY &c, double z) {
+	const double fz = floor(z);
+	const long long nz = (long long)fz;
+	const double dz = z - fz, ez = dz - 1.0;
+	const double f000 = surflet3h(t, g3, c.h00, nz, c.dx, c.dy, dz, c.s00), f100 = surflet3h(t, g3, c.h10, nz, c.ex, c.dy, dz, c.s10);
+	const double f010 = surflet3h(t, g3, c.h01, nz, c.dx, c.ey, dz, c.s01), f110 = surflet3h(t, g3, c.h11, nz, c.ex, c.ey, dz, c.s11);
+	const double f001 = surflet3h(t, g3, c.h00, nz + 1, c.dx, c.dy, ez, c.s00), f101 = surflet3h(t, g3, c.h10, nz + 1, c.ex, c.dy, ez, c.s10);
+	const double f011 = surflet3h(t, g3, c.h01, nz + 1, c.dx, c.ey, ez, c.s01), f111 = surflet3h(t, g3, c.h11, nz + 1, c.ex, c.ey, ez, c.s11);
 	return clamp1((f000 + f100 + f010 + f110 + f001 + f101 + f011 + f111) * 3.8898553255531074);
 }
 
@@ -203,13 +242,16 @@ struct Box {
 
 // one CTA of 256 threads per chunk, thread <-> column (x, y) = (tid >> 4, tid & 15): the reference's loop order
 #ifndef MM_MAPGEN_MINBLOCKS
-#define MM_MAPGEN_MINBLOCKS 5   // 48 registers: 1.43 ms per 4096 chunks against 1.75 ms uncapped (124 registers, two CTAs per SM)
+#define MM_MAPGEN_MINBLOCKS 5   // 48 registers, 5 CTAs per SM: measured best
 #endif
 __global__ void __launch_bounds__(256, MM_MAPGEN_MINBLOCKS) mapgen_kernel(const GenTables *__restrict__ gt, Box bx, uint32_t n, uint8_t *chunks,
                                                      long long *offs, uint32_t *tree_counts) {
 	__shared__ uint8_t perm[kFixedNoises + kMaxOres][256];
 	__shared__ uint32_t scratch[8];
+	__shared__ double g2[8][2], g3[32][3];
 	const int tid = threadIdx.x;
+	if (tid < 16) (&g2[0][0])[tid] = (&c_grad2[0][0])[tid];
+	if (tid < 96) (&g3[0][0])[tid] = (&c_grad3[0][0])[tid];
 	const uint32_t n_ores = gt->n_ores, n_plants = gt->n_plants;
 	for (uint32_t i = (uint32_t)tid; i < (kFixedNoises + n_ores) * 64u; i += 256u)
 		reinterpret_cast<uint32_t *>(perm)[i] = reinterpret_cast<const uint32_t *>(gt->perm)[i];
@@ -221,7 +263,7 @@ __global__ void __launch_bounds__(256, MM_MAPGEN_MINBLOCKS) mapgen_kernel(const 
 		if (tid < 3 && offs) offs[3 * (size_t)ci + tid] = tid == 0 ? ox : (tid == 1 ? oy : oz);
 		const u64 ph = pos_hash(ox, oy, oz);
 		const double px = (double)(ox + x), py = (double)(oy + y);
-		auto n2 = [&](int k) { return perlin2(perm[k], px * gt->freq[k], py * gt->freq[k]); };
+		auto n2 = [&](int k) { return perlin2(perm[k], g2, px * gt->freq[k], py * gt->freq[k]); };
 		// mapgen.rs:136-143
 		const double sm_elev = n2(N_SMACRO) * gt->mag[N_SMACRO];
 		const double amp = 1.0 + n2(N_AMP) * 0.9;
@@ -243,28 +285,43 @@ __global__ void __launch_bounds__(256, MM_MAPGEN_MINBLOCKS) mapgen_kernel(const 
 #pragma unroll
 		for (int i = 0; i < kMaxOres; i++) ore_pass[i] = 0;
 		uint32_t cave = 0;
-		for (int z = 0; z < (int)els; z++) {
-			const long long z_abs = oz + z;
-			const double pz = (double)z_abs;
-#pragma unroll
-			for (int i = 0; i < kMaxOres; i++)
-				if ((uint32_t)i < n_ores) {
-					const double limit = z_abs < gt->ore_boundary[i] ? gt->ore_limit_b[i] : gt->ore_limit_a[i];
-					const double f = gt->freq[kFixedNoises + i];
-					if (perlin3(perm[kFixedNoises + i], px * f, py * f, pz * f) > limit) ore_pass[i] |= 1u << z;
-				}
-			double mcave_thresh;
-			if (z_abs > -400) mcave_thresh = 2.0;
-			else {
-				double v = (double)(z_abs + 600) / 300.0;
-				v = v > -0.502 ? v : -0.502;
-				v = v < 0.0 ? v : 0.0;
-				mcave_thresh = 1.0 + v;
+		// (noise by noise, the column's cells inside: the tests are pure, their order is free)
+#pragma unroll 1
+		for (uint32_t i = 0; i < n_ores; i++) {
+			const double f = gt->freq[kFixedNoises + i], la = gt->ore_limit_a[i], lb = gt->ore_limit_b[i];
+			const long long boundary = gt->ore_boundary[i];
+			const uint8_t *t = perm[kFixedNoises + i];
+			const ColXY c = col_xy(t, px * f, py * f);
+			uint32_t pass = 0;
+			for (int z = 0; z < (int)els; z++) {
+				const long long z_abs = oz + z;
+				if (perlin3_col(t, g3, c, (double)z_abs * f) > (z_abs < boundary ? lb : la)) pass |= 1u << z;
 			}
+#pragma unroll
+			for (int k = 0; k < kMaxOres; k++)
+				if ((uint32_t)k == i) ore_pass[k] = pass;
+		}
+		{
 			const double fm = gt->freq[N_MCAVE], fc = gt->freq[N_CAVE];
-			const bool cave_block = perlin3(perm[N_MCAVE], px * fm, py * fm, pz * fm) > mcave_thresh ||
-			                        perlin3(perm[N_CAVE], px * fc, py * fc, pz * fc) > 0.45;
-			if (z + 10 < elev_blocks && cave_block) cave |= 1u << z;
+			const ColXY cm = col_xy(perm[N_MCAVE], px * fm, py * fm);
+			uint32_t big = 0;
+			for (int z = 0; z < (int)els; z++) {
+				const long long z_abs = oz + z;
+				double mcave_thresh;
+				if (z_abs > -400) mcave_thresh = 2.0;
+				else {
+					double v = (double)(z_abs + 600) / 300.0;
+					v = v > -0.502 ? v : -0.502;
+					v = v < 0.0 ? v : 0.0;
+					mcave_thresh = 1.0 + v;
+				}
+				if (perlin3_col(perm[N_MCAVE], g3, cm, (double)z_abs * fm) > mcave_thresh) big |= 1u << z;
+			}
+			const ColXY cc = col_xy(perm[N_CAVE], px * fc, py * fc);
+			for (int z = 0; z < (int)els; z++) {
+				const bool cave_block = ((big >> z) & 1u) || perlin3_col(perm[N_CAVE], g3, cc, (double)(oz + z) * fc) > 0.45;
+				if (z + 10 < elev_blocks && cave_block) cave |= 1u << z;
+			}
 		}
 		// ... then every ore stream is drawn from in (column, z) order: rank of this column's first draw by a block scan
 #pragma unroll
