@@ -148,28 +148,11 @@ __device__ double perlin2(const uint8_t *t, const double (*g2)[2], double x, dou
 	const double f01 = surflet2(t, g2, nx, ny + 1, dx, ey), f11 = surflet2(t, g2, nx + 1, ny + 1, ex, ey);
 	return clamp1((f00 + f10 + f01 + f11) * 3.1604938271604937);
 }
-__device__ __forceinline__ double surflet3(const uint8_t *t, const double (*g3)[3], long long cx, long long cy, long long cz, double dx, double dy, double dz) {
-	const double attn = 1.0 - (dx * dx + dy * dy + dz * dz);
-	if (attn > 0.0) {
-		const unsigned g = t[perm2(t, cx, cy) ^ (unsigned)(cz & 0xff)] & 31u;
-		return powi4(attn) * (dx * g3[g][0] + dy * g3[g][1] + dz * g3[g][2]);
-	}
-	return 0.0;
-}
-__device__ double perlin3(const uint8_t *t, const double (*g3)[3], double x, double y, double z) {
-	const double fx = floor(x), fy = floor(y), fz = floor(z);
-	const long long nx = (long long)fx, ny = (long long)fy, nz = (long long)fz;
-	const double dx = x - fx, dy = y - fy, dz = z - fz, ex = dx - 1.0, ey = dy - 1.0, ez = dz - 1.0;
-	const double f000 = surflet3(t, g3, nx, ny, nz, dx, dy, dz), f100 = surflet3(t, g3, nx + 1, ny, nz, ex, dy, dz);
-	const double f010 = surflet3(t, g3, nx, ny + 1, nz, dx, ey, dz), f110 = surflet3(t, g3, nx + 1, ny + 1, nz, ex, ey, dz);
-	const double f001 = surflet3(t, g3, nx, ny, nz + 1, dx, dy, ez), f101 = surflet3(t, g3, nx + 1, ny, nz + 1, ex, dy, ez);
-	const double f011 = surflet3(t, g3, nx, ny + 1, nz + 1, dx, ey, ez), f111 = surflet3(t, g3, nx + 1, ny + 1, nz + 1, ex, ey, ez);
-	return clamp1((f000 + f100 + f010 + f110 + f001 + f101 + f011 + f111) * 3.8898553255531074);
-}
-
-// perlin3 for the cells of ONE column: x and y are fixed, so the floors, the fractions, the four (x, y) corner hashes and
-// the partial sums dx*dx + dy*dy are worked out once per column and noise; every expression keeps the operand order of
-// surflet3 / perlin3 above, so the values are the same bit for bit.
+// perlin3 (noise 0.7.0: eight surflets attn^4 * dot(gradient, d), attn = 1 - (dx*dx + dy*dy + dz*dz), gradient index
+// t[t[t[x] ^ y] ^ z] & 31, sum * 3.8898553255531074, clamped; oracle/mapgen_oracle.c perlin3 is the literal form) for
+// the cells of ONE column: x and y are fixed, so the floors, the fractions, the four (x, y) corner hashes and the
+// partial sums dx*dx + dy*dy are worked out once per column and noise; every expression keeps the operand order of
+// the literal form, so the values are the same bit for bit.
 struct ColXY {
 	double dx, dy, ex, ey, s00, s10, s01, s11;
 	unsigned h00, h10, h01, h11;
